@@ -1,0 +1,150 @@
+/*
+ * panvc3_b200 — C-ABI of the B200-native project_alignments hot path.
+ *
+ * This is the drop-in boundary for the per-record work of PanVC 3's project_alignments
+ * (reference: libpanvc3/alignment_projector.cc:30-154, called from
+ * project-alignments/project_alignments.cc:721-732 and, for mates, :900).  One call processes a whole SoA batch of
+ * records on one GPU: projection of the start position through the MSA gap vectors, CIGAR rewrite, indel-run
+ * detection, realignment of the flagged runs and splice/collapse — bit-exact with the reference CPU code.
+ *
+ * Plain C, plain pointers and sizes; no CUDA or torch types.  All functions return PV3_OK (0) or a negative
+ * pv3_status; pv3_last_error() gives the message.  A context is single-submitter (one host thread at a time), owns
+ * one CUDA stream and all device memory, and is bound to one device (one context per GPU / per process rank).
+ *
+ * Encodings (what the reference's in-memory types already hold, so the adapter can memcpy):
+ *   seq   one byte per base, seqan3::dna5 rank  A=0 C=1 G=2 N=3 T=4     (lib/seqan3/.../nucleotide/dna5.hpp:95-110)
+ *   qual  one byte per base, seqan3::phred42 rank 0..41; an empty range selects the integer DP
+ *         (alignment_projector.cc:76,97)
+ *   cig   uint32  len << 4 | op,  op order M I D N S H P = X  (BAM)
+ *   gap rows  uint64 words, LSB first, bit = 1 where the aligned row has '-'   (msa_index.hh:22-32,58-65)
+ *   reference contigs  raw FASTA bytes, no case folding (rewrite_cigar.hh:104-110 compares raw bytes)
+ */
+#ifndef PANVC3_B200_H
+#define PANVC3_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PV3_ABI_VERSION 1
+
+typedef struct pv3_ctx pv3_ctx;
+
+typedef enum {
+	PV3_OK = 0,
+	PV3_ERR_INVALID = -1,   /* bad argument */
+	PV3_ERR_CUDA = -2,      /* CUDA runtime failure (no device, OOM, launch error) — never falls back to the CPU */
+	PV3_ERR_CAPACITY = -3,  /* an output buffer was too small; required sizes are in pv3_batch_out.{cig,rr}_used */
+	PV3_ERR_STATE = -4      /* call order (e.g. project before index_commit) */
+} pv3_status;
+
+/* Per-record flags: the record was rejected where the reference would abort or has undefined behaviour.
+ * Outputs of a flagged record are unspecified (cig_len = 0, rr_len = 0). */
+#define PV3_FLAG_BAD_OP      0x1u   /* CIGAR op outside MIDNSHP=X            (rewrite_cigar.hh:149-151 libbio_fail) */
+#define PV3_FLAG_POS_OOB     0x2u   /* reference-consuming base past the last non-gap of the source row
+                                       (select0 returns size(), rrr_vector_15.hpp:666, then OOB access) */
+#define PV3_FLAG_QUERY_OOB   0x4u   /* query_pos >= |SEQ|                    (rewrite_cigar.hh:102 assert) */
+#define PV3_FLAG_REF_OOB     0x8u   /* excess >= |dst contig|                (rewrite_cigar.hh:103 assert) */
+#define PV3_FLAG_TRACE_UB    0x10u  /* affine traceback leaves the matrix — reference UB, only with gap_open < 0
+                                       (affine_gap_policy.hpp:96-101) */
+#define PV3_FLAG_EMPTY_CIGAR 0x20u  /* final CIGAR empty: collapse_cigar_operations UB (cigar.cc:16-18) */
+#define PV3_FLAG_BAD_QUAL    0x40u  /* non-empty QUAL whose length differs from SEQ */
+#define PV3_FLAG_BAD_ID      0x80u  /* row or contig id not in the index (the CLI exits on failed lookups,
+                                       project_alignments.cc:113-114) */
+
+/* Input batch, structure of arrays. Replaces the reference's per-record project_task slots
+ * (project_alignments.cc:219-330) and the arguments of alignment_projector::project_alignment
+ * (include/panvc3/alignment_projector.hh:58-68). */
+typedef struct {
+	uint64_t        n;         /* records */
+	const uint32_t *src_row;   /* [n] row id (pv3_index_add_row) of the sequence the read was aligned to  — src_seq_entry */
+	const uint32_t *dst_row;   /* [n] row id of the projection target (e.g. REF)                          — dst_seq_entry */
+	const uint32_t *dst_ref;   /* [n] contig id (pv3_index_add_ref) of the target's unaligned bases       — ref_seq */
+	const uint64_t *src_pos;   /* [n] 0-based position in the source sequence                             — src_pos */
+	const uint64_t *seq_off;   /* [n+1] */
+	const uint8_t  *seq;       /* dna5 ranks                                                              — query_seq */
+	const uint64_t *qual_off;  /* [n+1], or NULL when no record has QUAL                                  — base_qualities */
+	const uint8_t  *qual;      /* phred42 ranks */
+	const uint64_t *cig_off;   /* [n+1] */
+	const uint32_t *cig;       /* BAM-packed ops                                                          — cigar_seq */
+} pv3_batch_in;
+
+/* Output batch. CIGARs and realigned ranges live in arenas and are addressed per record by (off, len); arena order
+ * is not record order. Mirrors the accessors alignment(), realigned_reference_ranges(), realigned_query_ranges()
+ * (alignment_projector.hh:70-72) and project_alignment's return value. */
+typedef struct {
+	uint64_t *dst_pos;   /* [n] projected position */
+	uint32_t *flags;     /* [n] PV3_FLAG_* */
+	uint64_t *cig_off;   /* [n] */
+	uint32_t *cig_len;   /* [n] */
+	uint32_t *cig;       /* [cig_cap] arena */
+	uint64_t  cig_cap;
+	uint64_t *rr_off;    /* [n] */
+	uint32_t *rr_len;    /* [n] realigned runs of the record */
+	uint64_t *rr;        /* [4*rr_cap]: ref_location (as the reference reports it, alignment_projector.cc:69-72), ref_length,
+	                        query_location, query_length */
+	uint64_t  rr_cap;
+	/* filled by the call */
+	uint64_t  cig_used;        /* arena words used (or required, with PV3_ERR_CAPACITY) */
+	uint64_t  rr_used;         /* runs written (or required) */
+	uint64_t  n_flagged;       /* records with flags != 0 */
+	uint64_t  n_realigned;     /* records with at least one realigned run */
+	uint64_t  dp_cells;        /* sum over runs of ref_length * query_length (GCUPS numerator) */
+} pv3_batch_out;
+
+/* Device-side durations of the last pv3_project or pv3_project_device call, from CUDA events on the context's stream. */
+typedef struct {
+	float    ms_rewrite;     /* projection + CIGAR rewrite + run detection kernel */
+	float    ms_realign;     /* DP + traceback kernel (0 when no run was found) */
+	float    ms_splice;      /* splice + collapse kernel */
+	float    ms_total;       /* first kernel start to last kernel end */
+	float    ms_h2d, ms_d2h; /* host path only */
+	uint64_t launches;       /* kernels launched by the call */
+} pv3_timing;
+
+/* -- lifetime ------------------------------------------------------------------------------------------------------ */
+int         pv3_abi_version(void);
+int         pv3_create(pv3_ctx **out, int device);          /* fails with PV3_ERR_CUDA when no usable GPU exists */
+void        pv3_destroy(pv3_ctx *);
+const char *pv3_last_error(const pv3_ctx *);                 /* ctx may be NULL: error of the last failed pv3_create */
+
+/* -- index (replaces msa_index::sequence_entry over sdsl::rrr_vector<15>, include/panvc3/msa_index.hh:47-74) --------- */
+int pv3_index_add_row(pv3_ctx *, const uint64_t *gap_words, uint64_t n_bits);  /* returns row id >= 0 */
+int pv3_index_add_ref(pv3_ctx *, const char *bases, uint64_t n);               /* returns contig id >= 0 */
+int pv3_index_commit(pv3_ctx *);                /* builds rank/select directories, uploads; index is immutable afterwards */
+
+/* -- parameters (project_alignments -g / -e; defaults 0 / -1, project-alignments/cmdline.ggo) ------------------------ */
+int pv3_set_params(pv3_ctx *, int32_t gap_open, int32_t gap_ext);
+int pv3_set_quality_lut(pv3_ctx *, const int32_t *lut84);   /* optional override of the Malde LUT (align.hh:28-37) */
+int pv3_get_quality_lut(const pv3_ctx *, int32_t *lut84);
+
+/* -- the hot path -------------------------------------------------------------------------------------------------- */
+/* Host buffers in and out (pinned or pageable); H2D copies, kernels and D2H copies all happen inside the call. */
+int pv3_project(pv3_ctx *, const pv3_batch_in *in, pv3_batch_out *out);
+/* Every pointer inside *in and *out is a DEVICE pointer on the context's device (the structs themselves are host). */
+int pv3_project_device(pv3_ctx *, const pv3_batch_in *in, pv3_batch_out *out);
+/* msa_index::sequence_entry::project_position (msa_index.hh:253-258) for n independent positions (mates,
+ * project_alignments.cc:880-906). Host buffers. */
+int pv3_project_positions(pv3_ctx *, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint64_t *pos,
+                          uint64_t *out_pos);
+/* Raw index queries for parity tests: op 0 = rank0(row,x) zeros in [0,x); 1 = select0(row,x) (x >= 1); 2 = access. */
+int pv3_index_query(pv3_ctx *, int op, uint64_t n, const uint32_t *row, const uint64_t *x, uint64_t *out);
+
+/* Parity probe: stage 1 stops after rewrite_cigar() (include/panvc3/rewrite_cigar.hh:19) — no run detection, no
+ * realignment; stage 0 (default) is the full project_alignment. */
+int pv3_set_stage(pv3_ctx *, int stage);
+
+int pv3_get_timing(const pv3_ctx *, pv3_timing *out);
+uint64_t pv3_total_launches(const pv3_ctx *);
+
+/* -- pinned host memory for batches --------------------------------------------------------------------------------- */
+void *pv3_host_alloc(size_t bytes);
+void  pv3_host_free(void *);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,243 @@
+"""ctypes binding of the C-ABI (include/panvc3_b200.h → panvc3_b200/libpanvc3_b200.so).
+
+This is the same stub a maintainer of the reference would write for any FFI.  It never falls back to
+a CPU implementation: if the library is missing or no GPU is usable the calls raise."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .batch import ProjectedBatch, RecordBatch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpanvc3_b200.so")
+
+PV3_OK, PV3_ERR_INVALID, PV3_ERR_CUDA, PV3_ERR_CAPACITY, PV3_ERR_STATE = 0, -1, -2, -3, -4
+
+EXPORTED_SYMBOLS = [
+    "pv3_abi_version", "pv3_create", "pv3_destroy", "pv3_last_error", "pv3_index_add_row", "pv3_index_add_ref",
+    "pv3_index_commit", "pv3_set_params", "pv3_set_quality_lut", "pv3_get_quality_lut", "pv3_project",
+    "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_get_timing",
+    "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
+]
+
+
+class BatchIn(C.Structure):
+    _fields_ = [("n", C.c_uint64), ("src_row", C.c_void_p), ("dst_row", C.c_void_p), ("dst_ref", C.c_void_p),
+                ("src_pos", C.c_void_p), ("seq_off", C.c_void_p), ("seq", C.c_void_p), ("qual_off", C.c_void_p),
+                ("qual", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p)]
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("dst_pos", C.c_void_p), ("flags", C.c_void_p), ("cig_off", C.c_void_p), ("cig_len", C.c_void_p),
+                ("cig", C.c_void_p), ("cig_cap", C.c_uint64), ("rr_off", C.c_void_p), ("rr_len", C.c_void_p),
+                ("rr", C.c_void_p), ("rr_cap", C.c_uint64),
+                ("cig_used", C.c_uint64), ("rr_used", C.c_uint64), ("n_flagged", C.c_uint64),
+                ("n_realigned", C.c_uint64), ("dp_cells", C.c_uint64)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("ms_rewrite", C.c_float), ("ms_realign", C.c_float), ("ms_splice", C.c_float), ("ms_total", C.c_float),
+                ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("launches", C.c_uint64)]
+
+    def as_dict(self) -> dict:
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Pv3Error(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"panvc3_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library(path: str = LIB_PATH) -> C.CDLL:
+    """Loads the CUDA library. Raises if it has not been built — the product has no CPU path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} not built; run `python -m panvc3_b200.build` (nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(path)
+    lib.pv3_abi_version.restype = C.c_int
+    lib.pv3_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+    lib.pv3_destroy.argtypes = [C.c_void_p]
+    lib.pv3_destroy.restype = None
+    lib.pv3_last_error.argtypes = [C.c_void_p]
+    lib.pv3_last_error.restype = C.c_char_p
+    lib.pv3_index_add_row.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.pv3_index_add_ref.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64]
+    lib.pv3_index_commit.argtypes = [C.c_void_p]
+    lib.pv3_set_params.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+    lib.pv3_set_quality_lut.argtypes = [C.c_void_p, C.c_void_p]
+    lib.pv3_get_quality_lut.argtypes = [C.c_void_p, C.c_void_p]
+    lib.pv3_set_stage.argtypes = [C.c_void_p, C.c_int]
+    lib.pv3_project.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+    lib.pv3_project_device.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+    lib.pv3_project_positions.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.pv3_index_query.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.pv3_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+    lib.pv3_total_launches.argtypes = [C.c_void_p]
+    lib.pv3_total_launches.restype = C.c_uint64
+    lib.pv3_host_alloc.argtypes = [C.c_size_t]
+    lib.pv3_host_alloc.restype = C.c_void_p
+    lib.pv3_host_free.argtypes = [C.c_void_p]
+    lib.pv3_host_free.restype = None
+    _lib = lib
+    return lib
+
+
+def _ptr(a: np.ndarray | None):
+    return None if a is None else a.ctypes.data
+
+
+class PinnedArena:
+    """Pinned host memory (cudaMallocHost) carved into numpy arrays — the 'pinned SoA batch' of the host pipeline."""
+
+    def __init__(self, lib: C.CDLL, nbytes: int):
+        self._lib = lib
+        self.nbytes = int(nbytes)
+        self.ptr = lib.pv3_host_alloc(self.nbytes)
+        if not self.ptr:
+            raise Pv3Error(PV3_ERR_CUDA, "pv3_host_alloc failed")
+        self._off = 0
+
+    def take(self, shape, dtype) -> np.ndarray:
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        off = (self._off + 255) // 256 * 256
+        if off + n > self.nbytes:
+            raise MemoryError("pinned arena exhausted")
+        buf = (C.c_uint8 * n).from_address(self.ptr + off)
+        self._off = off + n
+        arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        return arr
+
+    def close(self):
+        if self.ptr:
+            self._lib.pv3_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """One GPU context (pv3_ctx). Not thread-safe; one per process rank."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        st = self.lib.pv3_create(C.byref(h), device)
+        if st != PV3_OK:
+            raise Pv3Error(st, (self.lib.pv3_last_error(None) or b"").decode())
+        self.h = h
+        self.device = device
+        self.n_rows = 0
+        self.n_refs = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pv3_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st: int):
+        if st < 0:
+            raise Pv3Error(st, (self.lib.pv3_last_error(self.h) or b"").decode())
+        return st
+
+    # ---- index ---------------------------------------------------------------------------------------------------
+    def add_row(self, gap_words: np.ndarray, n_bits: int) -> int:
+        w = np.ascontiguousarray(gap_words, dtype=np.uint64)
+        self.n_rows += 1
+        return self._check(self.lib.pv3_index_add_row(self.h, w.ctypes.data if w.size else None, int(n_bits)))
+
+    def add_ref(self, bases: bytes) -> int:
+        self.n_refs += 1
+        return self._check(self.lib.pv3_index_add_ref(self.h, bytes(bases), len(bases)))
+
+    def commit(self):
+        self._check(self.lib.pv3_index_commit(self.h))
+
+    def set_params(self, gap_open: int = 0, gap_ext: int = -1):
+        self._check(self.lib.pv3_set_params(self.h, gap_open, gap_ext))
+
+    def set_stage(self, stage: int):
+        self._check(self.lib.pv3_set_stage(self.h, stage))
+
+    def quality_lut(self) -> np.ndarray:
+        lut = np.zeros(84, dtype=np.int32)
+        self._check(self.lib.pv3_get_quality_lut(self.h, lut.ctypes.data))
+        return lut.reshape(42, 2)
+
+    # ---- hot path ------------------------------------------------------------------------------------------------
+    def project(self, batch: RecordBatch, out: ProjectedBatch | None = None) -> ProjectedBatch:
+        """Host buffers in and out (pv3_project). `out` may be a preallocated (e.g. pinned) ProjectedBatch."""
+        n = batch.n
+        bi = BatchIn(n, _ptr(batch.src_row), _ptr(batch.dst_row), _ptr(batch.dst_ref), _ptr(batch.src_pos), _ptr(batch.seq_off),
+                     _ptr(batch.seq), _ptr(batch.qual_off), _ptr(batch.qual) if batch.qual_off is not None else None,
+                     _ptr(batch.cig_off), _ptr(batch.cig))
+        if out is None:
+            out = alloc_output(n, int(batch.cig.size) * 3 + n * 8 + 1024, n // 8 + 1024)
+        for _ in range(8):
+            bo = BatchOut(_ptr(out.dst_pos), _ptr(out.flags), _ptr(out.cig_off), _ptr(out.cig_len), _ptr(out.cig), out.cig.size,
+                          _ptr(out.rr_off), _ptr(out.rr_len), _ptr(out.rr), out.rr.shape[0], 0, 0, 0, 0, 0)
+            st = self.lib.pv3_project(self.h, C.byref(bi), C.byref(bo))
+            if st == PV3_ERR_CAPACITY:
+                out = alloc_output(n, max(int(bo.cig_used) * 2, out.cig.size * 2), max(int(bo.rr_used) * 2, out.rr.shape[0] * 2))
+                continue
+            self._check(st)
+            out.stats = dict(cig_used=int(bo.cig_used), rr_used=int(bo.rr_used), n_flagged=int(bo.n_flagged),
+                             n_realigned=int(bo.n_realigned), dp_cells=int(bo.dp_cells))
+            return out
+        raise Pv3Error(PV3_ERR_CAPACITY, "output capacity retry limit")
+
+    def project_device(self, bi: BatchIn, bo: BatchOut) -> int:
+        """Device pointers in and out (pv3_project_device). Returns the status (PV3_ERR_CAPACITY is not raised)."""
+        st = self.lib.pv3_project_device(self.h, C.byref(bi), C.byref(bo))
+        if st not in (PV3_OK, PV3_ERR_CAPACITY):
+            self._check(st)
+        return st
+
+    def project_positions(self, src_row, dst_row, pos) -> np.ndarray:
+        s = np.ascontiguousarray(src_row, dtype=np.uint32)
+        d = np.ascontiguousarray(dst_row, dtype=np.uint32)
+        p = np.ascontiguousarray(pos, dtype=np.uint64)
+        out = np.zeros(p.size, dtype=np.uint64)
+        self._check(self.lib.pv3_project_positions(self.h, p.size, _ptr(s), _ptr(d), _ptr(p), _ptr(out)))
+        return out
+
+    def index_query(self, op: int, row, x) -> np.ndarray:
+        r = np.ascontiguousarray(row, dtype=np.uint32)
+        xx = np.ascontiguousarray(x, dtype=np.uint64)
+        out = np.zeros(xx.size, dtype=np.uint64)
+        self._check(self.lib.pv3_index_query(self.h, op, xx.size, _ptr(r), _ptr(xx), _ptr(out)))
+        return out
+
+    def timing(self) -> dict:
+        t = Timing()
+        self._check(self.lib.pv3_get_timing(self.h, C.byref(t)))
+        return t.as_dict()
+
+    def total_launches(self) -> int:
+        return int(self.lib.pv3_total_launches(self.h))
+
+
+def alloc_output(n: int, cig_cap: int, rr_cap: int, arena: PinnedArena | None = None) -> ProjectedBatch:
+    mk = (lambda shape, dt: arena.take(shape, dt)) if arena is not None else (lambda shape, dt: np.zeros(shape, dtype=dt))
+    return ProjectedBatch(dst_pos=mk((n,), np.uint64), flags=mk((n,), np.uint32), cig_off=mk((n,), np.uint64),
+                          cig_len=mk((n,), np.uint32), cig=mk((max(cig_cap, 1),), np.uint32), rr_off=mk((n,), np.uint64),
+                          rr_len=mk((n,), np.uint32), rr=mk((max(rr_cap, 1), 4), np.uint64))

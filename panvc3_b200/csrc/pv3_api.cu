@@ -1,0 +1,565 @@
+// panvc3_b200 — host side of the C-ABI (include/panvc3_b200.h): context, index upload, batch pipeline.
+//
+// The context replaces, for the hot path, what project_task / input_processor own in the reference
+// (project-alignments/project_alignments.cc:219-330,485-654): per-task alignment_projector instances and their reusable
+// vectors become device buffers owned here and reused across batches; the loaded msa_index and the reference contigs
+// (sequence_buffer_store) become one immutable device-resident index.
+// There is no CPU fallback: every entry point fails with PV3_ERR_CUDA if the device is unusable.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pv3_kernels.h"
+
+using namespace pv3;
+
+namespace {
+
+std::string g_create_error;
+
+struct DevBuf {
+	void  *p = nullptr;
+	size_t cap = 0;
+	cudaError_t ensure(size_t bytes)
+	{
+		if (bytes <= cap) return cudaSuccess;
+		if (p) cudaFree(p);
+		p = nullptr; cap = 0;
+		size_t const want = bytes + bytes / 4 + 256;
+		cudaError_t e = cudaMalloc(&p, want);
+		if (e == cudaSuccess) cap = want;
+		return e;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+	template <typename T> T *as() const { return (T *) p; }
+};
+
+struct HostRow { std::vector <uint64_t> words; uint64_t n_bits; };
+struct HostRef { std::string bases; };
+
+} // namespace
+
+struct pv3_ctx {
+	int          device = 0;
+	int          n_sms = 148;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t  ev[8] = {};
+	std::string  error;
+
+	std::vector <HostRow> rows;
+	std::vector <HostRef> refs;
+	bool         committed = false;
+	DevBuf       index_mem;              // words, directories, contigs — one allocation
+	DevBuf       row_desc, ref_desc;
+	uint64_t     index_bytes = 0;
+
+	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
+	int32_t      lut[84];
+	int          stage = 0;
+
+	// device work buffers
+	DevBuf       counters, jobs, dp_arena, pool;
+	Counters    *h_counters = nullptr;   // pinned
+	// host-path device mirrors
+	DevBuf       in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig;
+	DevBuf       out_dst_pos, out_flags, out_cig_off, out_cig_len, out_arena, out_rr_off, out_rr_len, out_rr;
+	uint64_t     arena_cap_hint = 0, rr_cap_hint = 0;
+
+	pv3_timing   timing = {};
+	uint64_t     total_launches = 0;
+};
+
+namespace {
+
+int fail(pv3_ctx *ctx, int code, const char *fmt, ...)
+{
+	char buf[512];
+	va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+	if (ctx) ctx->error = buf; else g_create_error = buf;
+	return code;
+}
+
+#define PV3_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+	return fail((ctx), PV3_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); } while (0)
+
+// Malde quality scores truncated to int32 (align.hh:28-37); reference base at phred 41
+// (alignment_projector.cc:108). Same expression order as the reference.
+void default_quality_lut(int32_t *lut)
+{
+	for (int q = 0; q < 42; ++q) {
+		double const lhs_e = 1.0 / std::pow(10.0, 41 / 10.0);
+		double const rhs_e = 1.0 / std::pow(10.0, q / 10.0);
+		double const combined_e = lhs_e + rhs_e - lhs_e / 3.0 * rhs_e * 4.0;
+		lut[2 * q] = (int32_t) (2.0 + std::log2(1.0 - combined_e));
+		lut[2 * q + 1] = (int32_t) (2.0 - std::log2(3.0) + std::log2(combined_e));
+	}
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+} // namespace
+
+extern "C" {
+
+int pv3_abi_version(void) { return PV3_ABI_VERSION; }
+
+int pv3_create(pv3_ctx **out, int device)
+{
+	if (!out) return fail(nullptr, PV3_ERR_INVALID, "pv3_create: out is NULL");
+	*out = nullptr;
+	int n_dev = 0;
+	cudaError_t e = cudaGetDeviceCount(&n_dev);
+	if (e != cudaSuccess || n_dev == 0)
+		return fail(nullptr, PV3_ERR_CUDA, "pv3_create: no CUDA device (%s); panvc3_b200 has no CPU fallback",
+			e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+	if (device < 0 || device >= n_dev) return fail(nullptr, PV3_ERR_INVALID, "pv3_create: device %d out of range (%d devices)", device, n_dev);
+	PV3_CUDA(nullptr, cudaSetDevice(device));
+	cudaDeviceProp prop;
+	PV3_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10)
+		return fail(nullptr, PV3_ERR_CUDA, "pv3_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+	pv3_ctx *ctx = new pv3_ctx;
+	ctx->device = device;
+	ctx->n_sms = prop.multiProcessorCount;
+	default_quality_lut(ctx->lut);
+	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaStreamCreate failed"); }
+	for (auto &ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaEventCreate failed"); }
+	if (cudaMallocHost((void **) &ctx->h_counters, sizeof(Counters)) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaMallocHost failed"); }
+	if (ctx->counters.ensure(sizeof(Counters)) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaMalloc failed"); }
+	*out = ctx;
+	return PV3_OK;
+}
+
+void pv3_destroy(pv3_ctx *ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool,
+			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
+			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
+			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
+		b->release();
+	if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+	for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+const char *pv3_last_error(const pv3_ctx *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int pv3_index_add_row(pv3_ctx *ctx, const uint64_t *gap_words, uint64_t n_bits)
+{
+	if (!ctx || (!gap_words && n_bits)) return fail(ctx, PV3_ERR_INVALID, "pv3_index_add_row: bad argument");
+	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_add_row: index already committed");
+	HostRow row;
+	row.n_bits = n_bits;
+	row.words.assign(gap_words, gap_words + (n_bits + 63) / 64);
+	ctx->rows.emplace_back(std::move(row));
+	return (int) ctx->rows.size() - 1;
+}
+
+int pv3_index_add_ref(pv3_ctx *ctx, const char *bases, uint64_t n)
+{
+	if (!ctx || (!bases && n)) return fail(ctx, PV3_ERR_INVALID, "pv3_index_add_ref: bad argument");
+	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_add_ref: index already committed");
+	HostRef ref; ref.bases.assign(bases, bases + n);
+	ctx->refs.emplace_back(std::move(ref));
+	return (int) ctx->refs.size() - 1;
+}
+
+int pv3_index_commit(pv3_ctx *ctx)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_commit: already committed");
+	PV3_CUDA(ctx, cudaSetDevice(ctx->device));
+
+	// Layout of the single index allocation: per row [words | blk_zeros | sel], then the contigs; 256-byte aligned parts.
+	struct RowLayout { size_t words_off, blk_off, sel_off; uint64_t n_blocks, n_words_alloc, n_zeros, n_sel; };
+	std::vector <RowLayout> lay(ctx->rows.size());
+	size_t total = 0;
+	for (size_t r = 0; r < ctx->rows.size(); ++r) {
+		auto const &row = ctx->rows[r];
+		RowLayout &L = lay[r];
+		L.n_blocks = (row.n_bits + BLK_BITS - 1) / BLK_BITS; if (!L.n_blocks) L.n_blocks = 1;
+		L.n_words_alloc = L.n_blocks * BLK_WORDS + PAD_WORDS;
+		L.words_off = total; total = align_up(total + L.n_words_alloc * 8, 256);
+		L.blk_off = total; total = align_up(total + (L.n_blocks + 1 + 32) * 8, 256);
+		L.sel_off = total; // size known after counting zeros
+		uint64_t zeros = 0;
+		for (uint64_t w = 0; w < row.words.size(); ++w) {
+			uint64_t v = row.words[w];
+			if (w == row.words.size() - 1 && row.n_bits % 64) v |= ~0ull << (row.n_bits % 64);
+			zeros += (uint64_t) __builtin_popcountll(~v);
+		}
+		L.n_zeros = zeros;
+		L.n_sel = (zeros ? (zeros - 1) / SEL_RATE + 1 : 0) + 1;
+		total = align_up(total + L.n_sel * 4, 256);
+	}
+	std::vector <size_t> ref_off(ctx->refs.size());
+	for (size_t r = 0; r < ctx->refs.size(); ++r) { ref_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 16, 256); }
+	if (!total) total = 256;
+
+	std::vector <uint8_t> host(total, 0);
+	for (size_t r = 0; r < ctx->rows.size(); ++r) {
+		auto const &row = ctx->rows[r];
+		RowLayout const &L = lay[r];
+		uint64_t *words = (uint64_t *) (host.data() + L.words_off);
+		uint64_t *blk = (uint64_t *) (host.data() + L.blk_off);
+		uint32_t *sel = (uint32_t *) (host.data() + L.sel_off);
+		for (uint64_t w = 0; w < L.n_words_alloc; ++w) words[w] = (w < row.words.size()) ? row.words[w] : ~0ull;
+		if (row.n_bits % 64) words[row.words.size() - 1] |= ~0ull << (row.n_bits % 64);
+		uint64_t z = 0, next_sel = 0;   // next_sel: index of the next sample to write
+		for (uint64_t b = 0; b < L.n_blocks; ++b) {
+			blk[b] = z;
+			uint64_t zb = 0;
+			for (int w = 0; w < BLK_WORDS; ++w) zb += (uint64_t) __builtin_popcountll(~words[b * BLK_WORDS + w]);
+			// zero numbers (1-based) in this block: z+1 .. z+zb; sample s covers zero number s*SEL_RATE+1
+			while (next_sel + 1 < L.n_sel && next_sel * (uint64_t) SEL_RATE + 1 <= z + zb) sel[next_sel++] = (uint32_t) b;
+			z += zb;
+		}
+		for (uint64_t b = L.n_blocks; b < L.n_blocks + 1 + 32; ++b) blk[b] = z;
+		for (uint64_t s = next_sel; s < L.n_sel; ++s) sel[s] = (uint32_t) (L.n_blocks - 1);   // sentinel(s)
+	}
+	for (size_t r = 0; r < ctx->refs.size(); ++r) memcpy(host.data() + ref_off[r], ctx->refs[r].bases.data(), ctx->refs[r].bases.size());
+
+	PV3_CUDA(ctx, ctx->index_mem.ensure(total));
+	PV3_CUDA(ctx, cudaMemcpy(ctx->index_mem.p, host.data(), total, cudaMemcpyHostToDevice));
+	ctx->index_bytes = total;
+
+	std::vector <RowDesc> rd(ctx->rows.size() ? ctx->rows.size() : 1);
+	for (size_t r = 0; r < ctx->rows.size(); ++r) {
+		uint8_t *base = ctx->index_mem.as <uint8_t>();
+		rd[r].words = (const uint64_t *) (base + lay[r].words_off);
+		rd[r].blk_zeros = (const uint64_t *) (base + lay[r].blk_off);
+		rd[r].sel = (const uint32_t *) (base + lay[r].sel_off);
+		rd[r].n_bits = ctx->rows[r].n_bits;
+		rd[r].n_zeros = lay[r].n_zeros;
+		rd[r].n_blocks = lay[r].n_blocks;
+		rd[r].n_words_alloc = lay[r].n_words_alloc;
+	}
+	std::vector <RefDesc> fd(ctx->refs.size() ? ctx->refs.size() : 1);
+	for (size_t r = 0; r < ctx->refs.size(); ++r) {
+		fd[r].bases = (const char *) (ctx->index_mem.as <uint8_t>() + ref_off[r]);
+		fd[r].n = ctx->refs[r].bases.size();
+	}
+	PV3_CUDA(ctx, ctx->row_desc.ensure(rd.size() * sizeof(RowDesc)));
+	PV3_CUDA(ctx, ctx->ref_desc.ensure(fd.size() * sizeof(RefDesc)));
+	PV3_CUDA(ctx, cudaMemcpy(ctx->row_desc.p, rd.data(), rd.size() * sizeof(RowDesc), cudaMemcpyHostToDevice));
+	PV3_CUDA(ctx, cudaMemcpy(ctx->ref_desc.p, fd.data(), fd.size() * sizeof(RefDesc), cudaMemcpyHostToDevice));
+	ctx->committed = true;
+	// host copies are no longer needed
+	for (auto &row : ctx->rows) { std::vector <uint64_t>().swap(row.words); }
+	for (auto &ref : ctx->refs) { uint64_t n = ref.bases.size(); std::string().swap(ref.bases); (void) n; }
+	return PV3_OK;
+}
+
+int pv3_set_params(pv3_ctx *ctx, int32_t gap_open, int32_t gap_ext)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	ctx->gap_open = gap_open; ctx->gap_ext = gap_ext;
+	return PV3_OK;
+}
+
+int pv3_set_quality_lut(pv3_ctx *ctx, const int32_t *lut84)
+{
+	if (!ctx || !lut84) return PV3_ERR_INVALID;
+	memcpy(ctx->lut, lut84, sizeof ctx->lut);
+	return PV3_OK;
+}
+
+int pv3_get_quality_lut(const pv3_ctx *ctx, int32_t *lut84)
+{
+	if (!ctx || !lut84) return PV3_ERR_INVALID;
+	memcpy(lut84, ctx->lut, sizeof ctx->lut);
+	return PV3_OK;
+}
+
+int pv3_set_stage(pv3_ctx *ctx, int stage)   // not in the public header: parity probe (1 = rewrite_cigar() only)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	ctx->stage = stage;
+	return PV3_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+constexpr size_t POOL_BUDGET = (size_t) 8 << 30;   // HBM scratch for traces of runs too large for shared memory
+
+K1Params make_k1(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
+{
+	K1Params P;
+	memset(&P, 0, sizeof P);
+	P.n = in->n;
+	P.src_row = in->src_row; P.dst_row = in->dst_row; P.dst_ref = in->dst_ref; P.src_pos = in->src_pos;
+	P.seq_off = in->seq_off; P.seq = in->seq; P.qual_off = in->qual_off; P.qual = in->qual;
+	P.cig_off = in->cig_off; P.cig = in->cig;
+	P.rows = ctx->row_desc.as <RowDesc>(); P.n_rows = (uint32_t) ctx->rows.size();
+	P.refs = ctx->ref_desc.as <RefDesc>(); P.n_refs = (uint32_t) ctx->refs.size();
+	P.dst_pos = out->dst_pos; P.flags = out->flags; P.cig_out_off = out->cig_off; P.cig_out_len = out->cig_len;
+	P.arena = out->cig; P.arena_cap = out->cig_cap;
+	P.rr_off = out->rr_off; P.rr_len = out->rr_len; P.rr = out->rr; P.rr_cap = out->rr_cap;
+	P.jobs = ctx->jobs.as <Job>();
+	P.counters = ctx->counters.as <Counters>();
+	P.gap_open = ctx->gap_open; P.gap_ext = ctx->gap_ext;
+	P.stage = ctx->stage;
+	return P;
+}
+
+int fetch_counters(pv3_ctx *ctx)
+{
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PV3_OK;
+}
+
+// The kernel pipeline on device-resident buffers. Events: 0 start, 1 after K1, 2 after K3, 3 after K4.
+int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
+{
+	out->cig_used = out->rr_used = out->n_flagged = out->n_realigned = out->dp_cells = 0;
+	ctx->timing.ms_rewrite = ctx->timing.ms_realign = ctx->timing.ms_splice = ctx->timing.ms_total = 0;
+	ctx->timing.launches = 0;
+	if (!in->n) return PV3_OK;
+	PV3_CUDA(ctx, ctx->jobs.ensure((out->rr_cap ? out->rr_cap : 1) * sizeof(Job)));
+	K1Params P = make_k1(ctx, in, out);
+	PV3_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+	launch_k1(P, ctx->n_sms, ctx->stream);
+	PV3_CUDA(ctx, cudaGetLastError());
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+	ctx->timing.launches += 1;
+	int st = fetch_counters(ctx);
+	if (st) return st;
+	Counters c = *ctx->h_counters;
+	out->rr_used = c.job_cursor;
+	out->cig_used = c.arena_cursor + c.dp_path;   // upper bound of what the splice kernel may still append
+	if (c.overflow) {
+		ctx->total_launches += ctx->timing.launches;
+		return fail(ctx, PV3_ERR_CAPACITY, "output capacity too small: need cig_cap >= %llu, rr_cap >= %llu",
+			(unsigned long long) out->cig_used, (unsigned long long) out->rr_used);
+	}
+	uint64_t const n_jobs = c.job_cursor;
+	bool ran_dp = false;
+	if (n_jobs) {
+		if (c.arena_cursor + c.dp_path > out->cig_cap) {
+			ctx->total_launches += ctx->timing.launches;
+			return fail(ctx, PV3_ERR_CAPACITY, "output capacity too small: need cig_cap >= %llu", (unsigned long long) out->cig_used);
+		}
+		K3Params K;
+		memset(&K, 0, sizeof K);
+		K.k1 = P; K.n_jobs = n_jobs;
+		PV3_CUDA(ctx, ctx->dp_arena.ensure((c.dp_path + 1) * 4));
+		K.dp_arena = ctx->dp_arena.as <uint32_t>(); K.dp_arena_cap = c.dp_path;
+		uint64_t grid_warps = k3_default_grid_warps(ctx->n_sms);
+		if (c.dp_max_pool > k3_smem_pool_bytes()) {
+			size_t const slot = align_up((size_t) c.dp_max_pool, 256);
+			uint64_t const fit = POOL_BUDGET / slot ? POOL_BUDGET / slot : 1;
+			if (grid_warps > fit) grid_warps = fit;
+			if (grid_warps > n_jobs) grid_warps = n_jobs;
+			grid_warps = (grid_warps + 7) / 8 * 8;
+			PV3_CUDA(ctx, ctx->pool.ensure(slot * grid_warps));
+			K.pool = ctx->pool.as <uint8_t>(); K.pool_slot_bytes = slot;
+		}
+		memcpy(K.lut, ctx->lut, sizeof K.lut);
+		launch_k3(K, ctx->n_sms, grid_warps, ctx->stream);
+		PV3_CUDA(ctx, cudaGetLastError());
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+		launch_k4(P, n_jobs, K.dp_arena, ctx->stream);
+		PV3_CUDA(ctx, cudaGetLastError());
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+		ctx->timing.launches += 2;
+		st = fetch_counters(ctx);
+		if (st) return st;
+		c = *ctx->h_counters;
+		ran_dp = true;
+		if (c.overflow) {
+			ctx->total_launches += ctx->timing.launches;
+			return fail(ctx, PV3_ERR_CAPACITY, "output capacity too small (splice): need cig_cap >= %llu", (unsigned long long) c.arena_cursor);
+		}
+	}
+	out->cig_used = c.arena_cursor;
+	out->rr_used = c.job_cursor;
+	out->n_flagged = c.n_flagged;
+	out->n_realigned = c.n_realigned;
+	out->dp_cells = c.dp_cells;
+	cudaEventElapsedTime(&ctx->timing.ms_rewrite, ctx->ev[0], ctx->ev[1]);
+	if (ran_dp) {
+		cudaEventElapsedTime(&ctx->timing.ms_realign, ctx->ev[1], ctx->ev[2]);
+		cudaEventElapsedTime(&ctx->timing.ms_splice, ctx->ev[2], ctx->ev[3]);
+		cudaEventElapsedTime(&ctx->timing.ms_total, ctx->ev[0], ctx->ev[3]);
+	} else ctx->timing.ms_total = ctx->timing.ms_rewrite;
+	ctx->total_launches += ctx->timing.launches;
+	return PV3_OK;
+}
+
+int check_ready(pv3_ctx *ctx, const char *who)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	if (!ctx->committed) return fail(ctx, PV3_ERR_STATE, "%s: pv3_index_commit has not been called", who);
+	cudaError_t e = cudaSetDevice(ctx->device);
+	if (e != cudaSuccess) return fail(ctx, PV3_ERR_CUDA, "%s: cudaSetDevice failed: %s", who, cudaGetErrorString(e));
+	return PV3_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int pv3_project_device(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
+{
+	int st = check_ready(ctx, "pv3_project_device");
+	if (st) return st;
+	if (!in || !out) return fail(ctx, PV3_ERR_INVALID, "pv3_project_device: NULL batch");
+	ctx->timing.ms_h2d = ctx->timing.ms_d2h = 0;
+	return run_pipeline(ctx, in, out);
+}
+
+int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
+{
+	int st = check_ready(ctx, "pv3_project");
+	if (st) return st;
+	if (!in || !out) return fail(ctx, PV3_ERR_INVALID, "pv3_project: NULL batch");
+	uint64_t const n = in->n;
+	out->cig_used = out->rr_used = out->n_flagged = out->n_realigned = out->dp_cells = 0;
+	if (!n) return PV3_OK;
+	uint64_t const seq_bytes = in->seq_off[n], cig_words = in->cig_off[n];
+	uint64_t const qual_bytes = in->qual_off ? in->qual_off[n] : 0;
+
+	struct Copy { DevBuf *buf; const void *src; size_t bytes; };
+	Copy const copies[] = {
+		{ &ctx->in_src_row, in->src_row, n * 4 }, { &ctx->in_dst_row, in->dst_row, n * 4 }, { &ctx->in_dst_ref, in->dst_ref, n * 4 },
+		{ &ctx->in_src_pos, in->src_pos, n * 8 }, { &ctx->in_seq_off, in->seq_off, (n + 1) * 8 }, { &ctx->in_seq, in->seq, seq_bytes },
+		{ &ctx->in_qual_off, in->qual_off, in->qual_off ? (n + 1) * 8 : 0 }, { &ctx->in_qual, in->qual, qual_bytes },
+		{ &ctx->in_cig_off, in->cig_off, (n + 1) * 8 }, { &ctx->in_cig, in->cig, cig_words * 4 },
+	};
+	for (auto const &c : copies) PV3_CUDA(ctx, c.buf->ensure(c.bytes ? c.bytes : 16));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
+	for (auto const &c : copies)
+		if (c.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(c.buf->p, c.src, c.bytes, cudaMemcpyHostToDevice, ctx->stream));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
+
+	pv3_batch_in din = *in;
+	din.src_row = ctx->in_src_row.as <uint32_t>(); din.dst_row = ctx->in_dst_row.as <uint32_t>(); din.dst_ref = ctx->in_dst_ref.as <uint32_t>();
+	din.src_pos = ctx->in_src_pos.as <uint64_t>(); din.seq_off = ctx->in_seq_off.as <uint64_t>(); din.seq = ctx->in_seq.as <uint8_t>();
+	din.qual_off = in->qual_off ? ctx->in_qual_off.as <uint64_t>() : nullptr; din.qual = ctx->in_qual.as <uint8_t>();
+	din.cig_off = ctx->in_cig_off.as <uint64_t>(); din.cig = ctx->in_cig.as <uint32_t>();
+
+	PV3_CUDA(ctx, ctx->out_dst_pos.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_flags.ensure(n * 4));
+	PV3_CUDA(ctx, ctx->out_cig_off.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_cig_len.ensure(n * 4));
+	PV3_CUDA(ctx, ctx->out_rr_off.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_rr_len.ensure(n * 4));
+
+	uint64_t arena_cap = cig_words * 3 + n * 8 + 1024, rr_cap = n / 8 + 1024;
+	if (arena_cap < ctx->arena_cap_hint) arena_cap = ctx->arena_cap_hint;
+	if (rr_cap < ctx->rr_cap_hint) rr_cap = ctx->rr_cap_hint;
+	pv3_batch_out dout;
+	float ms_k[4] = { 0, 0, 0, 0 };
+	uint64_t launches = 0;
+	for (int attempt = 0; ; ++attempt) {
+		PV3_CUDA(ctx, ctx->out_arena.ensure(arena_cap * 4));
+		PV3_CUDA(ctx, ctx->out_rr.ensure(rr_cap * 32));
+		memset(&dout, 0, sizeof dout);
+		dout.dst_pos = ctx->out_dst_pos.as <uint64_t>(); dout.flags = ctx->out_flags.as <uint32_t>();
+		dout.cig_off = ctx->out_cig_off.as <uint64_t>(); dout.cig_len = ctx->out_cig_len.as <uint32_t>();
+		dout.cig = ctx->out_arena.as <uint32_t>(); dout.cig_cap = arena_cap;
+		dout.rr_off = ctx->out_rr_off.as <uint64_t>(); dout.rr_len = ctx->out_rr_len.as <uint32_t>();
+		dout.rr = ctx->out_rr.as <uint64_t>(); dout.rr_cap = rr_cap;
+		st = run_pipeline(ctx, &din, &dout);
+		launches += ctx->timing.launches;
+		if (st == PV3_ERR_CAPACITY && attempt < 6) {
+			// grow from what the kernels reported and run the batch again (results of the failed attempt are discarded)
+			if (dout.cig_used + 1024 > arena_cap) arena_cap = dout.cig_used * 2 + 1024; else arena_cap *= 2;
+			if (dout.rr_used + 64 > rr_cap) rr_cap = dout.rr_used * 2 + 64;
+			continue;
+		}
+		if (st) return st;
+		break;
+	}
+	ctx->arena_cap_hint = arena_cap; ctx->rr_cap_hint = rr_cap;
+	ms_k[0] = ctx->timing.ms_rewrite; ms_k[1] = ctx->timing.ms_realign; ms_k[2] = ctx->timing.ms_splice; ms_k[3] = ctx->timing.ms_total;
+
+	out->cig_used = dout.cig_used; out->rr_used = dout.rr_used; out->n_flagged = dout.n_flagged;
+	out->n_realigned = dout.n_realigned; out->dp_cells = dout.dp_cells;
+	if (dout.cig_used > out->cig_cap || dout.rr_used > out->rr_cap)
+		return fail(ctx, PV3_ERR_CAPACITY, "host output capacity too small: need cig_cap >= %llu, rr_cap >= %llu",
+			(unsigned long long) dout.cig_used, (unsigned long long) dout.rr_used);
+
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[6], ctx->stream));
+	struct Back { void *dst; const void *src; size_t bytes; };
+	Back const backs[] = {
+		{ out->dst_pos, dout.dst_pos, n * 8 }, { out->flags, dout.flags, n * 4 }, { out->cig_off, dout.cig_off, n * 8 },
+		{ out->cig_len, dout.cig_len, n * 4 }, { out->rr_off, dout.rr_off, n * 8 }, { out->rr_len, dout.rr_len, n * 4 },
+		{ out->cig, dout.cig, dout.cig_used * 4 }, { out->rr, dout.rr, dout.rr_used * 32 },
+	};
+	for (auto const &b : backs)
+		if (b.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(b.dst, b.src, b.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[7], ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	cudaEventElapsedTime(&ctx->timing.ms_h2d, ctx->ev[4], ctx->ev[5]);
+	cudaEventElapsedTime(&ctx->timing.ms_d2h, ctx->ev[6], ctx->ev[7]);
+	ctx->timing.ms_rewrite = ms_k[0]; ctx->timing.ms_realign = ms_k[1]; ctx->timing.ms_splice = ms_k[2]; ctx->timing.ms_total = ms_k[3];
+	ctx->timing.launches = launches;
+	return PV3_OK;
+}
+
+int pv3_project_positions(pv3_ctx *ctx, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint64_t *pos, uint64_t *out_pos)
+{
+	int st = check_ready(ctx, "pv3_project_positions");
+	if (st) return st;
+	if (!n) return PV3_OK;
+	if (!src_row || !dst_row || !pos || !out_pos) return fail(ctx, PV3_ERR_INVALID, "pv3_project_positions: NULL argument");
+	PV3_CUDA(ctx, ctx->in_src_row.ensure(n * 4)); PV3_CUDA(ctx, ctx->in_dst_row.ensure(n * 4));
+	PV3_CUDA(ctx, ctx->in_src_pos.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_dst_pos.ensure(n * 8));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->in_src_row.p, src_row, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->in_dst_row.p, dst_row, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->in_src_pos.p, pos, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+	launch_positions(ctx->row_desc.as <RowDesc>(), (uint32_t) ctx->rows.size(), n, ctx->in_src_row.as <uint32_t>(),
+		ctx->in_dst_row.as <uint32_t>(), ctx->in_src_pos.as <uint64_t>(), ctx->out_dst_pos.as <uint64_t>(), ctx->stream);
+	PV3_CUDA(ctx, cudaGetLastError());
+	ctx->total_launches += 1;
+	PV3_CUDA(ctx, cudaMemcpyAsync(out_pos, ctx->out_dst_pos.p, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PV3_OK;
+}
+
+int pv3_index_query(pv3_ctx *ctx, int op, uint64_t n, const uint32_t *row, const uint64_t *x, uint64_t *out)
+{
+	int st = check_ready(ctx, "pv3_index_query");
+	if (st) return st;
+	if (op < 0 || op > 2) return fail(ctx, PV3_ERR_INVALID, "pv3_index_query: op must be 0, 1 or 2");
+	if (!n) return PV3_OK;
+	PV3_CUDA(ctx, ctx->in_src_row.ensure(n * 4)); PV3_CUDA(ctx, ctx->in_src_pos.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_dst_pos.ensure(n * 8));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->in_src_row.p, row, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->in_src_pos.p, x, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+	launch_index_query(ctx->row_desc.as <RowDesc>(), (uint32_t) ctx->rows.size(), op, n, ctx->in_src_row.as <uint32_t>(),
+		ctx->in_src_pos.as <uint64_t>(), ctx->out_dst_pos.as <uint64_t>(), ctx->stream);
+	PV3_CUDA(ctx, cudaGetLastError());
+	ctx->total_launches += 1;
+	PV3_CUDA(ctx, cudaMemcpyAsync(out, ctx->out_dst_pos.p, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PV3_OK;
+}
+
+int pv3_get_timing(const pv3_ctx *ctx, pv3_timing *out)
+{
+	if (!ctx || !out) return PV3_ERR_INVALID;
+	*out = ctx->timing;
+	return PV3_OK;
+}
+
+uint64_t pv3_total_launches(const pv3_ctx *ctx) { return ctx ? ctx->total_launches : 0; }
+
+void *pv3_host_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+	return p;
+}
+
+void pv3_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+} // extern "C"

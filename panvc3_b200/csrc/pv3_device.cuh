@@ -1,0 +1,182 @@
+// panvc3_b200 — device-side data layout and warp-cooperative rank/select primitives (sm_100a).
+//
+// Replaces msa_index::sequence_entry over sdsl::rrr_vector<15> (reference include/panvc3/msa_index.hh:47-74,239-258;
+// lib/sdsl-lite/include/sdsl/rrr_vector_15.hpp:460-559 rank, :664-701 select).  rank0/select0/access are pure functions
+// of the bit sequence, so the H0-compressed blocks are replaced by plain words + a block directory that one warp
+// reads with coalesced loads:
+//
+//   words      uint64, LSB first, bit = 1 ⇔ gap; bits >= n_bits are 1; PAD_WORDS all-ones words follow so that a
+//              32-word window load never needs a bounds check
+//   blk_zeros  uint64 per 512-bit block: zeros in [0, 512*b); n_blocks+1 entries + 32 entries of padding (= n_zeros)
+//   sel        uint32 per SEL_RATE zeros: index of the block holding zero number s*SEL_RATE+1 (1-based); one sentinel
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace pv3 {
+
+constexpr int      BLK_WORDS = 8;            // 512-bit blocks
+constexpr int      BLK_BITS  = 512;
+constexpr uint32_t SEL_RATE  = 8192;
+constexpr int      PAD_WORDS = 72;           // >= 64 + BLK_WORDS
+constexpr unsigned FULL      = 0xffffffffu;
+
+struct RowDesc {
+	const uint64_t *words;
+	const uint64_t *blk_zeros;
+	const uint32_t *sel;
+	uint64_t        n_bits;
+	uint64_t        n_zeros;
+	uint64_t        n_blocks;   // ceil(n_bits / 512), at least 1
+	uint64_t        n_words_alloc;
+};
+
+struct RefDesc {
+	const char *bases;
+	uint64_t    n;
+};
+
+// One realigned indel run (indel_run_checker.cc:104-118 + alignment_projector.cc:61-73).
+struct Job {
+	uint64_t rec;
+	uint64_t ref_loc;      // DP window start in the target contig (true window, m_ref_range.location)
+	uint32_t ref_len;
+	uint32_t qry_loc;
+	uint32_t qry_len;
+	uint32_t op_begin;     // [op_begin, op_end) of the record's rewritten ops is replaced
+	uint32_t op_end;
+	uint32_t out_len;      // realigned ops (filled by the DP kernel)
+	uint64_t out_off;      // offset into the DP op arena
+};
+
+struct Counters {
+	unsigned long long arena_cursor;   // CIGAR arena words handed out
+	unsigned long long job_cursor;     // runs found
+	unsigned long long n_flagged;
+	unsigned long long n_realigned;    // records with >= 1 run
+	unsigned long long dp_cells;       // sum R*Q
+	unsigned long long dp_path;        // sum R+Q   (DP op arena bound)
+	unsigned long long dp_pool;        // sum of per-job scratch bytes
+	unsigned long long dp_max_pool;    // max per-job scratch bytes
+	unsigned long long dp_arena_cursor;
+	unsigned long long job_ticket;     // work-stealing counter of the DP kernel
+	unsigned int       overflow;       // bit0: CIGAR arena, bit1: rr/jobs, bit2: DP op arena
+	unsigned int       pad;
+};
+
+// BAM op codes
+enum : uint32_t { OP_M = 0, OP_I = 1, OP_D = 2, OP_N = 3, OP_S = 4, OP_H = 5, OP_P = 6, OP_EQ = 7, OP_X = 8, OP_NONE = 15 };
+
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ unsigned lanemask_lt() { unsigned m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
+
+__device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src)
+{
+	unsigned lo = __shfl_sync(FULL, (unsigned) v, src);
+	unsigned hi = __shfl_sync(FULL, (unsigned) (v >> 32), src);
+	return ((uint64_t) hi << 32) | lo;
+}
+
+// Position (0..31) of the k-th (1-based) set bit of x; caller guarantees popc(x) >= k. Branch-free popcount descent.
+__device__ __forceinline__ unsigned select_in_u32(unsigned x, unsigned k)
+{
+	unsigned pos = 0, c;
+	c = __popc(x & 0xffffu); if (k > c) { k -= c; pos += 16; x >>= 16; }
+	c = __popc(x & 0xffu);   if (k > c) { k -= c; pos += 8;  x >>= 8; }
+	c = __popc(x & 0xfu);    if (k > c) { k -= c; pos += 4;  x >>= 4; }
+	c = __popc(x & 0x3u);    if (k > c) { k -= c; pos += 2;  x >>= 2; }
+	c = x & 1u;              if (k > c) { pos += 1; }
+	return pos;
+}
+
+// Position (0..63) of the k-th (1-based) set bit of x; caller guarantees popc(x) >= k.
+__device__ __forceinline__ unsigned select_in_word(uint64_t x, unsigned k)
+{
+	unsigned lo = (unsigned) x, c = __popc(lo);
+	if (k <= c) return select_in_u32(lo, k);
+	return 32u + select_in_u32((unsigned) (x >> 32), k - c);
+}
+
+// ---- warp-cooperative queries: every lane passes the same arguments and receives the same result -----------------
+
+// zeros in [0, pos)  — project_aligned_position (msa_index.hh:247-251)
+__device__ __forceinline__ uint64_t rank0_warp(const RowDesc &r, uint64_t pos)
+{
+	if (pos >= r.n_bits) return r.n_zeros;
+	unsigned const lane = lane_id();
+	uint64_t const b = pos / BLK_BITS;
+	unsigned const wi = (unsigned) ((pos % BLK_BITS) / 64), bit = (unsigned) (pos % 64);
+	unsigned contrib = 0;
+	if (lane <= wi) {
+		uint64_t inv = ~__ldg(r.words + b * BLK_WORDS + lane);
+		if (lane == wi) inv &= (bit ? ((1ull << bit) - 1ull) : 0ull);
+		contrib = __popcll(inv);
+	}
+	contrib = __reduce_add_sync(FULL, contrib);
+	return __ldg(r.blk_zeros + b) + contrib;
+}
+
+// position of the k-th zero, k >= 1 — aligned_position(p) = select0(p + 1) (msa_index.hh:239-244);
+// returns n_bits when the row has fewer than k zeros (rrr_vector_15.hpp:666).
+__device__ __forceinline__ uint64_t select0_warp(const RowDesc &r, uint64_t k)
+{
+	if (k == 0 || k > r.n_zeros) return r.n_bits;
+	unsigned const lane = lane_id();
+	uint64_t const s = (k - 1) / SEL_RATE;
+	uint64_t lo = __ldg(r.sel + s), hi = __ldg(r.sel + s + 1);
+	while (hi - lo >= 32) {
+		uint64_t const mid = lo + (hi - lo + 1) / 2;
+		if (__ldg(r.blk_zeros + mid) < k) lo = mid; else hi = mid - 1;
+	}
+	uint64_t const v = __ldg(r.blk_zeros + lo + lane);
+	unsigned const m = __ballot_sync(FULL, (lo + lane <= hi) && (v < k));
+	uint64_t const b = lo + __popc(m) - 1;                      // lane 0 always qualifies
+	uint64_t const base = shfl_u64(v, __popc(m) - 1);
+	unsigned need = (unsigned) (k - base);                      // 1..512
+	uint64_t inv = 0;
+	unsigned pc = 0;
+	if (lane < BLK_WORDS) { inv = ~__ldg(r.words + b * BLK_WORDS + lane); pc = __popcll(inv); }
+	unsigned incl = pc;
+	#pragma unroll
+	for (int d = 1; d < BLK_WORDS; d <<= 1) { unsigned t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
+	unsigned const hit = __ballot_sync(FULL, lane < BLK_WORDS && incl >= need);
+	int const wl = __ffs(hit) - 1;
+	unsigned const before = __shfl_sync(FULL, incl - pc, wl);
+	uint64_t const w = shfl_u64(inv, wl);
+	return b * BLK_BITS + (uint64_t) wl * 64 + select_in_word(w, need - before);
+}
+
+// ---- single-thread versions (position-only queries: mates, parity probes) -----------------------------------------
+
+__device__ inline uint64_t rank0_thread(const RowDesc &r, uint64_t pos)
+{
+	if (pos >= r.n_bits) return r.n_zeros;
+	uint64_t const b = pos / BLK_BITS;
+	unsigned const wi = (unsigned) ((pos % BLK_BITS) / 64), bit = (unsigned) (pos % 64);
+	uint64_t z = __ldg(r.blk_zeros + b);
+	for (unsigned w = 0; w < wi; ++w) z += __popcll(~__ldg(r.words + b * BLK_WORDS + w));
+	if (bit) z += __popcll(~__ldg(r.words + b * BLK_WORDS + wi) & ((1ull << bit) - 1ull));
+	return z;
+}
+
+__device__ inline uint64_t select0_thread(const RowDesc &r, uint64_t k)
+{
+	if (k == 0 || k > r.n_zeros) return r.n_bits;
+	uint64_t const s = (k - 1) / SEL_RATE;
+	uint64_t lo = __ldg(r.sel + s), hi = __ldg(r.sel + s + 1);
+	while (lo < hi) {
+		uint64_t const mid = lo + (hi - lo + 1) / 2;
+		if (__ldg(r.blk_zeros + mid) < k) lo = mid; else hi = mid - 1;
+	}
+	unsigned need = (unsigned) (k - __ldg(r.blk_zeros + lo));
+	for (unsigned w = 0; w < (unsigned) BLK_WORDS; ++w) {
+		uint64_t const inv = ~__ldg(r.words + lo * BLK_WORDS + w);
+		unsigned const pc = __popcll(inv);
+		if (need <= pc) return lo * BLK_BITS + w * 64 + select_in_word(inv, need);
+		need -= pc;
+	}
+	return r.n_bits; // unreachable for a consistent directory
+}
+
+} // namespace pv3

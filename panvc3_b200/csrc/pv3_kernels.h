@@ -1,0 +1,73 @@
+// panvc3_b200 — kernel parameter blocks and host-side launchers (internal; the public surface is include/panvc3_b200.h).
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/panvc3_b200.h"
+#include "pv3_device.cuh"
+
+
+namespace pv3 {
+
+struct K1Params {
+	uint64_t        n;
+	const uint32_t *src_row, *dst_row, *dst_ref;
+	const uint64_t *src_pos, *seq_off;
+	const uint8_t  *seq;
+	const uint64_t *qual_off;    // may be null
+	const uint8_t  *qual;
+	const uint64_t *cig_off;
+	const uint32_t *cig;
+	const RowDesc  *rows; uint32_t n_rows;
+	const RefDesc  *refs; uint32_t n_refs;
+	uint64_t       *dst_pos;
+	uint32_t       *flags;
+	uint64_t       *cig_out_off;
+	uint32_t       *cig_out_len;
+	uint32_t       *arena; uint64_t arena_cap;
+	uint64_t       *rr_off;
+	uint32_t       *rr_len;
+	uint64_t       *rr; uint64_t rr_cap;
+	Job            *jobs;
+	Counters       *counters;
+	int32_t         gap_open, gap_ext;
+	int             stage;       // 0 = full pipeline, 1 = rewrite only (parity probe of rewrite_cigar())
+};
+
+// Scratch bytes one DP job needs: byte trace (Q+1)x(R+1), strip boundary arrays (H, up: int32; tup: byte), staged
+// reference ranks.
+__host__ __device__ inline unsigned long long dp_pool_bytes(uint32_t R, uint32_t Q, bool /*affine*/)
+{
+	unsigned long long const cols = (unsigned long long) R + 1, rows = (unsigned long long) Q + 1;
+	unsigned long long const a4 = ~3ull;
+	return ((rows * cols + 3) & a4) + 8 * cols + ((cols + 3) & a4) + ((cols + 3) & a4);
+}
+
+struct K3Params {
+	K1Params        k1;             // inputs, index, flags, counters, jobs
+	uint64_t        n_jobs;
+	uint32_t       *dp_arena; uint64_t dp_arena_cap;    // realigned ops, R+Q words reserved per job
+	uint8_t        *pool; uint64_t pool_slot_bytes;     // global scratch, one slot per resident warp (for jobs too large for smem)
+	int32_t         lut[84];        // quality LUT: [2*q] match, [2*q+1] mismatch
+};
+
+struct K4Params {
+	K1Params        k1;
+	K3Params const *unused;
+	uint64_t        n_jobs;
+	const uint32_t *dp_arena;
+	const uint64_t *realigned_recs; // unused (records are found through jobs)
+};
+
+void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);
+void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
+void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);
+void launch_positions(const RowDesc *rows, uint32_t n_rows, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row,
+	const uint64_t *pos, uint64_t *out, cudaStream_t stream);
+void launch_index_query(const RowDesc *rows, uint32_t n_rows, int op, uint64_t n, const uint32_t *row, const uint64_t *x,
+	uint64_t *out, cudaStream_t stream);
+uint64_t k3_default_grid_warps(int n_sms);
+uint32_t k3_smem_pool_bytes();
+
+} // namespace pv3
