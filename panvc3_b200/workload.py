@@ -135,47 +135,47 @@ def sample_reads(msa: Msa, n: int, read_len: int, seed: int, sub: float = 0.005,
 
     seq_parts: dict[int, np.ndarray] = {}
     cig_parts: dict[int, list[int]] = {}
+    ar = np.arange(read_len)
+
+    def match_ops(fr: np.ndarray, rr: np.ndarray) -> list[int]:
+        if fr.size == 0:
+            return []
+        if cigar_style == "M":
+            return [(int(fr.size) << 4) | 0]
+        mm = fr != rr
+        cut = np.flatnonzero(np.diff(mm.view(np.int8))) + 1
+        bounds = np.concatenate([[0], cut, [mm.size]])
+        return [((int(b1 - b0)) << 4) | (8 if mm[b0] else 7) for b0, b1 in zip(bounds[:-1], bounds[1:])]
+
     for i in np.flatnonzero(special):
         fseq = msa.ungapped[int(src_row[i])]
         p = int(start[i])
-        read: list[int] = []
-        ops: list[tuple[int, int]] = []      # (op, len) vs founder, M-style or =/X decided below
-        mism: list[bool] = []
-        consumed = 0
-        k = 0
-        ins_at = int(rng.integers(5, read_len - 5)) if has_ins[i] else -1
-        del_at = int(rng.integers(5, read_len - 5)) if has_del[i] else -1
-        while k < read_len:
-            if k == ins_at:
-                ln = int(rng.integers(1, 4))
-                read.extend(rng.integers(0, 5, ln).tolist()); ops.append((1, ln)); ins_at = -1
-                continue
-            if k == del_at:
-                ln = int(rng.integers(1, 4))
-                ops.append((2, ln)); consumed += ln; del_at = -1
-                continue
-            fb = int(ranks_from_ascii(fseq[p + consumed:p + consumed + 1])[0])
-            rb = int(ranks[i, k])
-            read.append(rb)
-            mm = fb != rb
-            if cigar_style == "M":
-                if ops and ops[-1][0] == 0: ops[-1] = (0, ops[-1][1] + 1)
-                else: ops.append((0, 1))
-            else:
-                op = 8 if mm else 7
-                if ops and ops[-1][0] == op: ops[-1] = (op, ops[-1][1] + 1)
-                else: ops.append((op, 1))
-            consumed += 1
-            k += 1
+        ia = int(rng.integers(5, read_len - 5)) if has_ins[i] else -1
+        da = int(rng.integers(5, read_len - 5)) if has_del[i] else -1
+        li = int(rng.integers(1, 4)) if ia >= 0 else 0
+        ld = int(rng.integers(1, 4)) if da >= 0 else 0
+        fidx = p + ar + (ld if da >= 0 else 0) * (ar >= da)      # founder offset of each founder-consuming read base
+        fr = ranks_from_ascii(fseq[fidx])
+        rr = np.where(submask[i], ranks_from_ascii(_ACGT[rng.integers(0, 4, read_len)]), fr)
+        cuts = sorted({0, read_len} | ({ia} if ia >= 0 else set()) | ({da} if da >= 0 else set()))
+        read_parts: list[np.ndarray] = []
+        ops: list[int] = []
+        for c0, c1 in zip(cuts[:-1], cuts[1:]):
+            if c0 == da and da >= 0:
+                ops.append((ld << 4) | 2)
+            if c0 == ia and ia >= 0:
+                ins_b = rng.integers(0, 5, li).astype(np.uint8)
+                read_parts.append(ins_b); ops.append((li << 4) | 1)
+            read_parts.append(rr[c0:c1]); ops.extend(match_ops(fr[c0:c1], rr[c0:c1]))
         if has_clip[i]:
             a = int(rng.integers(1, 21))
-            clip = rng.integers(0, 4, a).tolist()
+            clip = rng.integers(0, 4, a).astype(np.uint8)
             if rng.random() < 0.5:
-                read = clip + read; ops = [(4, a)] + ops
+                read_parts.insert(0, clip); ops.insert(0, (a << 4) | 4)
             else:
-                read = read + clip; ops = ops + [(4, a)]
-        seq_parts[int(i)] = np.asarray(read, dtype=np.uint8)
-        cig_parts[int(i)] = [(ln << 4) | op for op, ln in ops]
+                read_parts.append(clip); ops.append((a << 4) | 4)
+        seq_parts[int(i)] = np.concatenate(read_parts).astype(np.uint8)
+        cig_parts[int(i)] = ops
 
     seq_len = np.full(n, read_len, dtype=np.int64)
     cig_len = np.ones(n, dtype=np.int64)
@@ -185,7 +185,7 @@ def sample_reads(msa: Msa, n: int, read_len: int, seed: int, sub: float = 0.005,
         fr = ranks_from_ascii(concat[base_idx[plain]].reshape(-1)).reshape(plain.size, read_len)
         mm = fr != ranks[plain]
         for j, i in enumerate(plain):
-            plain_cig[int(i)] = _rle_eqx(mm[j])
+            plain_cig[int(i)] = match_ops(fr[j], ranks[plain[j]])
             cig_len[i] = len(plain_cig[int(i)])
     for i, s in seq_parts.items():
         seq_len[i] = s.size

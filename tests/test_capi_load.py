@@ -1,0 +1,67 @@
+"""CPU tests: the C-ABI library builds for sm_100a, loads, exports every symbol include/*.h declares, and fails loudly
+without a GPU (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib_path():
+    from panvc3_b200 import build
+    return build.build()
+
+
+def declared_symbols():
+    names = set()
+    inc = os.path.join(ROOT, "include")
+    for f in os.listdir(inc):
+        if f.endswith(".h"):
+            text = open(os.path.join(inc, f)).read()
+            text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+            names.update(re.findall(r"\b(pv3_[a-z0-9_]+)\s*\(", text))
+    return sorted(names)
+
+
+def test_library_exports_every_declared_symbol(lib_path):
+    lib = ctypes.CDLL(lib_path)
+    names = declared_symbols()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/ but not exported"
+    from panvc3_b200 import capi
+    assert sorted(capi.EXPORTED_SYMBOLS) == names
+    assert lib.pv3_abi_version() == 1
+
+
+def test_sass_is_sm100a(lib_path):
+    import shutil, subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run([cuobjdump, "-lelf", lib_path], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+
+
+def test_no_cpu_fallback_without_gpu(lib_path):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from panvc3_b200 import capi
+    with pytest.raises(capi.Pv3Error) as ei:
+        capi.Context(0)
+    assert ei.value.code == capi.PV3_ERR_CUDA
+    assert "no CPU fallback" in str(ei.value) or "CUDA" in str(ei.value)
+
+
+def test_product_does_not_import_oracle():
+    """The product package must never reach into oracle/ (test infrastructure)."""
+    pkg = os.path.join(ROOT, "panvc3_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hh", ".cc")):
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle_lib" not in text and "pv3_oracle" not in text and "libpv3_ref" not in text, f"{f} references the oracle"

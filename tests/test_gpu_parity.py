@@ -1,0 +1,260 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C-ABI, against the CPU oracle on the same seeded inputs,
+against the committed golden vectors of the compiled reference, and through size-independent properties at full size."""
+import os
+
+import numpy as np
+import pytest
+
+import casegen
+from panvc3_b200.batch import RecordBatch, format_cigar, pack_bits, parse_cigar
+from parity import assert_same, checksum, load_golden_random
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from panvc3_b200 import build
+    build.build()
+    return True
+
+
+def device_index(msa):
+    from panvc3_b200.projector import MsaIndex
+    return MsaIndex.from_msa(msa)
+
+
+# ---------------------------------------------------------------------------------------------- rank / select / access
+@pytest.mark.parametrize("n_bits,density", [(1, 0.5), (64, 0.5), (511, 0.02), (512, 0.95), (513, 0.5), (70000, 0.01), (70000, 0.9),
+                                            (3_000_000, 0.02), (3_000_000, 0.999)])
+def test_index_queries_match_oracle(gpu, port, n_bits, density):
+    from panvc3_b200.projector import MsaIndex
+    rng = np.random.default_rng(n_bits)
+    bits = rng.random(n_bits) < density
+    if n_bits > 100000:
+        bits[100000:1500000] = True          # a long all-gap stretch: select samples far apart
+    words = pack_bits(bits)
+    idx = MsaIndex(); idx.add_entry("r", words, n_bits); idx.commit()
+    zeros_before = np.concatenate([[0], np.cumsum(~bits)])
+    pos = np.unique(np.concatenate([rng.integers(0, n_bits + 1, 4000), [0, n_bits, max(n_bits - 1, 0)]])).astype(np.uint64)
+    row = np.zeros(pos.size, np.uint32)
+    assert np.array_equal(idx.ctx.index_query(0, row, pos), zeros_before[pos.astype(np.int64)].astype(np.uint64))
+    nz = int(zeros_before[-1])
+    zero_pos = np.flatnonzero(~bits)
+    if nz:
+        k = np.unique(np.concatenate([rng.integers(1, nz + 1, 4000), [1, nz]])).astype(np.uint64)
+        got = idx.ctx.index_query(1, np.zeros(k.size, np.uint32), k)
+        assert np.array_equal(got, zero_pos[k.astype(np.int64) - 1].astype(np.uint64))
+    past = idx.ctx.index_query(1, np.zeros(2, np.uint32), np.array([nz + 1, nz + 5], np.uint64))
+    assert past.tolist() == [n_bits, n_bits]                 # rrr_vector_15.hpp:666
+    acc = np.minimum(pos, n_bits - 1).astype(np.uint64)
+    assert np.array_equal(idx.ctx.index_query(2, row, acc), bits[acc.astype(np.int64)].astype(np.uint64))
+    # oracle agreement on a sample (same numbers through the C restatement)
+    oi = port.make_index([(words, n_bits)], [])
+    for p in pos[:50]:
+        assert oi.rank0(0, int(p)) == int(zeros_before[int(p)])
+
+
+def test_project_positions_matches_oracle(gpu, port, workflow_msa):
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    rng = np.random.default_rng(3)
+    n = 5000
+    s = rng.integers(0, workflow_msa.n_rows, n).astype(np.uint32)
+    d = rng.integers(0, workflow_msa.n_rows, n).astype(np.uint32)
+    p = np.array([rng.integers(0, workflow_msa.ungapped[int(r)].size) for r in s], dtype=np.uint64)
+    got = idx.ctx.project_positions(s, d, p)
+    exp = np.array([oi.project_position(int(a), int(b), int(c)) for a, b, c in zip(s, d, p)], dtype=np.uint64)
+    assert np.array_equal(got, exp)
+
+
+# ---------------------------------------------------------------------------------------------- reference tables
+def test_reference_tables_through_projector_api(gpu, fixtures_json):
+    """tests/rewrite_cigar_inputs.tsv + tests/alignment_projector_inputs.tsv through the mirrored reference API."""
+    from panvc3_b200.projector import AlignmentProjector, make_sequence_entry_pair, rewrite_cigar
+    for table in ("rewrite_cigar", "alignment_projector"):
+        for case in fixtures_json[table]:
+            idx, src, dst, rid = make_sequence_entry_pair(case["src"], case["dst"])
+            pos, ops = rewrite_cigar(idx, case["src_pos"], case["cigar"], src, dst, case["query"], rid)
+            assert pos == case["tsv_expected_pos"]
+            assert format_cigar(ops) == case["ref_rewrite"]["cigar"], case
+            proj = AlignmentProjector(idx)
+            for key, qual, go in (("ref_project_integer", None, 0), ("ref_project_quality", [41] * len(case["query"]), 0),
+                                  ("ref_project_affine_go-2", None, -2)):
+                proj.reset()
+                p = proj.project_alignment(case["src_pos"], src, dst, rid, case["query"], case["cigar"], qual, go, -1)
+                assert p == case[key]["pos"]
+                assert proj.alignment_str() == case[key]["cigar"], (case, key)
+                got = [[a.location, a.length, b.location, b.length]
+                       for a, b in zip(proj.realigned_reference_ranges(), proj.realigned_query_ranges())]
+                assert got == case[key]["ranges"], (case, key)
+
+
+def test_golden_random_vectors_of_compiled_reference(gpu):
+    for msa, b, go, ge, full, rew in load_golden_random():
+        idx = device_index(msa)
+        assert_same(idx.project_batch(b, go, ge), full, b, f"gpu vs golden(reference) full go={go} ge={ge}")
+        idx.ctx.set_stage(1)
+        assert_same(idx.project_batch(b, go, ge), rew, b, f"gpu vs golden(reference) rewrite go={go} ge={ge}")
+
+
+# ---------------------------------------------------------------------------------------------- differential vs oracle
+@pytest.mark.parametrize("seed", range(12))
+def test_random_batches_match_oracle(gpu, port, seed):
+    n_cols = [64, 300, 1500, 6000][seed % 4]
+    msa, b = casegen.random_batch(2000 + seed, 1500, n_cols=n_cols, max_len=[12, 40][seed % 2])
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    for go, ge in [(0, -1), (0, -3), (-2, -1), (-5, -2), (3, -1)]:
+        for stage in (1, 0):
+            idx.ctx.set_stage(stage)
+            got = idx.project_batch(b, go, ge)
+            assert_same(got, oi.project_batch(b, go, ge, stage=stage), b, f"seed={seed} stage={stage} go={go} ge={ge}")
+            assert got.stats["n_flagged"] == int((got.flags != 0).sum())
+
+
+def test_random_batches_match_compiled_reference(gpu, port, ref):
+    """Same comparison against the reference's own code where oracle/_ref travelled to this box."""
+    msa, b = casegen.random_batch(77, 3000, n_cols=800)
+    idx = device_index(msa)
+    rows, refs = casegen.index_inputs(msa)
+    for go, ge in [(0, -1), (-2, -1)]:
+        keep = np.flatnonzero(port.make_index(rows, refs).project_batch(b, go, ge).flags == 0)
+        recs = []
+        for i in keep:
+            s = b.slice(int(i), int(i) + 1)
+            recs.append(dict(src_row=int(s.src_row[0]), dst_row=int(s.dst_row[0]), dst_ref=int(s.dst_ref[0]), src_pos=int(s.src_pos[0]),
+                             seq=s.seq, cigar=s.cig, qual=(s.qual if s.qual.size else None)))
+        sub = RecordBatch.from_records(recs)
+        assert_same(idx.project_batch(sub, go, ge), ref.make_index(rows, refs).project_batch(sub, go, ge), sub, f"gpu vs reference go={go}")
+
+
+def test_dp_modes_large_windows(gpu, port):
+    """Indel runs with windows beyond one 32-row strip and beyond the shared-memory trace (multi-strip + HBM trace)."""
+    rng = np.random.default_rng(11)
+    recs = []
+    rows = []
+    refs = []
+    for t, (a, bl) in enumerate([(40, 45), (100, 90), (33, 200), (300, 310), (5, 700), (1200, 900)]):
+        # source row: a bases then bl gaps; target row: a gaps then bl bases ⇒ rewrite gives aI blD ⇒ one run a x bl
+        src = "A" * 10 + "".join(rng.choice(list("ACGT"), a)) + "-" * bl + "C" * 10
+        core = "".join(rng.choice(list("ACGT"), bl))
+        dst = "A" * 10 + "-" * a + core + "C" * 10
+        rows += [src, dst]
+        query = src.replace("-", "")
+        # make the query resemble the target so that the trace is not trivial
+        qmid = list(core[:a]) if bl >= a else list(core + "".join(rng.choice(list("ACGT"), a - bl)))
+        for k in range(0, len(qmid), 7):
+            qmid[k] = "G"
+        query = "A" * 10 + "".join(qmid) + "C" * 10
+        for qual in (None, rng.integers(0, 42, len(query)).astype(np.uint8)):
+            recs.append(dict(src_row=2 * t, dst_row=2 * t + 1, dst_ref=t, src_pos=0, seq=query, cigar=f"{len(query)}M", qual=qual))
+        refs.append(dst.replace("-", "").encode())
+    from panvc3_b200.batch import bits_from_aligned_row
+    from panvc3_b200.projector import MsaIndex
+    idx = MsaIndex()
+    gap_rows = []
+    for r in rows:
+        w, n = bits_from_aligned_row(r)
+        idx.add_entry("", w, n); gap_rows.append((w, n))
+    for r in refs:
+        idx.add_reference(r)
+    idx.commit()
+    oi = port.make_index(gap_rows, refs)
+    b = RecordBatch.from_records(recs)
+    for go, ge in [(0, -1), (-3, -1), (2, -2)]:
+        got = idx.project_batch(b, go, ge)
+        exp = oi.project_batch(b, go, ge)
+        assert_same(got, exp, b, f"large windows go={go} ge={ge}")
+        assert int(exp.rr_len.sum()) >= len(recs) - 2
+
+
+def test_long_reads_overflow_the_stage(gpu, port):
+    """10 kb reads with hundreds of ops: exceeds the per-warp shared staging ⇒ count pass + direct write path."""
+    from panvc3_b200.workload import sample_reads, synth_msa
+    msa = synth_msa(60000, 3, seed=5, p_gap=0.03, mean_gap=3, snp=0.02, anticorrelated=0.004)
+    b = sample_reads(msa, 300, 10000, seed=6, sub=0.03, ins=0.0, dele=0.0, clip_frac=0.3, cigar_style="EQX")
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    got = idx.project_batch(b, 0, -1)
+    exp = oi.project_batch(b, 0, -1)
+    assert int(exp.cig_len.max()) > 300
+    assert_same(got, exp, b, "long reads")
+
+
+def test_error_flags(gpu, port):
+    from panvc3_b200.projector import AlignmentProjector, ProjectionAbort, make_sequence_entry_pair
+    idx, src, dst, rid = make_sequence_entry_pair("GAT-ACA", "GATTACA")
+    from panvc3_b200.batch import bits_from_aligned_row
+    oi = port.make_index([bits_from_aligned_row("GAT-ACA"), bits_from_aligned_row("GATTACA")], [b"GATTACA"])
+    recs = [dict(src_row=0, dst_row=1, src_pos=2, seq="TA", cigar=np.array([(2 << 4) | 9], np.uint32)),
+            dict(src_row=0, dst_row=1, src_pos=4, seq="TACA", cigar="4M"),
+            dict(src_row=0, dst_row=1, src_pos=2, seq="T", cigar="2M"),
+            dict(src_row=0, dst_row=1, src_pos=2, seq="", cigar="0M0P"),
+            dict(src_row=0, dst_row=1, src_pos=2, seq="TA", cigar="2M"),
+            dict(src_row=0, dst_row=7, src_pos=2, seq="TA", cigar="2M")]
+    b = RecordBatch.from_records(recs)
+    got = idx.project_batch(b)
+    assert got.flags.tolist() == [0x1, 0x2, 0x4, 0x20, 0, 0x80]
+    exp = oi.project_batch(RecordBatch.from_records(recs[:5]))
+    assert exp.flags.tolist() == got.flags.tolist()[:5]
+    assert got.cigar_str(4) == "1=1D1="
+    proj = AlignmentProjector(idx)
+    with pytest.raises(ProjectionAbort):
+        proj.project_alignment(2, src, dst, rid, "T", "2M", None, 0, -1)
+
+
+def test_empty_and_ragged_batches(gpu, port, workflow_msa):
+    idx = device_index(workflow_msa)
+    empty = RecordBatch.from_records([])
+    out = idx.project_batch(empty)
+    assert out.n == 0
+    recs = [dict(src_row=1, dst_row=0, src_pos=5, seq="", cigar="3D"),
+            dict(src_row=2, dst_row=0, src_pos=0, seq="ACGTACGT", cigar="8S"),
+            dict(src_row=3, dst_row=0, src_pos=100, seq="A", cigar="1M"),
+            dict(src_row=4, dst_row=0, src_pos=9000, seq="ACGT" * 50, cigar="5H100M10N100M5H")]
+    b = RecordBatch.from_records(recs)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    assert_same(idx.project_batch(b), oi.project_batch(b), b, "ragged")
+
+
+# ---------------------------------------------------------------------------------------------- full-size properties
+def test_full_size_config2_properties(gpu, port, workflow_msa):
+    """BASELINE configs[1]: test-workflow index, 1 M synthetic 150-bp reads. Full oracle comparison on a 20 k sample;
+    at full size: determinism, shard-additivity (checksum of shards == checksum of whole), reference span == query span."""
+    from panvc3_b200.workload import sample_reads
+    n = 1_000_000
+    b = sample_reads(workflow_msa, n, 150, seed=20261104 + 2)
+    idx = device_index(workflow_msa)
+    out = idx.project_batch(b)
+    assert out.stats["n_flagged"] == 0
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    sub = b.slice(0, 20000)
+    exp = oi.project_batch(sub, n_threads=os.cpu_count() or 1)
+    from panvc3_b200.batch import ProjectedBatch
+    head = ProjectedBatch(dst_pos=out.dst_pos[:20000], flags=out.flags[:20000], cig_off=out.cig_off[:20000], cig_len=out.cig_len[:20000],
+                          cig=out.cig, rr_off=out.rr_off[:20000], rr_len=out.rr_len[:20000], rr=out.rr)
+    assert_same(head, exp, sub, "config2 sample")
+    # determinism
+    out2 = idx.project_batch(b)
+    assert checksum(out) == checksum(out2)
+    # query-consuming op lengths of every output CIGAR add up to |SEQ| (projection never changes the read)
+    lens = out.cig_len.astype(np.int64)
+    rep = np.repeat(np.arange(n), lens)
+    within = np.arange(int(lens.sum())) - np.repeat(np.cumsum(lens) - lens, lens)
+    w = out.cig[out.cig_off.astype(np.int64)[rep] + within]
+    op, cnt = w & 0xF, (w >> 4).astype(np.int64)
+    qcons = np.isin(op, [0, 1, 4, 7, 8])
+    qsum = np.zeros(n, np.int64); np.add.at(qsum, rep[qcons], cnt[qcons])
+    assert np.array_equal(qsum, np.diff(b.seq_off).astype(np.int64))
+    # no two adjacent ops are equal (collapsed) and no zero-length op
+    assert (cnt > 0).all()
+    same_rec = rep[1:] == rep[:-1]
+    assert not ((op[1:] == op[:-1]) & same_rec).any()
+    # shards give the same per-record results as the whole
+    a0 = idx.project_batch(b.slice(0, n // 2)); a1 = idx.project_batch(b.slice(n // 2, n))
+    assert np.array_equal(np.concatenate([a0.dst_pos, a1.dst_pos]), out.dst_pos)
+    assert np.array_equal(np.concatenate([a0.cig_len, a1.cig_len]), out.cig_len)

@@ -1,0 +1,130 @@
+"""CPU tests (-m "not gpu"): pin the oracle port against the reference's golden vectors and the compiled reference."""
+import numpy as np
+import pytest
+
+import casegen
+from panvc3_b200.batch import RecordBatch, bits_from_aligned_row, format_cigar, parse_cigar
+from parity import assert_same, load_golden_random
+
+
+def _pair_index(lib, src, dst):
+    return lib.make_index([bits_from_aligned_row(src), bits_from_aligned_row(dst)], [dst.replace("-", "").encode()])
+
+
+def test_port_quality_lut_matches_survey(port):
+    lut = port.quality_lut()
+    # observed values of the compiled reference
+    for q, (m, mm) in {0: (-13, 0), 1: (0, 0), 2: (0, 0), 3: (0, 0), 5: (1, -1), 10: (1, -2), 20: (1, -6), 30: (1, -9), 41: (1, -12)}.items():
+        assert tuple(lut[q]) == (m, mm)
+
+
+@pytest.mark.parametrize("table", ["rewrite_cigar", "alignment_projector"])
+def test_port_reproduces_reference_tables(port, fixtures_json, table):
+    """tests/rewrite_cigar_inputs.tsv and tests/alignment_projector_inputs.tsv: position exact as in the TSV; CIGAR equal
+    to what the compiled reference produced for the row (the TSV column is only fuzzy-compared by the reference, F8)."""
+    for case in fixtures_json[table]:
+        idx = _pair_index(port, case["src"], case["dst"])
+        q = case["query"]
+        b = RecordBatch.from_records([dict(src_row=0, dst_row=1, src_pos=case["src_pos"], seq=q, cigar=case["cigar"]),
+                                      dict(src_row=0, dst_row=1, src_pos=case["src_pos"], seq=q, cigar=case["cigar"], qual=[41] * len(q))])
+        o1 = idx.project_batch(b, stage=1)
+        assert int(o1.dst_pos[0]) == case["tsv_expected_pos"] == case["ref_rewrite"]["pos"]
+        assert o1.cigar_str(0) == case["ref_rewrite"]["cigar"]
+        o0 = idx.project_batch(b, 0, -1)
+        assert o0.cigar_str(0) == case["ref_project_integer"]["cigar"]
+        assert o0.cigar_str(1) == case["ref_project_quality"]["cigar"]
+        assert o0.ranges(0).tolist() == case["ref_project_integer"]["ranges"]
+        assert o0.ranges(1).tolist() == case["ref_project_quality"]["ranges"]
+        o2 = idx.project_batch(b, -2, -1)
+        assert o2.cigar_str(0) == case["ref_project_affine_go-2"]["cigar"]
+        if table == "rewrite_cigar":
+            # the TSV's expected CIGAR equals the reference's up to the order inside indel/padding runs (cigar_eq<true>)
+            def norm(c):
+                return sorted((int(v) & 0xF, int(v) >> 4) for v in parse_cigar(c))
+            assert norm(o1.cigar_str(0)) == norm(case["tsv_expected_cigar"])
+
+
+def test_port_indel_run_checker_table(port, fixtures_json):
+    """tests/indel_run_checker_inputs.tsv: exact run boundaries, ranges and final positions."""
+    for case in fixtures_json["indel_run_checker"]:
+        ops = parse_cigar(case["cigar"])
+        runs, fin, n = port.indel_runs(ops, 0)
+        assert runs.tolist() == case["ref_runs"]
+        assert [int(fin[0]), int(fin[1])] == case["ref_final"] == [case["tsv_final_query_pos"], case["tsv_final_ref_pos"]]
+        exp = [e for e in case["tsv_expected"] if e["kind"] == "I"]
+        assert n == len(exp)
+        for r, e in zip(runs, exp):
+            assert format_cigar(ops[int(r[0]):int(r[1])]) == e["cigar"]
+            assert (int(r[4]), int(r[4] + r[5]), int(r[2]), int(r[2] + r[3])) == (e["q_begin"], e["q_end"], e["r_begin"], e["r_end"])
+
+
+def test_port_matches_golden_random():
+    from oracle import oracle_lib
+    port = oracle_lib.load("port")
+    for msa, b, go, ge, full, rew in load_golden_random():
+        idx = port.make_index(*casegen.index_inputs(msa))
+        assert_same(idx.project_batch(b, go, ge, stage=0), full, b, f"port vs golden full go={go} ge={ge}")
+        assert_same(idx.project_batch(b, go, ge, stage=1), rew, b, f"port vs golden rewrite go={go} ge={ge}")
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_port_vs_compiled_reference_random(port, ref, seed):
+    msa, b = casegen.random_batch(1000 + seed, 300, n_cols=[64, 300, 1500][seed % 3])
+    rows, refs = casegen.index_inputs(msa)
+    pi, ri = port.make_index(rows, refs), ref.make_index(rows, refs)
+    for go, ge in [(0, -1), (0, -3), (-2, -1), (3, -1)]:
+        po = pi.project_batch(b, go, ge)
+        keep = np.flatnonzero(po.flags == 0)     # the reference has UB / aborts on flagged inputs
+        recs = []
+        for i in keep:
+            s = b.slice(int(i), int(i) + 1)
+            recs.append(dict(src_row=int(s.src_row[0]), dst_row=int(s.dst_row[0]), dst_ref=int(s.dst_ref[0]), src_pos=int(s.src_pos[0]),
+                             seq=s.seq, cigar=s.cig, qual=(s.qual if s.qual.size else None)))
+        sub = RecordBatch.from_records(recs)
+        for stage in (1, 0):
+            assert_same(pi.project_batch(sub, go, ge, stage=stage), ri.project_batch(sub, go, ge, stage=stage), sub,
+                        f"port vs reference stage={stage} go={go} ge={ge}")
+
+
+def test_port_dp_modes_vs_compiled_reference(port, ref):
+    n_ub = 0
+    for r, q, qual in casegen.random_pairs(7, 1500, max_len=90):
+        for go, ge, use_q in [(0, -1, False), (0, -5, False), (-3, -1, False), (0, -1, True), (-2, -2, True), (4, -1, True)]:
+            pops, pscore, pn = port.align_global(r, q, qual if use_q else None, go, ge)
+            if pn == -2:
+                n_ub += 1      # reference UB: excluded from parity
+                assert go < 0
+                continue
+            rops, rscore, rn = ref.align_global(r, q, qual if use_q else None, go, ge)
+            assert pn == rn and np.array_equal(pops, rops), (format_cigar(pops), format_cigar(rops), go, ge, use_q)
+            assert pscore == rscore
+    assert n_ub < 100
+
+
+def test_port_rank_select_vs_reference(port, ref):
+    rng = np.random.default_rng(5)
+    for n_bits in (1, 63, 64, 65, 511, 512, 513, 5000):
+        bits = rng.random(n_bits) < rng.choice([0.02, 0.5, 0.95])
+        from panvc3_b200.batch import pack_bits
+        rows = [(pack_bits(bits), n_bits)]
+        pi, ri = port.make_index(rows, []), ref.make_index(rows, [])
+        zeros = int((~bits).sum())
+        for pos in list(range(0, n_bits + 1, max(1, n_bits // 97))) + [n_bits]:
+            assert pi.rank0(0, pos) == ri.rank0(0, pos)
+        for k in list(range(1, zeros + 1, max(1, zeros // 97))) + ([zeros] if zeros else []):
+            assert pi.select0(0, k) == ri.select0(0, k)
+        if zeros:
+            assert pi.select0(0, zeros + 1) == ri.select0(0, zeros + 1) == n_bits
+
+
+def test_port_flags_error_cases(port):
+    idx = _pair_index(port, "GAT-ACA", "GATTACA")
+    cases = [
+        (dict(src_row=0, dst_row=1, src_pos=2, seq="TA", cigar=np.array([(2 << 4) | 9], np.uint32)), 0x1),   # op 'B'
+        (dict(src_row=0, dst_row=1, src_pos=4, seq="TACA", cigar="4M"), 0x2),       # runs past the last source base
+        (dict(src_row=0, dst_row=1, src_pos=2, seq="T", cigar="2M"), 0x4),          # query too short
+        (dict(src_row=0, dst_row=1, src_pos=2, seq="", cigar="0M0P"), 0x20),
+    ]
+    for rec, flag in cases:
+        o = idx.project_batch(RecordBatch.from_records([rec]))
+        assert int(o.flags[0]) == flag, (rec, int(o.flags[0]))
