@@ -111,6 +111,10 @@ int         pv3_create(pv3_ctx **out, int device);          /* fails with PV3_ER
 void        pv3_destroy(pv3_ctx *);
 const char *pv3_last_error(const pv3_ctx *);                 /* ctx may be NULL: error of the last failed pv3_create */
 
+/* Runs all work of the context on the caller's CUDA stream (a cudaStream_t passed as void*; NULL restores the context's
+ * own stream), so that callers can bracket calls with their own events or order them after their own kernels. */
+int         pv3_set_stream(pv3_ctx *, void *cuda_stream);
+
 /* -- index (replaces msa_index::sequence_entry over sdsl::rrr_vector<15>, include/panvc3/msa_index.hh:47-74) --------- */
 int pv3_index_add_row(pv3_ctx *, const uint64_t *gap_words, uint64_t n_bits);  /* returns row id >= 0 */
 int pv3_index_add_ref(pv3_ctx *, const char *bases, uint64_t n);               /* returns contig id >= 0 */

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(HERE, "libpanvc3_b200.so")
 PV3_OK, PV3_ERR_INVALID, PV3_ERR_CUDA, PV3_ERR_CAPACITY, PV3_ERR_STATE = 0, -1, -2, -3, -4
 
 EXPORTED_SYMBOLS = [
-    "pv3_abi_version", "pv3_create", "pv3_destroy", "pv3_last_error", "pv3_index_add_row", "pv3_index_add_ref",
+    "pv3_abi_version", "pv3_create", "pv3_destroy", "pv3_last_error", "pv3_set_stream", "pv3_index_add_row", "pv3_index_add_ref",
     "pv3_index_commit", "pv3_set_params", "pv3_set_quality_lut", "pv3_get_quality_lut", "pv3_project",
     "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_get_timing",
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
@@ -69,6 +69,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_destroy.restype = None
     lib.pv3_last_error.argtypes = [C.c_void_p]
     lib.pv3_last_error.restype = C.c_char_p
+    lib.pv3_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     lib.pv3_index_add_row.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.pv3_index_add_ref.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64]
     lib.pv3_index_commit.argtypes = [C.c_void_p]
@@ -174,6 +175,9 @@ class Context:
 
     def set_params(self, gap_open: int = 0, gap_ext: int = -1):
         self._check(self.lib.pv3_set_params(self.h, gap_open, gap_ext))
+
+    def set_stream(self, cuda_stream: int | None):
+        self._check(self.lib.pv3_set_stream(self.h, cuda_stream))
 
     def set_stage(self, stage: int):
         self._check(self.lib.pv3_set_stage(self.h, stage))

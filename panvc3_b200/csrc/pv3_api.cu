@@ -45,7 +45,8 @@ struct HostRef { std::string bases; };
 struct pv3_ctx {
 	int          device = 0;
 	int          n_sms = 148;
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr;       // the stream all work is issued on
+	cudaStream_t own_stream = nullptr;
 	cudaEvent_t  ev[8] = {};
 	std::string  error;
 
@@ -125,7 +126,8 @@ int pv3_create(pv3_ctx **out, int device)
 	ctx->device = device;
 	ctx->n_sms = prop.multiProcessorCount;
 	default_quality_lut(ctx->lut);
-	if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaStreamCreate failed"); }
+	if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaStreamCreate failed"); }
+	ctx->stream = ctx->own_stream;
 	for (auto &ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaEventCreate failed"); }
 	if (cudaMallocHost((void **) &ctx->h_counters, sizeof(Counters)) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaMallocHost failed"); }
 	if (ctx->counters.ensure(sizeof(Counters)) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaMalloc failed"); }
@@ -145,8 +147,17 @@ void pv3_destroy(pv3_ctx *ctx)
 		b->release();
 	if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
 	for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
-	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
+}
+
+int pv3_set_stream(pv3_ctx *ctx, void *cuda_stream)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	ctx->stream = cuda_stream ? (cudaStream_t) cuda_stream : ctx->own_stream;
+	return PV3_OK;
 }
 
 const char *pv3_last_error(const pv3_ctx *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
