@@ -1,0 +1,379 @@
+#!/usr/bin/env python3
+"""bench.py — project_alignments hot path on B200 (contract: see the task statement / DESIGN.md §Measurement).
+
+  python bench.py --gpus N --steps K --warmup W            our CUDA path (one process per GPU under torchrun for N>1)
+  python bench.py --impl reference --steps K --warmup W    the reference's own CPU implementation on the host cores
+
+A step = one pass of the hot path (projection → CIGAR rewrite → indel-run realignment → splice) over one batch of
+synthetic records. Workload at every N: BASELINE.json configs[1] — the test-workflow MSA index (5 rows × 12 636 columns,
+tests/golden/test_workflow_msa.npz) and 1 M synthetic 150-bp reads PER GPU sampled from the founder rows (weak scaling;
+contiguous shards, no data-path collective).
+
+  value     alignments/s, whole job, inputs resident in HBM, K steps timed with CUDA events on the launch stream
+  e2e       the same through pv3_project with pinned HOST buffers: H2D + kernels + D2H inside the timed region
+  roofline  dominant kernel (k1_rewrite_kernel): algorithmic bytes / its mean CUDA-event duration vs the measured HBM peak
+  cpu_baseline  oracle/_ref (the reference compiled in place) or the C port, timed on the host cores (rank 0, N=1 only)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "alignments projected+realigned/sec"
+UNIT = "alignments/s"
+SEED = 20261104 + 2          # seed = 20261104 + config id
+READ_LEN = 150
+RECORDS_PER_GPU = 1_000_000
+
+
+def load_workload(n: int, rank: int = 0, workload: str = "config2"):
+    from panvc3_b200.workload import load_msa_npz, sample_reads, synth_msa
+    if workload == "indel":
+        # configs[3]-style stress (scaled): dense abutting insertion/deletion columns force realignment (DP-bound)
+        msa = synth_msa(400_000, 4, seed=SEED + 11, p_gap=0.01, mean_gap=6, snp=0.01, anticorrelated=0.01)
+        batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank + 1, ins=0.001, dele=0.001)
+        name = "configs[3]-style indel-heavy stress: synthetic 400k-column MSA with abutting I/D columns, 150-bp reads"
+    else:
+        msa = load_msa_npz(os.path.join(ROOT, "tests", "golden", "test_workflow_msa.npz"))
+        batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank)
+        name = "configs[1]: test-workflow index (5 rows x 12636 cols) + 1M synthetic 150bp reads per GPU, QUAL present, M-style CIGARs"
+    return msa, batch, name
+
+
+def algorithmic_bytes(msa, batch, out_cig_words: int, n_runs: int, dp_window_bytes: int) -> dict:
+    """Bytes the path must move per SURVEY.md §8(d) (B_rec summed over the batch).
+
+    strict: what the rewrite kernel's algorithm has to touch — query bases, the compared target bytes, the src+dst gap
+    bits over the spanned columns, two directory entries, CIGAR ops in and out, positions/ids/offsets, range outputs.
+    QUAL is only needed for realigned windows, so only those bytes are counted. `survey` adds the full QUAL string as
+    §8(d)'s formula does (≈590 B per 150-bp record)."""
+    n = batch.n
+    ops = batch.cig & 0xF
+    cnt = (batch.cig >> 4).astype(np.int64)
+    rec_of_op = np.repeat(np.arange(n), np.diff(batch.cig_off).astype(np.int64))
+    ref_cons = np.zeros(n, np.int64)
+    m = np.isin(ops, [0, 2, 3, 7, 8])
+    np.add.at(ref_cons, rec_of_op[m], cnt[m])
+    mlike = np.zeros(n, np.int64)
+    mm = np.isin(ops, [0, 7, 8])
+    np.add.at(mlike, rec_of_op[mm], cnt[mm])
+    # columns spanned in the source row: select0(pos + ref_cons) - select0(pos + 1) + 1
+    span = np.zeros(n, np.int64)
+    for r in range(msa.n_rows):
+        sel = np.flatnonzero(batch.src_row == r)
+        if not sel.size:
+            continue
+        zero_pos = np.flatnonzero(msa.rows[r] != ord("-"))
+        p0 = batch.src_pos[sel].astype(np.int64)
+        p1 = np.minimum(p0 + np.maximum(ref_cons[sel], 1) - 1, zero_pos.size - 1)
+        span[sel] = zero_pos[p1] - zero_pos[np.minimum(p0, zero_pos.size - 1)] + 1
+    gap_bytes = 2 * ((span + 7) // 8)
+    seq_bytes = int(batch.seq.size)
+    strict = (seq_bytes + int(mlike.sum()) + int(gap_bytes.sum()) + 32 * n + 4 * (int(batch.cig.size) + out_cig_words)
+              + 16 * n + 12 * n + 32 * n_runs + dp_window_bytes)
+    survey = strict + (int(batch.qual.size) if batch.qual_off is not None else 0) - dp_window_bytes
+    return {"strict": int(strict), "survey": int(survey)}
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: int):
+        self.rows: list[list[str]] = []
+        self.proc = None
+        self.gpu_index = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu_index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs() -> tuple[float, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_lib():
+    from oracle import oracle_lib
+    if oracle_lib.have("reference"):
+        return oracle_lib.load("reference"), "reference"
+    return oracle_lib.load("port"), "port"
+
+
+def time_cpu(lib_index, batch, n_threads: int, repeats: int = 1) -> float:
+    """Best-of-`repeats` wall seconds of one pass of the CPU implementation over `batch`."""
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        lib_index.project_batch(batch, 0, -1, n_threads=n_threads)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def cpu_baseline(msa, batch) -> dict:
+    """Reference CPU path on the box's host cores over a bounded sample of the same workload (rank 0, N=1)."""
+    import casegen
+    lib, kind = cpu_reference_lib()
+    idx = lib.make_index(*casegen.index_inputs(msa))
+    cores = os.cpu_count() or 1
+    one = batch.slice(0, min(batch.n, 40_000))
+    t1 = time_cpu(idx, one, 1)
+    rate1 = one.n / t1
+    # all cores: size the sample for a few seconds of work
+    n_all = int(min(batch.n, max(40_000, rate1 * cores * 3)))
+    sample = batch.slice(0, n_all)
+    tall = time_cpu(idx, sample, cores, repeats=2)
+    return {"value": n_all / tall, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"first {n_all} records of the step's batch, {cores} threads (one alignment_projector per thread, contiguous shards), best of 2",
+            "value_1thread": rate1, "sample_1thread": f"first {one.n} records, 1 thread (what the shipped single-threaded binary does, SURVEY F6)"}
+
+
+def run_reference_arm(args) -> None:
+    """--impl reference: the reference's own CPU code for the path (oracle/_ref when built, else the C port), all host
+    threads, each step a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import casegen
+    n = 400_000
+    msa, batch, name = load_workload(n, 0, args.workload)
+    lib, kind = cpu_reference_lib()
+    idx = lib.make_index(*casegen.index_inputs(msa))
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        idx.project_batch(batch, 0, -1, n_threads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        idx.project_batch(batch, 0, -1, n_threads=cores)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": name, "records_per_step": n, "note": "bounded sample of the 1M-record step; CPU only, no GPU"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": f"{n} records per step, {cores} threads, one projector per thread"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu_arm(args) -> None:
+    import torch
+    import torch.distributed as dist
+    from panvc3_b200 import build as pv3_build
+    from panvc3_b200.capi import PinnedArena, alloc_output
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.projector import MsaIndex
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the panvc3_b200 hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    pv3_build.build()
+
+    n = args.records
+    msa, batch, name = load_workload(n, rank, args.workload)
+    idx = MsaIndex.from_msa(msa, device=local_rank)
+    ctx = idx.ctx
+    ctx.set_params(0, -1)                      # project_alignments defaults -g 0 -e -1
+    stream = torch.cuda.Stream(device=dev)
+    ctx.set_stream(stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- value: inputs resident in HBM ----------------------------------------------------------------------------
+    dbatch = DeviceBatch(batch, dev)
+    dout = project_device(ctx, dbatch)          # sizes the output arenas (and is warm-up step 0)
+    for _ in range(args.warmup):
+        project_device(ctx, dbatch, dout)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches0 = ctx.total_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k1_ms, k3_ms, k4_ms = [], [], []
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(args.steps):
+            project_device(ctx, dbatch, dout)
+            t = ctx.timing()
+            k1_ms.append(t["ms_rewrite"]); k3_ms.append(t["ms_realign"]); k4_ms.append(t["ms_splice"])
+        e1.record(stream)
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    gpu_launches = ctx.total_launches() - launches0
+    stats = dict(dout.stats)
+
+    # ---- e2e: pinned host buffers through pv3_project, H2D and D2H inside the timed region -------------------------
+    lib = ctx.lib
+    pin_in = PinnedArena(lib, batch.input_bytes() + 16 * 4096)
+    from panvc3_b200.batch import RecordBatch
+    kw = {}
+    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual"):
+        a = getattr(batch, k)
+        if a is None:
+            continue
+        p = pin_in.take(a.shape, a.dtype); p[...] = a; kw[k] = p
+    pbatch = RecordBatch.__new__(RecordBatch)
+    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual"):
+        setattr(pbatch, k, kw.get(k))
+    cig_cap, rr_cap = stats["cig_used"] + 4096, stats["rr_used"] + 1024
+    pin_out = PinnedArena(lib, n * 36 + cig_cap * 4 + rr_cap * 32 + 16 * 4096)
+    pout = alloc_output(n, cig_cap, rr_cap, pin_out)
+    for _ in range(max(args.warmup, 1)):
+        pout = ctx.project(pbatch, pout)
+    barrier()
+    t0 = time.perf_counter()
+    h2d_ms, d2h_ms = [], []
+    for _ in range(args.steps):
+        pout = ctx.project(pbatch, pout)
+        t = ctx.timing(); h2d_ms.append(t["ms_h2d"]); d2h_ms.append(t["ms_d2h"])
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop()
+    d2h_bytes = n * 36 + pout.stats["cig_used"] * 4 + pout.stats["rr_used"] * 32
+
+    # ---- max over ranks ---------------------------------------------------------------------------------------------
+    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    dev_ms_max, e2e_ms_max = float(times[0]), float(times[1])
+
+    # ---- ordered gather over NVLink (N>1): results of one step to rank 0 in input order, timed separately -----------
+    gather_ms = None
+    if world > 1:
+        from panvc3_b200.gather import gather_ordered
+        local = dict(dst_pos=dout.dst_pos[:n], flags=dout.flags[:n], cig_off=dout.cig_off[:n], cig_len=dout.cig_len[:n],
+                     rr_off=dout.rr_off[:n], rr_len=dout.rr_len[:n], cig=dout.cig[:stats["cig_used"]], rr=dout.rr[:4 * stats["rr_used"]])
+        gather_ordered(local, device=dev)       # warm-up (NCCL channel setup)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        merged = gather_ordered(local, device=dev)
+        g1.record()
+        barrier()
+        gt = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(gt, op=dist.ReduceOp.MAX)
+        gather_ms = float(gt[0])
+        if rank == 0:
+            assert merged.n == n * world
+
+    if rank == 0:
+        total_records = n * world * args.steps
+        value = total_records / (dev_ms_max * 1e-3)
+        e2e_value = total_records / (e2e_ms_max * 1e-3)
+        k1 = statistics.mean(k1_ms)
+        dp_window_bytes = 0
+        ab = algorithmic_bytes(msa, batch, int(dout.cig_len[:n].sum().item()), stats["rr_used"], dp_window_bytes)
+        peak, peak_src = measured_peak_gbs()
+        achieved = ab["strict"] / (k1 * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": name, "records_per_gpu_per_step": n, "read_len": READ_LEN, "gap_open": 0, "gap_ext": -1,
+                       "l2_policy": f"inputs larger than L2: {batch.input_bytes() / 1e6:.0f} MB of input per step per GPU vs 126 MB L2",
+                       "parallelism": f"{world} independent contiguous shards, index replicated per GPU, no data-path collective",
+                       "realigned_runs_per_step": stats["rr_used"], "dp_cells_per_step": stats["dp_cells"],
+                       "flagged_records": stats["n_flagged"]},
+            "roofline": {"bound": "hbm", "kernel": "k1_rewrite_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": ab["strict"], "bytes_per_record": ab["strict"] / n,
+                         "bytes_per_record_survey_formula": ab["survey"] / n, "kernel_ms": k1,
+                         "frac_survey_formula": ab["survey"] / (k1 * 1e-3) / 1e9 / peak},
+            "kernels_ms": {"rewrite": k1, "realign": statistics.mean(k3_ms), "splice": statistics.mean(k4_ms)},
+            "realign_gcups": (stats["dp_cells"] / (statistics.mean(k3_ms) * 1e-3) / 1e9) if statistics.mean(k3_ms) > 0 else None,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.input_bytes(), "d2h_bytes_per_step": int(d2h_bytes),
+                    "ms_per_step": e2e_ms_max / args.steps, "h2d_ms": statistics.mean(h2d_ms), "d2h_ms": statistics.mean(d2h_ms),
+                    "timer": "host perf_counter around K pv3_project calls, synchronized both sides, max over ranks"},
+            "gpu_launches": int(gpu_launches),
+            "clocks": clocks,
+        }
+        if gather_ms is not None:
+            line["ordered_gather"] = {"ms": gather_ms, "backend": "nccl", "what": "one step's results of all ranks to rank 0 in input order"}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(msa, batch)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="config2", choices=["config2", "indel"])
+    ap.add_argument("--records", type=int, default=RECORDS_PER_GPU)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()
