@@ -60,9 +60,10 @@ struct pv3_ctx {
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
 	int          stage = 0;
+	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
 
 	// device work buffers
-	DevBuf       counters, jobs, dp_arena, pool;
+	DevBuf       counters, jobs, dp_arena, pool, deferred;
 	Counters    *h_counters = nullptr;   // pinned
 	// host-path device mirrors
 	DevBuf       in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig;
@@ -140,7 +141,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool,
+	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred,
 			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
 			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
@@ -211,7 +212,11 @@ int pv3_index_commit(pv3_ctx *ctx)
 		total = align_up(total + L.n_sel * 4, 256);
 	}
 	std::vector <size_t> ref_off(ctx->refs.size());
-	for (size_t r = 0; r < ctx->refs.size(); ++r) { ref_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 16, 256); }
+	std::vector <size_t> code_off(ctx->refs.size());
+	for (size_t r = 0; r < ctx->refs.size(); ++r) {
+		ref_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 512, 256);
+		code_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 512, 256);
+	}
 	if (!total) total = 256;
 
 	std::vector <uint8_t> host(total, 0);
@@ -235,7 +240,22 @@ int pv3_index_commit(pv3_ctx *ctx)
 		for (uint64_t b = L.n_blocks; b < L.n_blocks + 1 + 32; ++b) blk[b] = z;
 		for (uint64_t s = next_sel; s < L.n_sel; ++s) sel[s] = (uint32_t) (L.n_blocks - 1);   // sentinel(s)
 	}
-	for (size_t r = 0; r < ctx->refs.size(); ++r) memcpy(host.data() + ref_off[r], ctx->refs[r].bases.data(), ctx->refs[r].bases.size());
+	for (size_t r = 0; r < ctx->refs.size(); ++r) {
+		auto const &bases = ctx->refs[r].bases;
+		memcpy(host.data() + ref_off[r], bases.data(), bases.size());
+		uint8_t *codes = host.data() + code_off[r];
+		for (size_t i = 0; i < bases.size(); ++i) {
+			uint8_t c;
+			switch (bases[i]) {   // dna5::assign_char (dna5.hpp:99-110); exact = byte equals dna5::to_char(rank)
+				case 'A': c = 0; break; case 'C': c = 1; break; case 'G': c = 2; break; case 'N': c = 3; break; case 'T': c = 4; break;
+				case 'a': c = 0x80; break; case 'c': c = 0x81; break; case 'g': c = 0x82; break;
+				case 't': case 'U': case 'u': c = 0x84; break;
+				default: c = 0x83; break;
+			}
+			codes[i] = c;
+		}
+		memset(codes + bases.size(), 0xff, 512);
+	}
 
 	PV3_CUDA(ctx, ctx->index_mem.ensure(total));
 	PV3_CUDA(ctx, cudaMemcpy(ctx->index_mem.p, host.data(), total, cudaMemcpyHostToDevice));
@@ -255,6 +275,7 @@ int pv3_index_commit(pv3_ctx *ctx)
 	std::vector <RefDesc> fd(ctx->refs.size() ? ctx->refs.size() : 1);
 	for (size_t r = 0; r < ctx->refs.size(); ++r) {
 		fd[r].bases = (const char *) (ctx->index_mem.as <uint8_t>() + ref_off[r]);
+		fd[r].codes = ctx->index_mem.as <uint8_t>() + code_off[r];
 		fd[r].n = ctx->refs[r].bases.size();
 	}
 	PV3_CUDA(ctx, ctx->row_desc.ensure(rd.size() * sizeof(RowDesc)));
@@ -286,6 +307,13 @@ int pv3_get_quality_lut(const pv3_ctx *ctx, int32_t *lut84)
 {
 	if (!ctx || !lut84) return PV3_ERR_INVALID;
 	memcpy(lut84, ctx->lut, sizeof ctx->lut);
+	return PV3_OK;
+}
+
+int pv3_set_kernel_path(pv3_ctx *ctx, int path)
+{
+	if (!ctx || path < 0 || path > 1) return PV3_ERR_INVALID;
+	ctx->kernel_path = path;
 	return PV3_OK;
 }
 
@@ -337,15 +365,38 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	ctx->timing.launches = 0;
 	if (!in->n) return PV3_OK;
 	PV3_CUDA(ctx, ctx->jobs.ensure((out->rr_cap ? out->rr_cap : 1) * sizeof(Job)));
+	PV3_CUDA(ctx, ctx->deferred.ensure(in->n * 8));
 	K1Params P = make_k1(ctx, in, out);
+	P.deferred = ctx->deferred.as <uint64_t>();
 	PV3_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
 	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
-	launch_k1(P, ctx->n_sms, ctx->stream);
-	PV3_CUDA(ctx, cudaGetLastError());
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-	ctx->timing.launches += 1;
-	int st = fetch_counters(ctx);
-	if (st) return st;
+	int st = PV3_OK;
+	if (ctx->kernel_path == 0) {
+		// short records: one thread each; whatever exceeds its fixed quotas comes back in the deferred list
+		launch_k1_thread(P, ctx->n_sms, ctx->stream);
+		PV3_CUDA(ctx, cudaGetLastError());
+		ctx->timing.launches += 1;
+		st = fetch_counters(ctx);
+		if (st) return st;
+		if (ctx->h_counters->n_deferred && !ctx->h_counters->overflow) {
+			K1Params P2 = P;
+			P2.rec_list = ctx->deferred.as <uint64_t>();
+			P2.n_list = ctx->h_counters->n_deferred;
+			launch_k1(P2, ctx->n_sms, ctx->stream);
+			PV3_CUDA(ctx, cudaGetLastError());
+			ctx->timing.launches += 1;
+			PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+			st = fetch_counters(ctx);
+			if (st) return st;
+		} else PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+	} else {
+		launch_k1(P, ctx->n_sms, ctx->stream);
+		PV3_CUDA(ctx, cudaGetLastError());
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+		ctx->timing.launches += 1;
+		st = fetch_counters(ctx);
+		if (st) return st;
+	}
 	Counters c = *ctx->h_counters;
 	out->rr_used = c.job_cursor;
 	out->cig_used = c.arena_cursor + c.dp_path;   // upper bound of what the splice kernel may still append

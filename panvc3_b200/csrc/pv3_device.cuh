@@ -33,8 +33,10 @@ struct RowDesc {
 };
 
 struct RefDesc {
-	const char *bases;
-	uint64_t    n;
+	const char    *bases;   // raw FASTA bytes (rewrite compares raw bytes)
+	const uint8_t *codes;   // per base: dna5 rank of assign_char(byte) in bits 0-2 | 0x80 unless byte is exactly one of "ACGNT";
+	                        // (query rank == code) ⇔ (dna5::to_char(query) == byte). 512 readable pad bytes follow.
+	uint64_t       n;
 };
 
 // One realigned indel run (indel_run_checker.cc:104-118 + alignment_projector.cc:61-73).
@@ -61,6 +63,7 @@ struct Counters {
 	unsigned long long dp_max_pool;    // max per-job scratch bytes
 	unsigned long long dp_arena_cursor;
 	unsigned long long job_ticket;     // work-stealing counter of the DP kernel
+	unsigned long long n_deferred;     // records the thread-per-record kernel handed to the warp-per-record kernel
 	unsigned int       overflow;       // bit0: CIGAR arena, bit1: rr/jobs, bit2: DP op arena
 	unsigned int       pad;
 };

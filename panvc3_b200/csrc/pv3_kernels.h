@@ -33,6 +33,9 @@ struct K1Params {
 	Counters       *counters;
 	int32_t         gap_open, gap_ext;
 	int             stage;       // 0 = full pipeline, 1 = rewrite only (parity probe of rewrite_cigar())
+	const uint64_t *rec_list;    // warp kernel: process records rec_list[0..n_list) instead of 0..n (null ⇒ all)
+	uint64_t        n_list;
+	uint64_t       *deferred;    // thread kernel: records it could not handle (capacity n)
 };
 
 // Scratch bytes one DP job needs: byte trace (Q+1)x(R+1), strip boundary arrays (H, up: int32; tup: byte), staged
@@ -60,7 +63,8 @@ struct K4Params {
 	const uint64_t *realigned_recs; // unused (records are found through jobs)
 };
 
-void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);
+void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
+void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream);   // thread per record (short records)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);
 void launch_positions(const RowDesc *rows, uint32_t n_rows, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row,

@@ -19,6 +19,7 @@
 // segments exactly where the reference pushes them.  No per-base rank/select is ever issued.
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
+#include "pv3_runs.cuh"
 
 namespace pv3 {
 
@@ -227,59 +228,6 @@ __device__ RecordResult rewrite_record(const K1Params &P, uint64_t rec, uint32_t
 
 namespace pv3 {
 
-// indel_run_checker::find_next_range_for_realigning over the rewritten ops (I S H P D = X only).
-// Warp-uniform scalar scan (ops are read by all lanes from the same address). WRITE = false counts runs;
-// WRITE = true stores the Job and the reported ranges of each run, lane 0 only.
-template <bool WRITE>
-__device__ uint32_t scan_runs(const uint32_t *ops, uint32_t n_ops, uint64_t dst_pos, uint64_t rec, uint64_t nq, uint64_t ref_n,
-	Job *jobs, uint64_t *rr, uint32_t &flags, unsigned long long &cells, unsigned long long &path,
-	unsigned long long &pool, unsigned long long &max_pool, bool affine)
-{
-	uint64_t ref = dst_pos, qry = 0, run_ref = dst_pos, run_qry = 0;
-	uint32_t run_k = 0, type = 0, n_runs = 0;
-	for (uint32_t k = 0; k <= n_ops; ++k) {
-		uint64_t const ref0 = ref, qry0 = qry;
-		uint32_t const type0 = type;
-		if (k < n_ops) {
-			uint32_t const v = ops[k], n = v >> 4, op = v & 0xfu;
-			if (!type) { run_ref = ref; run_qry = qry; run_k = k; }       // indel_run_checker.cc:44-49
-			if (op == OP_I) { qry += n; type |= 1u; continue; }            // :60-63
-			if (op == OP_D) { ref += n; type |= 2u; continue; }            // :65-68
-			if (op == OP_S) qry += n;                                      // :70-75
-			else if (op == OP_EQ || op == OP_X || op == OP_M) { ref += n; qry += n; }  // :84-92
-			else if (op == OP_N) ref += n;                                 // :77-82 (never produced by the rewrite)
-			type = 0;                                                      // H, P: :54-58
-		}
-		if (type0 == 3u) {                                                 // report_run :104-108 / final run :111-118
-			uint64_t const rlen = ref0 - run_ref, qlen = qry0 - run_qry;
-			if (run_ref + rlen > ref_n) flags |= PV3_FLAG_REF_OOB;
-			if (run_qry + qlen > nq) flags |= PV3_FLAG_QUERY_OOB;
-			if (rlen > 0x7fffffffull || qlen > 0x7fffffffull) flags |= PV3_FLAG_REF_OOB;
-			if (WRITE) {
-				if (lane_id() == 0) {
-					Job j;
-					j.rec = rec; j.ref_loc = run_ref; j.ref_len = (uint32_t) rlen; j.qry_loc = (uint32_t) run_qry;
-					j.qry_len = (uint32_t) qlen; j.op_begin = run_k; j.op_end = k; j.out_len = 0; j.out_off = 0;
-					jobs[n_runs] = j;
-					// alignment_projector.cc:69-73 — location is the live m_ref_pos, already advanced over the
-					// run-terminating op; the length is the true window length.
-					rr[4 * n_runs + 0] = ref; rr[4 * n_runs + 1] = rlen; rr[4 * n_runs + 2] = run_qry; rr[4 * n_runs + 3] = qlen;
-				}
-			} else {
-				cells += rlen * qlen;
-				path += rlen + qlen;
-				unsigned long long const need = dp_pool_bytes((uint32_t) rlen, (uint32_t) qlen, affine);
-				pool += need;
-				if (need > max_pool) max_pool = need;
-			}
-			++n_runs;
-			type = (k < n_ops) ? type : 0;
-		}
-		if (k == n_ops) break;
-	}
-	return n_runs;
-}
-
 // Records are handled in groups of GROUP consecutive records per warp: the rewritten CIGARs of a group are staged in
 // shared memory and leave with one arena allocation (one atomic per group) and one coalesced copy.
 constexpr int GROUP       = 8;
@@ -342,7 +290,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 			if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);
 			bool const affine = has_qual || P.gap_open != 0;
 			unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
-			n_runs = scan_runs<false>(ops, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine);
+			n_runs = scan_runs<false>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine, false);
 			if (!res.flags && n_runs) {
 				if (lane == 0) {
 					job_base = atomicAdd(&P.counters->job_cursor, (unsigned long long) n_runs);
@@ -357,7 +305,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 					if (lane == 0) atomicOr(&P.counters->overflow, 2u);
 				} else {
 					uint32_t f = 0; unsigned long long a = 0, b = 0, c = 0, d = 0;
-					scan_runs<true>(ops, res.n_ops, res.dst_pos, rec, nq, ref_n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine);
+					scan_runs<true>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, lane == 0);
 				}
 			} else n_runs = 0;
 		}
@@ -379,7 +327,8 @@ k1_rewrite_kernel(K1Params P)
 	unsigned const lane = lane_id();
 	unsigned const warp_in_block = threadIdx.x >> 5;
 	uint32_t *stage = stage_all[warp_in_block];
-	uint64_t const n_groups = (P.n + GROUP - 1) / GROUP;
+	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
+	uint64_t const n_groups = (n_items + GROUP - 1) / GROUP;
 	uint64_t const warp_global = (uint64_t) blockIdx.x * K1_WARPS + warp_in_block;
 	uint64_t const n_warps = (uint64_t) gridDim.x * K1_WARPS;
 
@@ -387,9 +336,9 @@ k1_rewrite_kernel(K1Params P)
 
 	for (uint64_t grp = warp_global; grp < n_groups; grp += n_warps) {
 		uint64_t const rec0 = grp * GROUP;
-		int const n_in_group = (int) ((P.n - rec0 < (uint64_t) GROUP) ? (P.n - rec0) : GROUP);
+		int const n_in_group = (int) ((n_items - rec0 < (uint64_t) GROUP) ? (n_items - rec0) : GROUP);
 		for (int r = 0; r < n_in_group; ++r) {
-			uint64_t const rec = rec0 + r;
+			uint64_t const rec = P.rec_list ? P.rec_list[rec0 + r] : rec0 + r;
 			RecordResult res = rewrite_record(P, rec, stage + g.stage_n, STAGE_OPS - g.stage_n);
 			if (res.overflow && g.stage_n) {
 				// does not fit behind the records already staged: send those off and redo this one on an empty stage
@@ -426,7 +375,8 @@ k1_rewrite_kernel(K1Params P)
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)
 {
-	uint64_t const n_groups = (P.n + GROUP - 1) / GROUP;
+	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
+	uint64_t const n_groups = (n_items + GROUP - 1) / GROUP;
 	uint64_t blocks = (n_groups + K1_WARPS - 1) / K1_WARPS;
 	uint64_t const max_blocks = (uint64_t) n_sms * 8;   // 8 resident CTAs of 256 threads per SM
 	if (blocks > max_blocks) blocks = max_blocks;

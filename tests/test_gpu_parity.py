@@ -96,9 +96,12 @@ def test_reference_tables_through_projector_api(gpu, fixtures_json):
 def test_golden_random_vectors_of_compiled_reference(gpu):
     for msa, b, go, ge, full, rew in load_golden_random():
         idx = device_index(msa)
-        assert_same(idx.project_batch(b, go, ge), full, b, f"gpu vs golden(reference) full go={go} ge={ge}")
-        idx.ctx.set_stage(1)
-        assert_same(idx.project_batch(b, go, ge), rew, b, f"gpu vs golden(reference) rewrite go={go} ge={ge}")
+        for path in (0, 1):
+            idx.ctx.set_kernel_path(path)
+            idx.ctx.set_stage(0)
+            assert_same(idx.project_batch(b, go, ge), full, b, f"gpu vs golden(reference) full go={go} ge={ge} path={path}")
+            idx.ctx.set_stage(1)
+            assert_same(idx.project_batch(b, go, ge), rew, b, f"gpu vs golden(reference) rewrite go={go} ge={ge} path={path}")
 
 
 # ---------------------------------------------------------------------------------------------- differential vs oracle
@@ -110,10 +113,13 @@ def test_random_batches_match_oracle(gpu, port, seed):
     oi = port.make_index(*casegen.index_inputs(msa))
     for go, ge in [(0, -1), (0, -3), (-2, -1), (-5, -2), (3, -1)]:
         for stage in (1, 0):
-            idx.ctx.set_stage(stage)
-            got = idx.project_batch(b, go, ge)
-            assert_same(got, oi.project_batch(b, go, ge, stage=stage), b, f"seed={seed} stage={stage} go={go} ge={ge}")
-            assert got.stats["n_flagged"] == int((got.flags != 0).sum())
+            exp = oi.project_batch(b, go, ge, stage=stage)
+            for path in (0, 1):
+                idx.ctx.set_stage(stage)
+                idx.ctx.set_kernel_path(path)
+                got = idx.project_batch(b, go, ge)
+                assert_same(got, exp, b, f"seed={seed} stage={stage} go={go} ge={ge} path={path}")
+                assert got.stats["n_flagged"] == int((got.flags != 0).sum())
 
 
 def test_random_batches_match_compiled_reference(gpu, port, ref):
@@ -166,9 +172,11 @@ def test_dp_modes_large_windows(gpu, port):
     oi = port.make_index(gap_rows, refs)
     b = RecordBatch.from_records(recs)
     for go, ge in [(0, -1), (-3, -1), (2, -2)]:
-        got = idx.project_batch(b, go, ge)
         exp = oi.project_batch(b, go, ge)
-        assert_same(got, exp, b, f"large windows go={go} ge={ge}")
+        for path in (0, 1):
+            idx.ctx.set_kernel_path(path)
+            got = idx.project_batch(b, go, ge)
+            assert_same(got, exp, b, f"large windows go={go} ge={ge} path={path}")
         assert int(exp.rr_len.sum()) >= len(recs) - 2
 
 
@@ -179,10 +187,11 @@ def test_long_reads_overflow_the_stage(gpu, port):
     b = sample_reads(msa, 300, 10000, seed=6, sub=0.03, ins=0.0, dele=0.0, clip_frac=0.3, cigar_style="EQX")
     idx = device_index(msa)
     oi = port.make_index(*casegen.index_inputs(msa))
-    got = idx.project_batch(b, 0, -1)
     exp = oi.project_batch(b, 0, -1)
     assert int(exp.cig_len.max()) > 300
-    assert_same(got, exp, b, "long reads")
+    for path in (0, 1):
+        idx.ctx.set_kernel_path(path)
+        assert_same(idx.project_batch(b, 0, -1), exp, b, f"long reads path={path}")
 
 
 def test_error_flags(gpu, port):
@@ -197,6 +206,9 @@ def test_error_flags(gpu, port):
             dict(src_row=0, dst_row=1, src_pos=2, seq="TA", cigar="2M"),
             dict(src_row=0, dst_row=7, src_pos=2, seq="TA", cigar="2M")]
     b = RecordBatch.from_records(recs)
+    idx.ctx.set_kernel_path(1)
+    assert idx.project_batch(b).flags.tolist() == [0x1, 0x2, 0x4, 0x20, 0, 0x80]
+    idx.ctx.set_kernel_path(0)
     got = idx.project_batch(b)
     assert got.flags.tolist() == [0x1, 0x2, 0x4, 0x20, 0, 0x80]
     exp = oi.project_batch(RecordBatch.from_records(recs[:5]))
@@ -258,3 +270,26 @@ def test_full_size_config2_properties(gpu, port, workflow_msa):
     a0 = idx.project_batch(b.slice(0, n // 2)); a1 = idx.project_batch(b.slice(n // 2, n))
     assert np.array_equal(np.concatenate([a0.dst_pos, a1.dst_pos]), out.dst_pos)
     assert np.array_equal(np.concatenate([a0.cig_len, a1.cig_len]), out.cig_len)
+
+
+def test_realistic_reads_both_paths_and_mixed_lengths(gpu, port, workflow_msa):
+    """150-bp reads with read indels / clips (the bench distribution) plus a few 2-kb reads in the same batch: the
+    thread-per-record kernel must defer exactly what it cannot hold and the merged result must equal the oracle."""
+    from panvc3_b200.workload import sample_reads
+    short = sample_reads(workflow_msa, 20000, 150, seed=99, ins=0.003, dele=0.003, clip_frac=0.1)
+    long_ = sample_reads(workflow_msa, 40, 2000, seed=98, cigar_style="EQX", sub=0.02)
+    eqx = sample_reads(workflow_msa, 3000, 150, seed=97, cigar_style="EQX", sub=0.05, with_qual=False)
+    recs = []
+    for bb in (short.slice(0, 7000), long_, short.slice(7000, 20000), eqx):
+        for i in range(bb.n):
+            s = bb.slice(i, i + 1)
+            recs.append(dict(src_row=int(s.src_row[0]), dst_row=int(s.dst_row[0]), dst_ref=int(s.dst_ref[0]), src_pos=int(s.src_pos[0]),
+                             seq=s.seq, cigar=s.cig, qual=(s.qual if s.qual is not None and s.qual.size else None)))
+    b = RecordBatch.from_records(recs)
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    for go, ge in [(0, -1), (-2, -1)]:
+        exp = oi.project_batch(b, go, ge, n_threads=os.cpu_count() or 1)
+        for path in (0, 1):
+            idx.ctx.set_kernel_path(path)
+            assert_same(idx.project_batch(b, go, ge), exp, b, f"mixed go={go} path={path}")
