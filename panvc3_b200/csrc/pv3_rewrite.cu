@@ -321,22 +321,22 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 }
 
 __global__ void __launch_bounds__(K1_WARPS * 32)
-k1_rewrite_kernel(K1Params P)
+k1_rewrite_kernel(K1Params P, int group)
 {
 	__shared__ uint32_t stage_all[K1_WARPS][STAGE_OPS];
 	unsigned const lane = lane_id();
 	unsigned const warp_in_block = threadIdx.x >> 5;
 	uint32_t *stage = stage_all[warp_in_block];
 	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
-	uint64_t const n_groups = (n_items + GROUP - 1) / GROUP;
+	uint64_t const n_groups = (n_items + group - 1) / group;
 	uint64_t const warp_global = (uint64_t) blockIdx.x * K1_WARPS + warp_in_block;
 	uint64_t const n_warps = (uint64_t) gridDim.x * K1_WARPS;
 
 	GroupState g; g.stage_n = 0; g.my_off = 0; g.my_len = 0; g.my_rec = ~0ull;
 
 	for (uint64_t grp = warp_global; grp < n_groups; grp += n_warps) {
-		uint64_t const rec0 = grp * GROUP;
-		int const n_in_group = (int) ((n_items - rec0 < (uint64_t) GROUP) ? (n_items - rec0) : GROUP);
+		uint64_t const rec0 = grp * group;
+		int const n_in_group = (int) ((n_items - rec0 < (uint64_t) group) ? (n_items - rec0) : group);
 		for (int r = 0; r < n_in_group; ++r) {
 			uint64_t const rec = P.rec_list ? P.rec_list[rec0 + r] : rec0 + r;
 			RecordResult res = rewrite_record(P, rec, stage + g.stage_n, STAGE_OPS - g.stage_n);
@@ -376,12 +376,14 @@ k1_rewrite_kernel(K1Params P)
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)
 {
 	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
-	uint64_t const n_groups = (n_items + GROUP - 1) / GROUP;
+	// few records (the deferred list of the thread kernel): one record per warp so that they spread over the SMs
+	int const group = (n_items < (uint64_t) n_sms * 8 * K1_WARPS * GROUP) ? 1 : GROUP;
+	uint64_t const n_groups = (n_items + group - 1) / group;
 	uint64_t blocks = (n_groups + K1_WARPS - 1) / K1_WARPS;
 	uint64_t const max_blocks = (uint64_t) n_sms * 8;   // 8 resident CTAs of 256 threads per SM
 	if (blocks > max_blocks) blocks = max_blocks;
 	if (blocks == 0) return;
-	k1_rewrite_kernel<<<(unsigned) blocks, K1_WARPS * 32, 0, stream>>>(P);
+	k1_rewrite_kernel<<<(unsigned) blocks, K1_WARPS * 32, 0, stream>>>(P, group);
 }
 
 } // namespace pv3

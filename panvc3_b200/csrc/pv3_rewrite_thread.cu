@@ -14,7 +14,7 @@
 // Tile pipeline (128 threads = 128 consecutive records):
 //   A  each thread: ids, src_pos, select0/rank0 of its record → c0, e0
 //   B  cooperative, coalesced staging into shared memory: the tile's query bytes (contiguous in the batch), and per record
-//      a 192-byte window of target codes at e0 and 6 words (384 columns) of both gap rows at c0
+//      a 208-byte window of target codes at e0 (gap words are read through L1: a record touches 3-4 words per row)
 //   C  each thread rewrites its record out of shared memory into a 24-op staging column; detects indel runs
 //   D  block scan of op counts → one atomic on the arena cursor → ops and per-record results written (coalesced
 //      per-record arrays)
@@ -28,21 +28,24 @@ namespace pv3 {
 
 constexpr int      TT        = 128;            // threads per CTA = records per tile
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
-constexpr uint32_t T_QSTAGE  = TT * 176;       // bytes of query staged per tile
-constexpr uint32_t T_RWIN    = 192;            // bytes of target codes staged per record
-constexpr uint32_t T_GW      = 6;              // gap words staged per row per record
+constexpr uint32_t T_QSTAGE  = TT * 168;       // bytes of query staged per tile
+constexpr uint32_t T_RWIN    = 208;            // bytes of target codes staged per record (13 x 16)
+constexpr uint32_t T_MMW     = 6;              // mismatch bit words per record (query coordinates): reads up to 192 bases
 
+// 64.6 KB ⇒ 3 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
 struct TileSmem {
-	uint32_t out[T_OUTQ][TT];                  // [op index][record]: conflict-free when all lanes write the same op index
+	uint32_t prov[T_OUTQ][TT];                 // provisional ops: '=' means "compare run", decided in C2/C3
+	uint32_t mm[T_MMW][TT];
 	uint4    q[T_QSTAGE / 16 + 2];
-	uint4    ref[TT][T_RWIN / 16];
-	uint64_t gaps[TT][2 * T_GW];               // [record][src words | dst words]
+	union {
+		uint4    ref[TT][T_RWIN / 16];         // [record][staged target codes]
+		uint32_t fin[T_OUTQ][TT];              // final ops
+	};
 	const uint8_t  *ref_ptr[TT];               // staging sources published by phase A
-	const uint64_t *src_ptr[TT];
-	const uint64_t *dst_ptr[TT];
 	uint32_t scan[TT / 32];
 	unsigned long long base;
 };
+static_assert(sizeof(uint4) * (T_RWIN / 16) * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in ref");
 
 struct TEmitter {
 	uint32_t *out;        // &smem.out[0][tid]
@@ -70,48 +73,24 @@ struct TEmitter {
 
 __device__ __forceinline__ uint32_t ctz64(uint64_t x) { return (uint32_t) __ffsll((long long) x) - 1u; }   // x != 0
 
-// Mismatch bits of m (<= 64) bytes: bit i set ⇔ q[qa + i] != r[ra + i]. Both byte strings live in shared memory and may be
-// read up to 7 bytes past the run (staging guarantees the slack).
-__device__ __forceinline__ uint64_t mismatch_mask(const uint32_t *qs, uint32_t qa, const uint32_t *rs, uint32_t ra, uint32_t m)
+// 4 bytes at byte offset a of a word array in shared memory (may read the following word)
+__device__ __forceinline__ uint32_t load4(const uint32_t *base, uint32_t a)
 {
-	uint32_t const qsh = (qa & 3u) * 8u, rsh = (ra & 3u) * 8u;
-	const uint32_t *qp = qs + (qa >> 2), *rp = rs + (ra >> 2);
-	uint32_t qlo = *qp++, rlo = *rp++;
-	uint32_t lo = 0, hi = 0;
-	for (uint32_t i = 0; i < m; i += 4) {
-		uint32_t const qhi = *qp++, rhi = *rp++;
-		uint32_t const t = __funnelshift_r(qlo, qhi, qsh) ^ __funnelshift_r(rlo, rhi, rsh);
-		qlo = qhi; rlo = rhi;
-		uint32_t const nz = (((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;   // bit 7 of each non-zero byte
-		uint32_t const bits = (nz * 0x00204081u) >> 28;                              // gathered into 4 bits
-		if (i < 32) lo |= bits << i; else hi |= bits << (i - 32);
-	}
-	uint64_t mask = ((uint64_t) hi << 32) | lo;
-	if (m < 64) mask &= (1ull << m) - 1ull;
-	return mask;
+	const uint32_t *p = base + (a >> 2);
+	return __funnelshift_r(p[0], p[1], (a & 3u) * 8u);
 }
 
-// Slow path of the same: target codes from global memory, byte by byte (windows that leave the staged 192 bytes).
-__device__ uint64_t mismatch_mask_global(const uint8_t *qbytes, const uint8_t *codes, uint32_t m)
+__device__ __forceinline__ uint32_t load4_global(const uint8_t *p)   // codes have 512 readable pad bytes
 {
-	uint64_t mask = 0;
-	for (uint32_t i = 0; i < m; ++i) if (qbytes[i] != __ldg(codes + i)) mask |= 1ull << i;
-	return mask;
+	return (uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) | ((uint32_t) __ldg(p + 3) << 24);
 }
 
-__device__ __forceinline__ void push_compare(TEmitter &em, uint64_t mm, uint32_t len)
+// bit i set ⇔ byte i of t is non-zero (SWAR; no per-byte branches)
+__device__ __forceinline__ uint32_t nonzero_bytes(uint32_t t)
 {
-	if (!mm) { em.push(OP_EQ, len); return; }
-	uint32_t pos = 0;
-	while (pos < len) {
-		uint64_t const rest = mm >> pos;
-		uint32_t l;
-		if (rest & 1ull) { uint64_t const inv = ~rest; l = inv ? ctz64(inv) : 64u; if (l > len - pos) l = len - pos; em.push(OP_X, l); }
-		else { l = rest ? ctz64(rest) : 64u; if (l > len - pos) l = len - pos; em.push(OP_EQ, l); }
-		pos += l;
-	}
+	uint32_t const nz = (((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;
+	return (nz * 0x00204081u) >> 28;
 }
-
 
 __global__ void __launch_bounds__(TT)
 k1_thread_kernel(K1Params P)
@@ -139,7 +118,7 @@ k1_thread_kernel(K1Params P)
 		bool defer = !tile_staged;
 		RowDesc S = {}, D = {};
 		RefDesc R = {};
-		uint64_t c0 = 0, e0 = 0, spos = 0, qoff = 0, nq = 0, cbase = 0, w0e = 0;
+		uint64_t c0 = 0, e0 = 0, spos = 0, qoff = 0, nq = 0, cbase = 0;
 		uint32_t nc = 0;
 		sm.ref_ptr[tid] = nullptr;
 		if (active) {
@@ -158,12 +137,9 @@ k1_thread_kernel(K1Params P)
 				spos = __ldg(P.src_pos + rec);
 				c0 = (spos < S.n_zeros) ? select0_thread(S, spos + 1) : S.n_bits;     // rewrite_cigar.hh:51
 				e0 = rank0_thread(D, c0);                                              // :52
-				if (S.n_bits != D.n_bits || e0 > R.n) defer = true;                    // unusual index: the general kernel guards it
+				if (S.n_bits != D.n_bits || e0 > R.n || nq > 32u * T_MMW) defer = true;                    // unusual index: the general kernel guards it
 				if (!defer) {
-					w0e = (c0 >> 6) & ~1ull;
 					sm.ref_ptr[tid] = R.codes + (e0 & ~15ull);
-					sm.src_ptr[tid] = S.words + w0e;
-					sm.dst_ptr[tid] = D.words + w0e;
 				}
 			}
 		}
@@ -175,25 +151,21 @@ k1_thread_kernel(K1Params P)
 			const uint4 *g = reinterpret_cast <const uint4 *>((uintptr_t) q_addr16);
 			for (uint32_t i = tid; i < n16; i += TT) sm.q[i] = __ldg(g + i);
 		}
-		for (uint32_t r = warp * 32; r < warp * 32 + 32; ++r) {
+		for (uint32_t r = warp * 32 + (lane >> 4); r < warp * 32 + 32; r += 2) {       // half-warp per record
 			const uint8_t *rp = sm.ref_ptr[r];
-			if (!rp) continue;                                   // uniform across the warp
-			if (lane < 12) sm.ref[r][lane] = __ldg(reinterpret_cast <const uint4 *>(rp) + lane);
-			else if (lane < 15) reinterpret_cast <uint4 *>(sm.gaps[r])[lane - 12] = __ldg(reinterpret_cast <const uint4 *>(sm.src_ptr[r]) + (lane - 12));
-			else if (lane < 18) reinterpret_cast <uint4 *>(sm.gaps[r])[3 + lane - 15] = __ldg(reinterpret_cast <const uint4 *>(sm.dst_ptr[r]) + (lane - 15));
+			uint32_t const l16 = lane & 15u;
+			if (rp && l16 < T_RWIN / 16) sm.ref[r][l16] = __ldg(reinterpret_cast <const uint4 *>(rp) + l16);
 		}
 		__syncthreads();
 
-		// ---- phase C: rewrite out of shared memory ------------------------------------------------------------------
-		uint32_t n_ops = 0, n_runs = 0;
+		// ---- phase C1: gap words → provisional ops (compare runs become '=' of unknown content) --------------------
+		uint32_t n_prov = 0, n_ops = 0, n_runs = 0;
 		unsigned long long job_base = 0;
-		if (active && !flags && !defer) {
-			TEmitter em; em.init(&sm.out[0][tid]);
-			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q);
-			uint32_t const qrel = q_lead + (uint32_t) (qoff - tq0);
-			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
-			uint64_t const e0a = e0 & ~15ull;
-			const uint64_t *gs = sm.gaps[tid];
+		bool adjacent_id = false;
+		uint64_t const e0a = e0 & ~15ull;
+		bool const work = active && !flags && !defer;
+		if (work) {
+			TEmitter em; em.init(&sm.prov[0][tid]);
 			uint64_t col = c0, e = e0, qpos = 0;
 			uint64_t src_left = (spos < S.n_zeros) ? (S.n_zeros - spos) : 0;
 
@@ -209,10 +181,7 @@ k1_thread_kernel(K1Params P)
 				uint32_t rem = cnt;
 				while (rem && !flags) {
 					uint64_t const wi = col >> 6;
-					uint64_t const gi = wi - w0e;
-					uint64_t Sw, Dw;
-					if (gi < (uint64_t) T_GW) { Sw = gs[gi]; Dw = gs[T_GW + gi]; }
-					else { Sw = __ldg(S.words + wi); Dw = __ldg(D.words + wi); }
+					uint64_t const Sw = __ldg(S.words + wi), Dw = __ldg(D.words + wi);
 					uint64_t valid = ~0ull << (col & 63);
 					uint64_t const z = ~Sw & valid;
 					uint32_t const zc = __popcll(z);
@@ -238,11 +207,7 @@ k1_thread_kernel(K1Params P)
 							if (sb && db) {
 								if (qpos + len > nq) { flags |= PV3_FLAG_QUERY_OOB; break; }      // :102
 								if (e + len > R.n) { flags |= PV3_FLAG_REF_OOB; break; }          // :103
-								uint64_t const ra = e - e0a;
-								uint64_t const mm = (ra + len + 8 <= (uint64_t) T_RWIN)
-									? mismatch_mask(qs, qrel + (uint32_t) qpos, rs, (uint32_t) ra, len)
-									: mismatch_mask_global(reinterpret_cast <const uint8_t *>(sm.q) + qrel + qpos, R.codes + e, len);
-								push_compare(em, mm, len);
+								em.push(OP_EQ, len);
 								qpos += len; e += len;
 							} else if (sb) { em.push(OP_I, len); qpos += len; }
 							else { em.push(OP_D, len); e += len; }
@@ -253,16 +218,88 @@ k1_thread_kernel(K1Params P)
 				}
 			}
 			em.flush();
+			n_prov = em.n_out;
+			adjacent_id = em.adjacent_id;
+			if (em.overflow) defer = true;
+		}
+
+		// ---- phase C2: one flat loop over the provisional ops, 4 bases per step: mismatch bits in query coordinates -----
+		bool const work2 = work && !flags && !defer;
+		if (work2) {
+			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q);
+			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
+			uint32_t const qrel = q_lead + (uint32_t) (qoff - tq0);
+			#pragma unroll
+			for (uint32_t w = 0; w < T_MMW; ++w) sm.mm[w][tid] = 0;
+			uint32_t j = 0, remaining = 0, qpos = 0, ra = (uint32_t) (e0 - e0a), acc = 0, wcur = 0;
+			while (j < n_prov || remaining) {
+				if (!remaining) {
+					uint32_t const v = sm.prov[j][tid]; ++j;
+					uint32_t const op = v & 0xfu, len = v >> 4;
+					if (op == OP_EQ) remaining = len;
+					else if (op == OP_I || op == OP_S) {
+						qpos += len;
+						if (qpos > 32u * T_MMW) qpos = 32u * T_MMW;           // I/S beyond |SEQ| (no compare can follow)
+						uint32_t const wn = qpos >> 5;
+						if (wn != wcur) { if (wcur < T_MMW) sm.mm[wcur][tid] = acc; acc = 0; wcur = wn; }
+					} else if (op == OP_D) ra += len;
+				} else {
+					uint32_t const n = remaining < 4u ? remaining : 4u;
+					uint32_t const rv = (ra + 8u <= T_RWIN) ? load4(rs, ra) : load4_global(R.codes + e0a + ra);   // beyond the staged window: L1
+					uint32_t bits = nonzero_bytes(load4(qs, qrel + qpos) ^ rv) & ((1u << n) - 1u);
+					uint32_t const bit = qpos & 31u;
+					acc |= bits << bit;
+					qpos += n; ra += n; remaining -= n;
+					if (bit + n >= 32u) {
+						sm.mm[wcur][tid] = acc;
+						acc = (bit + n > 32u) ? (bits >> (32u - bit)) : 0u;
+						++wcur;
+					}
+				}
+			}
+			if (wcur < T_MMW) sm.mm[wcur][tid] = acc;
+		}
+
+		__syncthreads();        // the staged target windows are dead from here on: fin overwrites them
+
+		// ---- phase C3: final ops: provisional '=' runs are split where the mismatch bits say so ---------------------------
+		if (work2) {
+			TEmitter em; em.init(&sm.fin[0][tid]);
+			uint32_t qpos = 0;
+			for (uint32_t j = 0; j < n_prov; ++j) {
+				uint32_t const v = sm.prov[j][tid];
+				uint32_t const op = v & 0xfu, len = v >> 4;
+				if (op != OP_EQ) { em.push(op, len); if (op == OP_I || op == OP_S) qpos += len; continue; }
+				uint32_t left = len;
+				while (left) {
+					uint32_t const bit = qpos & 31u;
+					uint32_t const n = (32u - bit < left) ? (32u - bit) : left;
+					uint32_t m = (sm.mm[qpos >> 5][tid] >> bit) & ((n == 32u) ? ~0u : ((1u << n) - 1u));
+					if (!m) em.push(OP_EQ, n);
+					else {
+						uint32_t pos = 0;
+						while (pos < n) {
+							uint32_t const rest = m >> pos;
+							uint32_t l;
+							if (rest & 1u) { uint32_t const inv = ~rest; l = inv ? (uint32_t) (__ffs((int) inv) - 1) : 32u; if (l > n - pos) l = n - pos; em.push(OP_X, l); }
+							else { l = rest ? (uint32_t) (__ffs((int) rest) - 1) : 32u; if (l > n - pos) l = n - pos; em.push(OP_EQ, l); }
+							pos += l;
+						}
+					}
+					qpos += n; left -= n;
+				}
+			}
+			em.flush();
 			n_ops = em.n_out;
 			if (em.overflow) defer = true;
-			if (!flags && !defer && P.stage == 0) {
+			if (!defer && P.stage == 0) {
 				if (n_ops == 0) flags |= PV3_FLAG_EMPTY_CIGAR;                                   // cigar.cc:16-18 UB
-				else if (em.adjacent_id) {
+				else if (adjacent_id) {
 					bool has_qual = false;
 					if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);
 					bool const affine = has_qual || P.gap_open != 0;
 					unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
-					n_runs = scan_runs <false>(&sm.out[0][tid], TT, n_ops, e0, rec, nq, R.n, nullptr, nullptr, flags, cells, path, pool, max_pool, affine, false);
+					n_runs = scan_runs <false>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, nullptr, nullptr, flags, cells, path, pool, max_pool, affine, false);
 					if (!flags && n_runs) {
 						job_base = atomicAdd(&P.counters->job_cursor, (unsigned long long) n_runs);
 						atomicAdd(&P.counters->n_realigned, 1ull);
@@ -273,7 +310,7 @@ k1_thread_kernel(K1Params P)
 						if (job_base + n_runs > P.rr_cap) atomicOr(&P.counters->overflow, 2u);
 						else {
 							uint32_t f = 0; unsigned long long a = 0, b = 0, c = 0, d = 0;
-							scan_runs <true>(&sm.out[0][tid], TT, n_ops, e0, rec, nq, R.n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, true);
+							scan_runs <true>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, true);
 						}
 					} else n_runs = 0;
 				}
@@ -313,7 +350,7 @@ k1_thread_kernel(K1Params P)
 			P.rr_len[rec] = n_runs;
 			P.cig_out_off[rec] = (base == ~0ull || flags) ? 0 : base + my_off;
 			P.cig_out_len[rec] = (base == ~0ull) ? 0 : cnt;
-			if (base != ~0ull) for (uint32_t j = 0; j < cnt; ++j) P.arena[base + my_off + j] = sm.out[j][tid];
+			if (base != ~0ull) for (uint32_t j = 0; j < cnt; ++j) P.arena[base + my_off + j] = sm.fin[j][tid];
 		}
 		__syncthreads();
 	}
