@@ -118,7 +118,8 @@ int         pv3_set_stream(pv3_ctx *, void *cuda_stream);
 /* -- index (replaces msa_index::sequence_entry over sdsl::rrr_vector<15>, include/panvc3/msa_index.hh:47-74) --------- */
 int pv3_index_add_row(pv3_ctx *, const uint64_t *gap_words, uint64_t n_bits);  /* returns row id >= 0 */
 int pv3_index_add_ref(pv3_ctx *, const char *bases, uint64_t n);               /* returns contig id >= 0 */
-int pv3_index_commit(pv3_ctx *);                /* builds rank/select directories, uploads; index is immutable afterwards */
+int pv3_index_commit(pv3_ctx *);                /* builds rank/select directories and uploads. Rows/contigs may still be added
+                                                   afterwards (ids are stable); the next commit uploads the whole index again */
 
 /* -- parameters (project_alignments -g / -e; defaults 0 / -1, project-alignments/cmdline.ggo) ------------------------ */
 int pv3_set_params(pv3_ctx *, int32_t gap_open, int32_t gap_ext);

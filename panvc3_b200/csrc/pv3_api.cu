@@ -166,7 +166,7 @@ const char *pv3_last_error(const pv3_ctx *ctx) { return ctx ? ctx->error.c_str()
 int pv3_index_add_row(pv3_ctx *ctx, const uint64_t *gap_words, uint64_t n_bits)
 {
 	if (!ctx || (!gap_words && n_bits)) return fail(ctx, PV3_ERR_INVALID, "pv3_index_add_row: bad argument");
-	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_add_row: index already committed");
+	ctx->committed = false;   // rows may be added later (lazily registered entries); the next commit re-uploads
 	HostRow row;
 	row.n_bits = n_bits;
 	row.words.assign(gap_words, gap_words + (n_bits + 63) / 64);
@@ -177,7 +177,7 @@ int pv3_index_add_row(pv3_ctx *ctx, const uint64_t *gap_words, uint64_t n_bits)
 int pv3_index_add_ref(pv3_ctx *ctx, const char *bases, uint64_t n)
 {
 	if (!ctx || (!bases && n)) return fail(ctx, PV3_ERR_INVALID, "pv3_index_add_ref: bad argument");
-	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_add_ref: index already committed");
+	ctx->committed = false;
 	HostRef ref; ref.bases.assign(bases, bases + n);
 	ctx->refs.emplace_back(std::move(ref));
 	return (int) ctx->refs.size() - 1;
@@ -186,7 +186,8 @@ int pv3_index_add_ref(pv3_ctx *ctx, const char *bases, uint64_t n)
 int pv3_index_commit(pv3_ctx *ctx)
 {
 	if (!ctx) return PV3_ERR_INVALID;
-	if (ctx->committed) return fail(ctx, PV3_ERR_STATE, "pv3_index_commit: already committed");
+	if (ctx->committed) return PV3_OK;
+	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	PV3_CUDA(ctx, cudaSetDevice(ctx->device));
 
 	// Layout of the single index allocation: per row [words | blk_zeros | sel], then the contigs; 256-byte aligned parts.
@@ -283,9 +284,6 @@ int pv3_index_commit(pv3_ctx *ctx)
 	PV3_CUDA(ctx, cudaMemcpy(ctx->row_desc.p, rd.data(), rd.size() * sizeof(RowDesc), cudaMemcpyHostToDevice));
 	PV3_CUDA(ctx, cudaMemcpy(ctx->ref_desc.p, fd.data(), fd.size() * sizeof(RefDesc), cudaMemcpyHostToDevice));
 	ctx->committed = true;
-	// host copies are no longer needed
-	for (auto &row : ctx->rows) { std::vector <uint64_t>().swap(row.words); }
-	for (auto &ref : ctx->refs) { uint64_t n = ref.bases.size(); std::string().swap(ref.bases); (void) n; }
 	return PV3_OK;
 }
 
