@@ -42,11 +42,26 @@ struct HostRef { std::string bases; };
 
 } // namespace
 
+// One of two buffer sets of the chunked host pipeline (device mirrors of a chunk's inputs and outputs).
+struct HostSet {
+	DevBuf   in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig;
+	DevBuf   out_dst_pos, out_flags, out_cig_off, out_cig_len, out_arena, out_rr_off, out_rr_len, out_rr;
+	uint64_t arena_cap_hint = 0, rr_cap_hint = 0;
+	void release()
+	{
+		for (DevBuf *b : { &in_src_row, &in_dst_row, &in_dst_ref, &in_src_pos, &in_seq_off, &in_seq, &in_qual_off, &in_qual, &in_cig_off, &in_cig,
+				&out_dst_pos, &out_flags, &out_cig_off, &out_cig_len, &out_arena, &out_rr_off, &out_rr_len, &out_rr }) b->release();
+	}
+};
+
 struct pv3_ctx {
 	int          device = 0;
 	int          n_sms = 148;
 	cudaStream_t stream = nullptr;       // the stream all work is issued on
 	cudaStream_t own_stream = nullptr;
+	cudaStream_t stream2 = nullptr;      // second stream of the chunked host pipeline
+	cudaEvent_t  cev[2][4] = {};         // per buffer set: H2D begin/end, D2H begin/end
+	HostSet      sets[2];
 	cudaEvent_t  ev[8] = {};
 	std::string  error;
 
@@ -63,7 +78,9 @@ struct pv3_ctx {
 	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
 
 	// device work buffers
-	DevBuf       counters, jobs, dp_arena, pool, deferred;
+	DevBuf       counters, jobs, dp_arena, pool, deferred, d_packed, d_job_qual_off;
+	Job         *h_jobs = nullptr; uint64_t *h_job_qual_off = nullptr; uint64_t h_jobs_cap = 0;   // pinned (lazy QUAL)
+	uint8_t     *h_packed = nullptr; uint64_t h_packed_cap = 0;
 	Counters    *h_counters = nullptr;   // pinned
 	// host-path device mirrors
 	DevBuf       in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig;
@@ -141,13 +158,19 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred,
+	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->d_packed, &ctx->d_job_qual_off,
 			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
 			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
 		b->release();
 	if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+	if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
+	if (ctx->h_job_qual_off) cudaFreeHost(ctx->h_job_qual_off);
+	if (ctx->h_packed) cudaFreeHost(ctx->h_packed);
 	for (auto &ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+	for (auto &hs : ctx->sets) hs.release();
+	for (auto &row : ctx->cev) for (auto &ev : row) if (ev) cudaEventDestroy(ev);
+	if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -348,16 +371,29 @@ K1Params make_k1(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	return P;
 }
 
-int fetch_counters(pv3_ctx *ctx)
+int fetch_counters(pv3_ctx *ctx, cudaStream_t stream)
 {
-	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, ctx->stream));
-	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(stream));
 	return PV3_OK;
 }
 
 // The kernel pipeline on device-resident buffers. Events: 0 start, 1 after K1, 2 after K3, 3 after K4.
-int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
+// Host-side description of where a chunk's QUAL lives when it has NOT been uploaded (lazy QUAL): the rewrite kernel never
+// reads base qualities, only the realignment of the (few) indel runs does, so the host path uploads just those windows.
+struct PipeOpts {
+	cudaStream_t    stream = nullptr;
+	uint64_t        arena_off = 0, rr_base = 0;
+	bool            lazy_qual = false;
+	const uint64_t *h_qual_off = nullptr;   // host, indexed by chunk-local record, values are offsets into h_qual
+	const uint8_t  *h_qual = nullptr;       // host
+	uint8_t        *d_qual_chunk = nullptr; // device buffer for the whole chunk's QUAL (bulk fallback)
+	uint64_t        chunk_q0 = 0, chunk_q1 = 0;
+};
+
+int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeOpts const &opt)
 {
+	cudaStream_t const stream = opt.stream ? opt.stream : ctx->stream;
 	out->cig_used = out->rr_used = out->n_flagged = out->n_realigned = out->dp_cells = 0;
 	ctx->timing.ms_rewrite = ctx->timing.ms_realign = ctx->timing.ms_splice = ctx->timing.ms_total = 0;
 	ctx->timing.launches = 0;
@@ -366,33 +402,34 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	PV3_CUDA(ctx, ctx->deferred.ensure(in->n * 8));
 	K1Params P = make_k1(ctx, in, out);
 	P.deferred = ctx->deferred.as <uint64_t>();
-	PV3_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), ctx->stream));
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+	P.arena_off = opt.arena_off; P.rr_base = opt.rr_base;
+	PV3_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), stream));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[0], stream));
 	int st = PV3_OK;
 	if (ctx->kernel_path == 0) {
 		// short records: one thread each; whatever exceeds its fixed quotas comes back in the deferred list
-		launch_k1_thread(P, ctx->n_sms, ctx->stream);
+		launch_k1_thread(P, ctx->n_sms, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		ctx->timing.launches += 1;
-		st = fetch_counters(ctx);
+		st = fetch_counters(ctx, stream);
 		if (st) return st;
 		if (ctx->h_counters->n_deferred && !ctx->h_counters->overflow) {
 			K1Params P2 = P;
 			P2.rec_list = ctx->deferred.as <uint64_t>();
 			P2.n_list = ctx->h_counters->n_deferred;
-			launch_k1(P2, ctx->n_sms, ctx->stream);
+			launch_k1(P2, ctx->n_sms, stream);
 			PV3_CUDA(ctx, cudaGetLastError());
 			ctx->timing.launches += 1;
-			PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-			st = fetch_counters(ctx);
+			PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
+			st = fetch_counters(ctx, stream);
 			if (st) return st;
-		} else PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+		} else PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
 	} else {
-		launch_k1(P, ctx->n_sms, ctx->stream);
+		launch_k1(P, ctx->n_sms, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
-		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
 		ctx->timing.launches += 1;
-		st = fetch_counters(ctx);
+		st = fetch_counters(ctx, stream);
 		if (st) return st;
 	}
 	Counters c = *ctx->h_counters;
@@ -426,14 +463,51 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 			K.pool = ctx->pool.as <uint8_t>(); K.pool_slot_bytes = slot;
 		}
 		memcpy(K.lut, ctx->lut, sizeof K.lut);
-		launch_k3(K, ctx->n_sms, grid_warps, ctx->stream);
+		if (opt.lazy_qual) {
+			if (n_jobs * 16 > in->n) {
+				// many runs (indel-heavy input): one bulk upload of the chunk's QUAL beats gathering windows
+				PV3_CUDA(ctx, cudaMemcpyAsync(opt.d_qual_chunk, opt.h_qual + opt.chunk_q0, opt.chunk_q1 - opt.chunk_q0, cudaMemcpyHostToDevice, stream));
+			} else {
+				// gather the query windows of the runs on the host and upload only those bytes
+				if (ctx->h_jobs_cap < n_jobs) {
+					if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
+					if (ctx->h_job_qual_off) cudaFreeHost(ctx->h_job_qual_off);
+					ctx->h_jobs_cap = n_jobs * 2 + 1024;
+					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_jobs, ctx->h_jobs_cap * sizeof(Job)));
+					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_job_qual_off, ctx->h_jobs_cap * 8));
+				}
+				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_jobs, ctx->jobs.p, n_jobs * sizeof(Job), cudaMemcpyDeviceToHost, stream));
+				PV3_CUDA(ctx, cudaStreamSynchronize(stream));
+				uint64_t need = 0;
+				for (uint64_t j = 0; j < n_jobs; ++j) need += ctx->h_jobs[j].qry_len;
+				if (ctx->h_packed_cap < need + 16) {
+					if (ctx->h_packed) cudaFreeHost(ctx->h_packed);
+					ctx->h_packed_cap = need * 2 + 4096;
+					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_packed, ctx->h_packed_cap));
+				}
+				uint64_t w = 0;
+				for (uint64_t j = 0; j < n_jobs; ++j) {
+					Job const &job = ctx->h_jobs[j];
+					ctx->h_job_qual_off[j] = w;
+					uint64_t const q0 = opt.h_qual_off[job.rec], q1 = opt.h_qual_off[job.rec + 1];
+					if (q1 > q0) { memcpy(ctx->h_packed + w, opt.h_qual + q0 + job.qry_loc, job.qry_len); w += job.qry_len; }
+				}
+				PV3_CUDA(ctx, ctx->d_packed.ensure(w + 16));
+				PV3_CUDA(ctx, ctx->d_job_qual_off.ensure(n_jobs * 8));
+				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->d_packed.p, ctx->h_packed, w, cudaMemcpyHostToDevice, stream));
+				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->d_job_qual_off.p, ctx->h_job_qual_off, n_jobs * 8, cudaMemcpyHostToDevice, stream));
+				K.packed_qual = ctx->d_packed.as <uint8_t>();
+				K.job_qual_off = ctx->d_job_qual_off.as <uint64_t>();
+			}
+		}
+		launch_k3(K, ctx->n_sms, grid_warps, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
-		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
-		launch_k4(P, n_jobs, K.dp_arena, ctx->stream);
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[2], stream));
+		launch_k4(P, n_jobs, K.dp_arena, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
-		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[3], stream));
 		ctx->timing.launches += 2;
-		st = fetch_counters(ctx);
+		st = fetch_counters(ctx, stream);
 		if (st) return st;
 		c = *ctx->h_counters;
 		ran_dp = true;
@@ -476,93 +550,159 @@ int pv3_project_device(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	if (st) return st;
 	if (!in || !out) return fail(ctx, PV3_ERR_INVALID, "pv3_project_device: NULL batch");
 	ctx->timing.ms_h2d = ctx->timing.ms_d2h = 0;
-	return run_pipeline(ctx, in, out);
+	return run_pipeline(ctx, in, out, PipeOpts());
 }
 
 int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 {
+	// Host pipeline (replaces the 16-slot SPSC ring of 4-record tasks, include/panvc3/spsc_queue.hh): the batch is cut
+	// into chunks; chunk i+1's H2D copy runs on the other stream while chunk i's kernels and chunk i-1's D2H copy run,
+	// so PCIe transfers in both directions overlap the compute. QUAL is uploaded lazily (see PipeOpts).
 	int st = check_ready(ctx, "pv3_project");
 	if (st) return st;
 	if (!in || !out) return fail(ctx, PV3_ERR_INVALID, "pv3_project: NULL batch");
 	uint64_t const n = in->n;
 	out->cig_used = out->rr_used = out->n_flagged = out->n_realigned = out->dp_cells = 0;
+	memset(&ctx->timing, 0, sizeof ctx->timing);
 	if (!n) return PV3_OK;
-	uint64_t const seq_bytes = in->seq_off[n], cig_words = in->cig_off[n];
-	uint64_t const qual_bytes = in->qual_off ? in->qual_off[n] : 0;
 
-	struct Copy { DevBuf *buf; const void *src; size_t bytes; };
-	Copy const copies[] = {
-		{ &ctx->in_src_row, in->src_row, n * 4 }, { &ctx->in_dst_row, in->dst_row, n * 4 }, { &ctx->in_dst_ref, in->dst_ref, n * 4 },
-		{ &ctx->in_src_pos, in->src_pos, n * 8 }, { &ctx->in_seq_off, in->seq_off, (n + 1) * 8 }, { &ctx->in_seq, in->seq, seq_bytes },
-		{ &ctx->in_qual_off, in->qual_off, in->qual_off ? (n + 1) * 8 : 0 }, { &ctx->in_qual, in->qual, qual_bytes },
-		{ &ctx->in_cig_off, in->cig_off, (n + 1) * 8 }, { &ctx->in_cig, in->cig, cig_words * 4 },
+	bool const own_streams = (ctx->stream == ctx->own_stream);
+	uint64_t n_chunks = own_streams ? (n + 125000) / 250000 : 1;
+	if (n_chunks < 1) n_chunks = 1;
+	if (n_chunks > 64) n_chunks = 64;
+	if (own_streams && !ctx->stream2) PV3_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+	cudaStream_t const streams[2] = { ctx->stream, own_streams ? ctx->stream2 : ctx->stream };
+	for (int k = 0; k < 2; ++k) for (int e = 0; e < 4; ++e)
+		if (!ctx->cev[k][e]) PV3_CUDA(ctx, cudaEventCreate(&ctx->cev[k][e]));
+
+	auto chunk_begin = [&](uint64_t c) { return (n * c / n_chunks) / 128 * 128; };   // tile-aligned cuts
+	auto chunk_end = [&](uint64_t c) { return c + 1 == n_chunks ? n : (n * (c + 1) / n_chunks) / 128 * 128; };
+
+	// H2D of chunk c into buffer set c % 2 (QUAL bytes are not copied)
+	auto enqueue_h2d = [&](uint64_t c) -> int {
+		HostSet &hs = ctx->sets[c % 2];
+		cudaStream_t const stream = streams[c % 2];
+		uint64_t const b = chunk_begin(c), e = chunk_end(c), m = e - b;
+		uint64_t const s0 = in->seq_off[b], s1 = in->seq_off[e], c0 = in->cig_off[b], c1 = in->cig_off[e];
+		struct Copy { DevBuf *buf; const void *src; size_t bytes; };
+		Copy const copies[] = {
+			{ &hs.in_src_row, in->src_row + b, m * 4 }, { &hs.in_dst_row, in->dst_row + b, m * 4 }, { &hs.in_dst_ref, in->dst_ref + b, m * 4 },
+			{ &hs.in_src_pos, in->src_pos + b, m * 8 }, { &hs.in_seq_off, in->seq_off + b, (m + 1) * 8 }, { &hs.in_seq, in->seq + s0, s1 - s0 },
+			{ &hs.in_qual_off, in->qual_off ? in->qual_off + b : nullptr, in->qual_off ? (m + 1) * 8 : 0 },
+			{ &hs.in_cig_off, in->cig_off + b, (m + 1) * 8 }, { &hs.in_cig, in->cig + c0, (c1 - c0) * 4 },
+		};
+		for (auto const &cp : copies) PV3_CUDA(ctx, cp.buf->ensure((cp.bytes ? cp.bytes : 16) + 32));
+		if (in->qual_off) PV3_CUDA(ctx, hs.in_qual.ensure(in->qual_off[e] - in->qual_off[b] + 32));
+		PV3_CUDA(ctx, cudaEventRecord(ctx->cev[c % 2][0], stream));
+		for (auto const &cp : copies)
+			if (cp.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(cp.buf->p, cp.src, cp.bytes, cudaMemcpyHostToDevice, stream));
+		PV3_CUDA(ctx, cudaEventRecord(ctx->cev[c % 2][1], stream));
+		return PV3_OK;
 	};
-	for (auto const &c : copies) PV3_CUDA(ctx, c.buf->ensure(c.bytes ? c.bytes : 16));
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
-	for (auto const &c : copies)
-		if (c.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(c.buf->p, c.src, c.bytes, cudaMemcpyHostToDevice, ctx->stream));
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
 
-	pv3_batch_in din = *in;
-	din.src_row = ctx->in_src_row.as <uint32_t>(); din.dst_row = ctx->in_dst_row.as <uint32_t>(); din.dst_ref = ctx->in_dst_ref.as <uint32_t>();
-	din.src_pos = ctx->in_src_pos.as <uint64_t>(); din.seq_off = ctx->in_seq_off.as <uint64_t>(); din.seq = ctx->in_seq.as <uint8_t>();
-	din.qual_off = in->qual_off ? ctx->in_qual_off.as <uint64_t>() : nullptr; din.qual = ctx->in_qual.as <uint8_t>();
-	din.cig_off = ctx->in_cig_off.as <uint64_t>(); din.cig = ctx->in_cig.as <uint32_t>();
-
-	PV3_CUDA(ctx, ctx->out_dst_pos.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_flags.ensure(n * 4));
-	PV3_CUDA(ctx, ctx->out_cig_off.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_cig_len.ensure(n * 4));
-	PV3_CUDA(ctx, ctx->out_rr_off.ensure(n * 8)); PV3_CUDA(ctx, ctx->out_rr_len.ensure(n * 4));
-
-	uint64_t arena_cap = cig_words * 3 + n * 8 + 1024, rr_cap = n / 8 + 1024;
-	if (arena_cap < ctx->arena_cap_hint) arena_cap = ctx->arena_cap_hint;
-	if (rr_cap < ctx->rr_cap_hint) rr_cap = ctx->rr_cap_hint;
-	pv3_batch_out dout;
-	float ms_k[4] = { 0, 0, 0, 0 };
+	uint64_t arena_off = 0, rr_base = 0;
+	bool host_short = false;
+	float ms_h2d = 0, ms_d2h = 0, ms_k[4] = { 0, 0, 0, 0 };
 	uint64_t launches = 0;
-	for (int attempt = 0; ; ++attempt) {
-		PV3_CUDA(ctx, ctx->out_arena.ensure(arena_cap * 4));
-		PV3_CUDA(ctx, ctx->out_rr.ensure(rr_cap * 32));
-		memset(&dout, 0, sizeof dout);
-		dout.dst_pos = ctx->out_dst_pos.as <uint64_t>(); dout.flags = ctx->out_flags.as <uint32_t>();
-		dout.cig_off = ctx->out_cig_off.as <uint64_t>(); dout.cig_len = ctx->out_cig_len.as <uint32_t>();
-		dout.cig = ctx->out_arena.as <uint32_t>(); dout.cig_cap = arena_cap;
-		dout.rr_off = ctx->out_rr_off.as <uint64_t>(); dout.rr_len = ctx->out_rr_len.as <uint32_t>();
-		dout.rr = ctx->out_rr.as <uint64_t>(); dout.rr_cap = rr_cap;
-		st = run_pipeline(ctx, &din, &dout);
-		launches += ctx->timing.launches;
-		if (st == PV3_ERR_CAPACITY && attempt < 6) {
-			// grow from what the kernels reported and run the batch again (results of the failed attempt are discarded)
-			if (dout.cig_used + 1024 > arena_cap) arena_cap = dout.cig_used * 2 + 1024; else arena_cap *= 2;
-			if (dout.rr_used + 64 > rr_cap) rr_cap = dout.rr_used * 2 + 64;
-			continue;
-		}
-		if (st) return st;
-		break;
-	}
-	ctx->arena_cap_hint = arena_cap; ctx->rr_cap_hint = rr_cap;
-	ms_k[0] = ctx->timing.ms_rewrite; ms_k[1] = ctx->timing.ms_realign; ms_k[2] = ctx->timing.ms_splice; ms_k[3] = ctx->timing.ms_total;
+	int pending_d2h[2] = { 0, 0 };
 
-	out->cig_used = dout.cig_used; out->rr_used = dout.rr_used; out->n_flagged = dout.n_flagged;
-	out->n_realigned = dout.n_realigned; out->dp_cells = dout.dp_cells;
-	if (dout.cig_used > out->cig_cap || dout.rr_used > out->rr_cap)
-		return fail(ctx, PV3_ERR_CAPACITY, "host output capacity too small: need cig_cap >= %llu, rr_cap >= %llu",
-			(unsigned long long) dout.cig_used, (unsigned long long) dout.rr_used);
-
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[6], ctx->stream));
-	struct Back { void *dst; const void *src; size_t bytes; };
-	Back const backs[] = {
-		{ out->dst_pos, dout.dst_pos, n * 8 }, { out->flags, dout.flags, n * 4 }, { out->cig_off, dout.cig_off, n * 8 },
-		{ out->cig_len, dout.cig_len, n * 4 }, { out->rr_off, dout.rr_off, n * 8 }, { out->rr_len, dout.rr_len, n * 4 },
-		{ out->cig, dout.cig, dout.cig_used * 4 }, { out->rr, dout.rr, dout.rr_used * 32 },
+	auto harvest_copy_times = [&](int k) {
+		float t = 0;
+		if (cudaEventElapsedTime(&t, ctx->cev[k][0], ctx->cev[k][1]) == cudaSuccess) ms_h2d += t;
+		if (pending_d2h[k] && cudaEventElapsedTime(&t, ctx->cev[k][2], ctx->cev[k][3]) == cudaSuccess) ms_d2h += t;
+		pending_d2h[k] = 0;
 	};
-	for (auto const &b : backs)
-		if (b.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(b.dst, b.src, b.bytes, cudaMemcpyDeviceToHost, ctx->stream));
-	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[7], ctx->stream));
-	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	cudaEventElapsedTime(&ctx->timing.ms_h2d, ctx->ev[4], ctx->ev[5]);
-	cudaEventElapsedTime(&ctx->timing.ms_d2h, ctx->ev[6], ctx->ev[7]);
+
+	st = enqueue_h2d(0);
+	if (st) return st;
+	for (uint64_t c = 0; c < n_chunks; ++c) {
+		int const k = (int) (c % 2);
+		HostSet &hs = ctx->sets[k];
+		cudaStream_t const stream = streams[k];
+		uint64_t const b = chunk_begin(c), e = chunk_end(c), m = e - b;
+		if (c + 1 < n_chunks) {
+			// the other set's previous D2H (chunk c-1) only reads its output buffers; its input buffers are free
+			if (own_streams) { st = enqueue_h2d(c + 1); if (st) return st; }
+		}
+		if (!m) { if (!own_streams && c + 1 < n_chunks) { st = enqueue_h2d(c + 1); if (st) return st; } continue; }
+
+		pv3_batch_in din = *in;
+		din.n = m;
+		din.src_row = hs.in_src_row.as <uint32_t>(); din.dst_row = hs.in_dst_row.as <uint32_t>(); din.dst_ref = hs.in_dst_ref.as <uint32_t>();
+		din.src_pos = hs.in_src_pos.as <uint64_t>(); din.seq_off = hs.in_seq_off.as <uint64_t>();
+		din.seq = hs.in_seq.as <uint8_t>() - in->seq_off[b];              // offsets in seq_off stay batch-global
+		din.qual_off = in->qual_off ? hs.in_qual_off.as <uint64_t>() : nullptr;
+		din.qual = in->qual_off ? hs.in_qual.as <uint8_t>() - in->qual_off[b] : nullptr;
+		din.cig_off = hs.in_cig_off.as <uint64_t>();
+		din.cig = hs.in_cig.as <uint32_t>() - in->cig_off[b];
+
+		PV3_CUDA(ctx, hs.out_dst_pos.ensure(m * 8)); PV3_CUDA(ctx, hs.out_flags.ensure(m * 4));
+		PV3_CUDA(ctx, hs.out_cig_off.ensure(m * 8)); PV3_CUDA(ctx, hs.out_cig_len.ensure(m * 4));
+		PV3_CUDA(ctx, hs.out_rr_off.ensure(m * 8)); PV3_CUDA(ctx, hs.out_rr_len.ensure(m * 4));
+		uint64_t arena_cap = (in->cig_off[e] - in->cig_off[b]) * 3 + m * 8 + 1024, rr_cap = m / 8 + 1024;
+		if (arena_cap < hs.arena_cap_hint) arena_cap = hs.arena_cap_hint;
+		if (rr_cap < hs.rr_cap_hint) rr_cap = hs.rr_cap_hint;
+
+		PipeOpts opt;
+		opt.stream = stream; opt.arena_off = arena_off; opt.rr_base = rr_base;
+		if (in->qual_off) {
+			opt.lazy_qual = true; opt.h_qual_off = in->qual_off + b; opt.h_qual = in->qual;
+			opt.d_qual_chunk = hs.in_qual.as <uint8_t>(); opt.chunk_q0 = in->qual_off[b]; opt.chunk_q1 = in->qual_off[e];
+		}
+		pv3_batch_out dout;
+		for (int attempt = 0; ; ++attempt) {
+			PV3_CUDA(ctx, hs.out_arena.ensure(arena_cap * 4));
+			PV3_CUDA(ctx, hs.out_rr.ensure(rr_cap * 32));
+			memset(&dout, 0, sizeof dout);
+			dout.dst_pos = hs.out_dst_pos.as <uint64_t>(); dout.flags = hs.out_flags.as <uint32_t>();
+			dout.cig_off = hs.out_cig_off.as <uint64_t>(); dout.cig_len = hs.out_cig_len.as <uint32_t>();
+			dout.cig = hs.out_arena.as <uint32_t>(); dout.cig_cap = arena_cap;
+			dout.rr_off = hs.out_rr_off.as <uint64_t>(); dout.rr_len = hs.out_rr_len.as <uint32_t>();
+			dout.rr = hs.out_rr.as <uint64_t>(); dout.rr_cap = rr_cap;
+			st = run_pipeline(ctx, &din, &dout, opt);
+			launches += ctx->timing.launches;
+			if (st == PV3_ERR_CAPACITY && attempt < 6) {
+				// grow from what the kernels reported and run the chunk again (results of the failed attempt are discarded)
+				if (dout.cig_used + 1024 > arena_cap) arena_cap = dout.cig_used * 2 + 1024; else arena_cap *= 2;
+				if (dout.rr_used + 64 > rr_cap) rr_cap = dout.rr_used * 2 + 64;
+				continue;
+			}
+			if (st) return st;
+			break;
+		}
+		hs.arena_cap_hint = arena_cap; hs.rr_cap_hint = rr_cap;
+		ms_k[0] += ctx->timing.ms_rewrite; ms_k[1] += ctx->timing.ms_realign; ms_k[2] += ctx->timing.ms_splice; ms_k[3] += ctx->timing.ms_total;
+		harvest_copy_times(k);     // run_pipeline synchronized this stream: the events of its H2D (and older D2H) are complete
+
+		out->n_flagged += dout.n_flagged; out->n_realigned += dout.n_realigned; out->dp_cells += dout.dp_cells;
+		if (arena_off + dout.cig_used > out->cig_cap || rr_base + dout.rr_used > out->rr_cap) host_short = true;
+		if (!host_short) {
+			PV3_CUDA(ctx, cudaEventRecord(ctx->cev[k][2], stream));
+			struct Back { void *dst; const void *src; size_t bytes; };
+			Back const backs[] = {
+				{ out->dst_pos + b, dout.dst_pos, m * 8 }, { out->flags + b, dout.flags, m * 4 }, { out->cig_off + b, dout.cig_off, m * 8 },
+				{ out->cig_len + b, dout.cig_len, m * 4 }, { out->rr_off + b, dout.rr_off, m * 8 }, { out->rr_len + b, dout.rr_len, m * 4 },
+				{ out->cig + arena_off, dout.cig, dout.cig_used * 4 }, { out->rr + 4 * rr_base, dout.rr, dout.rr_used * 32 },
+			};
+			for (auto const &bk : backs)
+				if (bk.bytes) PV3_CUDA(ctx, cudaMemcpyAsync(bk.dst, bk.src, bk.bytes, cudaMemcpyDeviceToHost, stream));
+			PV3_CUDA(ctx, cudaEventRecord(ctx->cev[k][3], stream));
+			pending_d2h[k] = 1;
+		}
+		arena_off += dout.cig_used; rr_base += dout.rr_used;
+		if (!own_streams && c + 1 < n_chunks) { st = enqueue_h2d(c + 1); if (st) return st; }
+	}
+	PV3_CUDA(ctx, cudaStreamSynchronize(streams[0]));
+	if (own_streams) PV3_CUDA(ctx, cudaStreamSynchronize(streams[1]));
+	for (int k = 0; k < 2; ++k) if (pending_d2h[k]) { float t = 0; if (cudaEventElapsedTime(&t, ctx->cev[k][2], ctx->cev[k][3]) == cudaSuccess) ms_d2h += t; }
+
+	out->cig_used = arena_off; out->rr_used = rr_base;
 	ctx->timing.ms_rewrite = ms_k[0]; ctx->timing.ms_realign = ms_k[1]; ctx->timing.ms_splice = ms_k[2]; ctx->timing.ms_total = ms_k[3];
+	ctx->timing.ms_h2d = ms_h2d; ctx->timing.ms_d2h = ms_d2h;
 	ctx->timing.launches = launches;
+	if (host_short)
+		return fail(ctx, PV3_ERR_CAPACITY, "host output capacity too small: need cig_cap >= %llu, rr_cap >= %llu",
+			(unsigned long long) arena_off, (unsigned long long) rr_base);
 	return PV3_OK;
 }
 

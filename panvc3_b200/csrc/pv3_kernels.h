@@ -36,6 +36,8 @@ struct K1Params {
 	const uint64_t *rec_list;    // warp kernel: process records rec_list[0..n_list) instead of 0..n (null ⇒ all)
 	uint64_t        n_list;
 	uint64_t       *deferred;    // thread kernel: records it could not handle (capacity n)
+	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
+	uint64_t        rr_base;     // added to every stored rr_off
 };
 
 // Scratch bytes one DP job needs: byte trace (Q+1)x(R+1), strip boundary arrays (H, up: int32; tup: byte), staged
@@ -53,6 +55,8 @@ struct K3Params {
 	uint32_t       *dp_arena; uint64_t dp_arena_cap;    // realigned ops, R+Q words reserved per job
 	uint8_t        *pool; uint64_t pool_slot_bytes;     // global scratch, one slot per resident warp (for jobs too large for smem)
 	int32_t         lut[84];        // quality LUT: [2*q] match, [2*q+1] mismatch
+	const uint8_t  *packed_qual;    // lazy-QUAL path: phred ranks of the runs' query windows only, run j at job_qual_off[j]
+	const uint64_t *job_qual_off;   // null ⇒ read k1.qual
 };
 
 struct K4Params {

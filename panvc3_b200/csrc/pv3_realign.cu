@@ -72,7 +72,7 @@ k3_realign_kernel(K3Params P)
 		if (B.qual_off) {
 			uint64_t const q0 = __ldg(B.qual_off + rec);
 			has_qual = __ldg(B.qual_off + rec + 1) > q0;
-			qlptr = B.qual + q0 + job.qry_loc;
+			qlptr = P.job_qual_off ? (P.packed_qual + P.job_qual_off[jid]) : (B.qual + q0 + job.qry_loc);
 		}
 		bool const edit = !has_qual && B.gap_open == 0;
 

@@ -259,7 +259,7 @@ __device__ void flush_group(const K1Params &P, GroupState &g, const uint32_t *st
 	if (g.stage_n) {
 		uint64_t const base = arena_alloc(P, g.stage_n);
 		if (g.my_rec != ~0ull) {
-			P.cig_out_off[g.my_rec] = (base == ~0ull) ? 0 : base + g.my_off;
+			P.cig_out_off[g.my_rec] = (base == ~0ull) ? 0 : base + g.my_off + P.arena_off;
 			P.cig_out_len[g.my_rec] = (base == ~0ull) ? 0 : g.my_len;
 		}
 		if (base != ~0ull) {
@@ -314,7 +314,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 	if (lane == 0) {
 		P.dst_pos[rec] = res.dst_pos;
 		P.flags[rec] = res.flags;
-		P.rr_off[rec] = job_base;
+		P.rr_off[rec] = job_base + P.rr_base;
 		P.rr_len[rec] = n_runs;
 		if (res.flags) atomicAdd(&P.counters->n_flagged, 1ull);
 	}
@@ -359,7 +359,7 @@ k1_rewrite_kernel(K1Params P, int group)
 					finish_record(P, rec, res, stage);
 				}
 				if (lane == 0) {
-					P.cig_out_off[rec] = (base == ~0ull) ? 0 : base;
+					P.cig_out_off[rec] = (base == ~0ull) ? 0 : base + P.arena_off;
 					P.cig_out_len[rec] = (base == ~0ull || res.flags) ? 0 : res.n_ops;
 				}
 				continue;

@@ -346,9 +346,9 @@ k1_thread_kernel(K1Params P)
 			if (flags) { n_runs = 0; atomicAdd(&P.counters->n_flagged, 1ull); }
 			P.dst_pos[rec] = e0;
 			P.flags[rec] = flags;
-			P.rr_off[rec] = job_base;
+			P.rr_off[rec] = job_base + P.rr_base;
 			P.rr_len[rec] = n_runs;
-			P.cig_out_off[rec] = (base == ~0ull || flags) ? 0 : base + my_off;
+			P.cig_out_off[rec] = (base == ~0ull || flags) ? 0 : base + my_off + P.arena_off;
 			P.cig_out_len[rec] = (base == ~0ull) ? 0 : cnt;
 			if (base != ~0ull) for (uint32_t j = 0; j < cnt; ++j) P.arena[base + my_off + j] = sm.fin[j][tid];
 		}

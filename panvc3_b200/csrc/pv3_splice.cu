@@ -15,11 +15,11 @@ __global__ void k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp
 	uint64_t const jid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	if (jid >= n_jobs) return;
 	uint64_t const rec = P.jobs[jid].rec;
-	if (P.rr_off[rec] != jid) return;
+	if (P.rr_off[rec] != jid + P.rr_base) return;
 	uint32_t const n_runs = P.rr_len[rec];
 	if (P.flags[rec]) { P.cig_out_len[rec] = 0; P.rr_len[rec] = 0; return; }   // flagged by the DP kernel
 
-	const uint32_t *pre = P.arena + P.cig_out_off[rec];
+	const uint32_t *pre = P.arena + (P.cig_out_off[rec] - P.arena_off);
 	uint32_t const n_pre = P.cig_out_len[rec];
 	unsigned long long bound = n_pre;
 	for (uint32_t r = 0; r < n_runs; ++r) {
@@ -44,7 +44,7 @@ __global__ void k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp
 		k = j.op_end;
 	}
 	for (; k < n_pre; ++k) push(pre[k]);                                // :145-148
-	P.cig_out_off[rec] = base;
+	P.cig_out_off[rec] = base + P.arena_off;
 	P.cig_out_len[rec] = (uint32_t) (w + 1);
 }
 
