@@ -250,13 +250,14 @@ def run_gpu_arm(args) -> None:
     sampler.start()
     launches0 = ctx.total_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k1_ms, k3_ms, k4_ms = [], [], []
+    k1_ms, k3_ms, k4_ms, k1m_ms, n_def = [], [], [], [], []
     with torch.cuda.stream(stream):
         e0.record(stream)
         for _ in range(args.steps):
             project_device(ctx, dbatch, dout)
             t = ctx.timing()
             k1_ms.append(t["ms_rewrite"]); k3_ms.append(t["ms_realign"]); k4_ms.append(t["ms_splice"])
+            k1m_ms.append(t["ms_rewrite_main"]); n_def.append(t["n_deferred"])
         e1.record(stream)
     barrier()
     dev_ms = e0.elapsed_time(e1)
@@ -344,7 +345,7 @@ def run_gpu_arm(args) -> None:
                          "algorithmic_bytes_per_launch": ab["strict"], "bytes_per_record": ab["strict"] / n,
                          "bytes_per_record_survey_formula": ab["survey"] / n, "kernel_ms": k1,
                          "frac_survey_formula": ab["survey"] / (k1 * 1e-3) / 1e9 / peak},
-            "kernels_ms": {"rewrite": k1, "realign": statistics.mean(k3_ms), "splice": statistics.mean(k4_ms)},
+            "kernels_ms": {"rewrite": k1, "rewrite_thread_kernel_alone": statistics.mean(k1m_ms), "deferred_records": int(max(n_def)), "realign": statistics.mean(k3_ms), "splice": statistics.mean(k4_ms)},
             "realign_gcups": (stats["dp_cells"] / (statistics.mean(k3_ms) * 1e-3) / 1e9) if statistics.mean(k3_ms) > 0 else None,
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": int(batch.input_bytes() - (batch.qual.nbytes if batch.qual_off is not None else 0) + lazy_qual_bytes),

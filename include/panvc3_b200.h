@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PV3_ABI_VERSION 1
+#define PV3_ABI_VERSION 2
 
 typedef struct pv3_ctx pv3_ctx;
 
@@ -103,6 +103,9 @@ typedef struct {
 	float    ms_total;       /* first kernel start to last kernel end */
 	float    ms_h2d, ms_d2h; /* host path only */
 	uint64_t launches;       /* kernels launched by the call */
+	uint64_t n_deferred;     /* records the thread-per-record rewrite kernel handed to the warp-per-record kernel */
+	float    ms_rewrite_main;/* the thread-per-record rewrite kernel alone (ms_rewrite also holds the deferred pass) */
+	float    pad_;
 } pv3_timing;
 
 /* -- lifetime ------------------------------------------------------------------------------------------------------ */

@@ -40,7 +40,8 @@ class BatchOut(C.Structure):
 
 class Timing(C.Structure):
     _fields_ = [("ms_rewrite", C.c_float), ("ms_realign", C.c_float), ("ms_splice", C.c_float), ("ms_total", C.c_float),
-                ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("launches", C.c_uint64)]
+                ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("launches", C.c_uint64), ("n_deferred", C.c_uint64),
+                ("ms_rewrite_main", C.c_float), ("pad_", C.c_float)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -62,7 +62,7 @@ struct pv3_ctx {
 	cudaStream_t stream2 = nullptr;      // second stream of the chunked host pipeline
 	cudaEvent_t  cev[2][4] = {};         // per buffer set: H2D begin/end, D2H begin/end
 	HostSet      sets[2];
-	cudaEvent_t  ev[8] = {};
+	cudaEvent_t  ev[8] = {};             // 0 start, 1 rewrite end, 2 realign end, 3 splice end, 4 thread-kernel end
 	std::string  error;
 
 	std::vector <HostRow> rows;
@@ -395,8 +395,8 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 {
 	cudaStream_t const stream = opt.stream ? opt.stream : ctx->stream;
 	out->cig_used = out->rr_used = out->n_flagged = out->n_realigned = out->dp_cells = 0;
-	ctx->timing.ms_rewrite = ctx->timing.ms_realign = ctx->timing.ms_splice = ctx->timing.ms_total = 0;
-	ctx->timing.launches = 0;
+	ctx->timing.ms_rewrite = ctx->timing.ms_realign = ctx->timing.ms_splice = ctx->timing.ms_total = ctx->timing.ms_rewrite_main = 0;
+	ctx->timing.launches = 0; ctx->timing.n_deferred = 0;
 	if (!in->n) return PV3_OK;
 	PV3_CUDA(ctx, ctx->jobs.ensure((out->rr_cap ? out->rr_cap : 1) * sizeof(Job)));
 	PV3_CUDA(ctx, ctx->deferred.ensure(in->n * 8));
@@ -410,6 +410,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 		// short records: one thread each; whatever exceeds its fixed quotas comes back in the deferred list
 		launch_k1_thread(P, ctx->n_sms, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], stream));
 		ctx->timing.launches += 1;
 		st = fetch_counters(ctx, stream);
 		if (st) return st;
@@ -522,6 +523,9 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 	out->n_realigned = c.n_realigned;
 	out->dp_cells = c.dp_cells;
 	cudaEventElapsedTime(&ctx->timing.ms_rewrite, ctx->ev[0], ctx->ev[1]);
+	if (ctx->kernel_path == 0) cudaEventElapsedTime(&ctx->timing.ms_rewrite_main, ctx->ev[0], ctx->ev[4]);
+	else ctx->timing.ms_rewrite_main = ctx->timing.ms_rewrite;
+	ctx->timing.n_deferred = c.n_deferred;
 	if (ran_dp) {
 		cudaEventElapsedTime(&ctx->timing.ms_realign, ctx->ev[1], ctx->ev[2]);
 		cudaEventElapsedTime(&ctx->timing.ms_splice, ctx->ev[2], ctx->ev[3]);
@@ -603,7 +607,8 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	uint64_t arena_off = 0, rr_base = 0;
 	bool host_short = false;
 	float ms_h2d = 0, ms_d2h = 0, ms_k[4] = { 0, 0, 0, 0 };
-	uint64_t launches = 0;
+	uint64_t launches = 0, n_deferred = 0;
+	float ms_main = 0;
 	int pending_d2h[2] = { 0, 0 };
 
 	auto harvest_copy_times = [&](int k) {
@@ -672,6 +677,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		}
 		hs.arena_cap_hint = arena_cap; hs.rr_cap_hint = rr_cap;
 		ms_k[0] += ctx->timing.ms_rewrite; ms_k[1] += ctx->timing.ms_realign; ms_k[2] += ctx->timing.ms_splice; ms_k[3] += ctx->timing.ms_total;
+		n_deferred += ctx->timing.n_deferred; ms_main += ctx->timing.ms_rewrite_main;
 		harvest_copy_times(k);     // run_pipeline synchronized this stream: the events of its H2D (and older D2H) are complete
 
 		out->n_flagged += dout.n_flagged; out->n_realigned += dout.n_realigned; out->dp_cells += dout.dp_cells;
@@ -698,6 +704,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 
 	out->cig_used = arena_off; out->rr_used = rr_base;
 	ctx->timing.ms_rewrite = ms_k[0]; ctx->timing.ms_realign = ms_k[1]; ctx->timing.ms_splice = ms_k[2]; ctx->timing.ms_total = ms_k[3];
+	ctx->timing.n_deferred = n_deferred; ctx->timing.ms_rewrite_main = ms_main;
 	ctx->timing.ms_h2d = ms_h2d; ctx->timing.ms_d2h = ms_d2h;
 	ctx->timing.launches = launches;
 	if (host_short)

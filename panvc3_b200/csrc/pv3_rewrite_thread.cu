@@ -1,24 +1,27 @@
 // panvc3_b200 — kernel K1T: projection + CIGAR rewrite + run detection, ONE THREAD PER RECORD, word-parallel (sm_100a).
 //
 // Same semantics as the warp-per-record kernel in pv3_rewrite.cu (reference: include/panvc3/rewrite_cigar.hh:19-157,
-// libpanvc3/cigar.cc:61-95, libpanvc3/indel_run_checker.cc:31-121, libpanvc3/alignment_projector.cc:61-73) but the
-// per-column work is done 64 columns at a time with bit operations on the source/target gap words:
+// libpanvc3/cigar.cc:61-95, libpanvc3/indel_run_checker.cc:31-121, libpanvc3/alignment_projector.cc:61-73).
+// Every MSA column of the record's span yields at most one unit op, decided by (source bit, target bit, op class):
 //     src base & dst base   → compare run ('=' / 'X')          src base & dst gap → 'I'
 //     src gap  & dst base   → 'D' (leading deletion)           both gaps          → nothing
-// Maximal runs of one class inside a word are found with ctz; a compare run XORs 4 query ranks against 4 target codes per
-// step (RefDesc::codes: equal byte ⇔ dna5::to_char(query) == raw target byte) and extracts the mismatch bits with SWAR
-// arithmetic.  The ncu profile of the lane-per-column kernel (profiles/r1_v1_*) showed ≈1600 warp instructions per
-// 150-bp record, i.e. instruction-bound at 3 % of the HBM roofline; here a record costs O(10²..10³) *thread*
-// instructions, and 128 records are processed per CTA tile.
+//
+// v4 (this file): the ncu profile of v3 (profiles/r1_v3_*) showed 451 warp instructions per record at 11 of 32 active
+// lanes — nested per-record loops with four inlined copies of the run-length emitter diverged badly. The per-record
+// work is now three FLAT loops, each with one body that every lane executes in lock-step and one store site:
+//   C1  one iteration per column run (maximal run of equal (src bit, dst bit) inside a 64-column word) or input op:
+//       → raw run list (u16: op | len << 4, or a reference to a pass-through input op) and compare-piece list
+//   C2  one iteration per 8 bases of a compare piece: XOR of staged query ranks and target codes → mismatch bits in
+//       query coordinates
+//   C3  one iteration per output run: raw runs, '=' runs split by the mismatch bits, one cigar_buffer::push_back site
 //
 // Tile pipeline (128 threads = 128 consecutive records):
 //   A  each thread: ids, src_pos, select0/rank0 of its record → c0, e0
 //   B  cooperative, coalesced staging into shared memory: the tile's query bytes (contiguous in the batch), and per record
-//      a 208-byte window of target codes at e0 (gap words are read through L1: a record touches 3-4 words per row)
-//   C  each thread rewrites its record out of shared memory into a 24-op staging column; detects indel runs
-//   D  block scan of op counts → one atomic on the arena cursor → ops and per-record results written (coalesced
-//      per-record arrays)
-// Records that do not fit the fixed quotas (long reads, > 24 output ops, windows beyond the staged data, malformed index)
+//      a 208-byte window of target codes at e0
+//   C1..C3 as above; run detection on the final ops (only when an I abuts a D)
+//   D  block scan of op counts → one atomic on the arena cursor → ops and per-record results written
+// Records that do not fit the fixed quotas (long reads, too many runs, windows beyond the staged data, malformed index)
 // are appended to a deferred list and handled by the warp-per-record kernel afterwards — results are bit-identical.
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
@@ -28,14 +31,19 @@ namespace pv3 {
 
 constexpr int      TT        = 128;            // threads per CTA = records per tile
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
+constexpr int      T_RAWQ    = 40;             // raw runs per record (column runs + pass-through ops)
+constexpr int      T_PIECEQ  = 16;             // compare pieces per record
 constexpr uint32_t T_QSTAGE  = TT * 168;       // bytes of query staged per tile
 constexpr uint32_t T_RWIN    = 208;            // bytes of target codes staged per record (13 x 16)
 constexpr uint32_t T_MMW     = 6;              // mismatch bit words per record (query coordinates): reads up to 192 bases
+constexpr uint32_t T_C1_ITERS = 192;           // bound of the column walk (long gaps / deletions go to the warp kernel)
+constexpr uint32_t RAW_PASS  = 0x8000u;        // raw entry refers to input op (entry & 0x7fff)
 
-// 64.6 KB ⇒ 3 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
+// 71 KB ⇒ 3 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
 struct TileSmem {
-	uint32_t prov[T_OUTQ][TT];                 // provisional ops: '=' means "compare run", decided in C2/C3
-	uint32_t mm[T_MMW][TT];
+	uint16_t raw[T_RAWQ][TT];
+	uint32_t piece[T_PIECEQ][TT];              // qpos | (target offset from the staged window start) << 8 | len << 24
+	uint32_t mm[T_MMW + 1][TT];
 	uint4    q[T_QSTAGE / 16 + 2];
 	union {
 		uint4    ref[TT][T_RWIN / 16];         // [record][staged target codes]
@@ -47,49 +55,29 @@ struct TileSmem {
 };
 static_assert(sizeof(uint4) * (T_RWIN / 16) * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in ref");
 
-struct TEmitter {
-	uint32_t *out;        // &smem.out[0][tid]
-	uint32_t  n_out, carry_op, carry_cnt;
-	bool      overflow, adjacent_id;
-
-	__device__ __forceinline__ void init(uint32_t *o) { out = o; n_out = 0; carry_op = OP_NONE; carry_cnt = 0; overflow = false; adjacent_id = false; }
-	__device__ __forceinline__ void flush()
-	{
-		if (carry_op != OP_NONE) {
-			if (n_out < (uint32_t) T_OUTQ) out[n_out * TT] = (carry_cnt << 4) | carry_op; else overflow = true;
-			++n_out;
-		}
-	}
-	// cigar_buffer::push_back (cigar.cc:61-86)
-	__device__ __forceinline__ void push(uint32_t op, uint32_t cnt)
-	{
-		if (!cnt) return;
-		if (carry_op == op) { carry_cnt += cnt; return; }
-		if ((carry_op == OP_I && op == OP_D) || (carry_op == OP_D && op == OP_I)) adjacent_id = true;
-		flush();
-		carry_op = op; carry_cnt = cnt;
-	}
-};
-
 __device__ __forceinline__ uint32_t ctz64(uint64_t x) { return (uint32_t) __ffsll((long long) x) - 1u; }   // x != 0
 
-// 4 bytes at byte offset a of a word array in shared memory (may read the following word)
-__device__ __forceinline__ uint32_t load4(const uint32_t *base, uint32_t a)
-{
-	const uint32_t *p = base + (a >> 2);
-	return __funnelshift_r(p[0], p[1], (a & 3u) * 8u);
-}
-
-__device__ __forceinline__ uint32_t load4_global(const uint8_t *p)   // codes have 512 readable pad bytes
-{
-	return (uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) | ((uint32_t) __ldg(p + 3) << 24);
-}
-
-// bit i set ⇔ byte i of t is non-zero (SWAR; no per-byte branches)
-__device__ __forceinline__ uint32_t nonzero_bytes(uint32_t t)
+// bits 28..31 set ⇔ bytes 0..3 of t are non-zero (SWAR; no per-byte branches); callers shift
+__device__ __forceinline__ uint32_t nonzero_bytes_hi(uint32_t t)
 {
 	uint32_t const nz = (((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;
-	return (nz * 0x00204081u) >> 28;
+	return nz * 0x00204081u;
+}
+
+// 8 bytes at byte offset a of a word array in shared memory (reads 3 words)
+__device__ __forceinline__ void load8(const uint32_t *base, uint32_t a, uint32_t &lo, uint32_t &hi)
+{
+	const uint32_t *p = base + (a >> 2);
+	uint32_t const sh = (a & 3u) * 8u;
+	uint32_t const w0 = p[0], w1 = p[1], w2 = p[2];
+	lo = __funnelshift_r(w0, w1, sh);
+	hi = __funnelshift_r(w1, w2, sh);
+}
+
+__device__ __noinline__ void load8_global(const uint8_t *p, uint32_t &lo, uint32_t &hi)   // codes have 512 readable pad bytes
+{
+	lo = (uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) | ((uint32_t) __ldg(p + 3) << 24);
+	hi = (uint32_t) __ldg(p + 4) | ((uint32_t) __ldg(p + 5) << 8) | ((uint32_t) __ldg(p + 6) << 16) | ((uint32_t) __ldg(p + 7) << 24);
 }
 
 __global__ void __launch_bounds__(TT)
@@ -137,7 +125,7 @@ k1_thread_kernel(K1Params P)
 				spos = __ldg(P.src_pos + rec);
 				c0 = (spos < S.n_zeros) ? select0_thread(S, spos + 1) : S.n_bits;     // rewrite_cigar.hh:51
 				e0 = rank0_thread(D, c0);                                              // :52
-				if (S.n_bits != D.n_bits || e0 > R.n || nq > 32u * T_MMW) defer = true;                    // unusual index: the general kernel guards it
+				if (S.n_bits != D.n_bits || e0 > R.n || nq > 32u * T_MMW || nc >= RAW_PASS) defer = true;   // unusual: the general kernel guards it
 				if (!defer) {
 					sm.ref_ptr[tid] = R.codes + (e0 & ~15ull);
 				}
@@ -156,142 +144,152 @@ k1_thread_kernel(K1Params P)
 			uint32_t const l16 = lane & 15u;
 			if (rp && l16 < T_RWIN / 16) sm.ref[r][l16] = __ldg(reinterpret_cast <const uint4 *>(rp) + l16);
 		}
-		__syncthreads();
 
-		// ---- phase C1: gap words → provisional ops (compare runs become '=' of unknown content) --------------------
-		uint32_t n_prov = 0, n_ops = 0, n_runs = 0;
+		// ---- phase C1: one flat walk over the column runs of the record's span -------------------------------------
+		// Output: raw runs ('=' stands for a compare run of unknown content) and the compare pieces.
+		uint32_t n_raw = 0, n_piece = 0, n_ops = 0, n_runs = 0;
 		unsigned long long job_base = 0;
-		bool adjacent_id = false;
 		uint64_t const e0a = e0 & ~15ull;
 		bool const work = active && !flags && !defer;
 		if (work) {
-			TEmitter em; em.init(&sm.prov[0][tid]);
-			uint64_t col = c0, e = e0, qpos = 0;
+			uint64_t col = c0, e = e0, wcur = ~0ull, Sinv = 0, Dinv = 0;
 			uint64_t src_left = (spos < S.n_zeros) ? (S.n_zeros - spos) : 0;
-
-			for (uint32_t k = 0; k < nc && !flags; ++k) {
-				uint32_t const packed = __ldg(P.cig + cbase + k);
-				uint32_t const cnt = packed >> 4, op = packed & 0xfu;
-				if (op == OP_I || op == OP_S) { em.push(op, cnt); qpos += cnt; continue; }     // rewrite_cigar.hh:68-72
-				if (op == OP_H || op == OP_P) { em.push(op, cnt); continue; }                  // :74-77
-				if (op > OP_X) { flags |= PV3_FLAG_BAD_OP; break; }                             // :149-151
-				bool const mlike = (op == OP_M || op == OP_EQ || op == OP_X);
-				if (cnt > src_left) { flags |= PV3_FLAG_POS_OOB; break; }
-				src_left -= cnt;
-				uint32_t rem = cnt;
-				while (rem && !flags) {
-					uint64_t const wi = col >> 6;
-					uint64_t const Sw = __ldg(S.words + wi), Dw = __ldg(D.words + wi);
-					uint64_t valid = ~0ull << (col & 63);
-					uint64_t const z = ~Sw & valid;
-					uint32_t const zc = __popcll(z);
-					uint32_t take;
-					if (zc >= rem) {
-						unsigned const last = select_in_word(z, rem);
-						if (last < 63) valid &= (2ull << last) - 1ull;
-						take = rem;
-						col = wi * 64 + last + 1;
-					} else { take = zc; col = (wi + 1) * 64; }
-					uint64_t const sz = ~Sw & valid, dz = ~Dw & valid;
-					if (!mlike) {                                        // D, N: rewrite_cigar.hh:119-147
-						uint32_t const nd = __popcll(dz);
-						em.push(OP_D, nd); e += nd;
-					} else {                                             // M, =, X: :79-117
-						uint64_t x = sz | dz;
-						while (x) {
-							uint32_t const p = ctz64(x);
-							uint64_t const sb = (sz >> p) & 1ull, db = (dz >> p) & 1ull;
-							uint64_t const same = ~((sz ^ (0ull - sb)) | (dz ^ (0ull - db)));
-							uint64_t const nr = ~(same >> p);
-							uint32_t const len = nr ? ctz64(nr) : 64u;
-							if (sb && db) {
-								if (qpos + len > nq) { flags |= PV3_FLAG_QUERY_OOB; break; }      // :102
-								if (e + len > R.n) { flags |= PV3_FLAG_REF_OOB; break; }          // :103
-								em.push(OP_EQ, len);
-								qpos += len; e += len;
-							} else if (sb) { em.push(OP_I, len); qpos += len; }
-							else { em.push(OP_D, len); e += len; }
-							x = (p + len >= 64u) ? 0ull : (x & (~0ull << (p + len)));
-						}
+			uint32_t qpos = 0, k = 0, rem = 0;
+			bool mlike = false;
+			for (uint32_t it = 0; ; ++it) {
+				if (it >= T_C1_ITERS) { defer = true; break; }
+				if (rem == 0) {                                                    // next input op
+					if (k == nc) break;
+					uint32_t const packed = __ldg(P.cig + cbase + k);
+					uint32_t const cnt = packed >> 4, op = packed & 0xfu;
+					if (op > OP_X) { flags |= PV3_FLAG_BAD_OP; break; }              // rewrite_cigar.hh:149-151
+					if ((0x72u >> op) & 1u) {                                          // I S H P pass through (:68-77)
+						if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) (RAW_PASS | k);
+						++n_raw;
+						if (op == OP_I || op == OP_S) { qpos += cnt; if (qpos > 0x10000u) qpos = 0x10000u; }
+						++k;
+						continue;
 					}
-					rem -= take;
+					mlike = (op != OP_D && op != OP_N);
+					if (cnt > src_left) { flags |= PV3_FLAG_POS_OOB; break; }
+					src_left -= cnt;
+					rem = cnt; ++k;
+					if (!rem) continue;
 				}
+				uint64_t const wi = col >> 6;
+				uint32_t const b = (uint32_t) col & 63u;
+				if (wi != wcur) { Sinv = ~__ldg(S.words + wi); Dinv = ~__ldg(D.words + wi); wcur = wi; }
+				uint64_t const s = Sinv >> b, d = Dinv >> b;
+				uint32_t const sb = (uint32_t) s & 1u, db = (uint32_t) d & 1u;
+				uint64_t const nr = (s ^ (0ull - (uint64_t) sb)) | (d ^ (0ull - (uint64_t) db));
+				uint32_t len = nr ? ctz64(nr) : 64u;
+				if (len > 64u - b) len = 64u - b;
+				if (sb) { if (len > rem) len = rem; rem -= len; }
+				col += len;
+				bool const isq = sb && mlike;                                       // the run consumes query bases
+				if (db) {
+					uint32_t op = OP_D;                                               // :92-93, :127-137
+					if (isq) {                                                        // compare run (:102-113)
+						op = OP_EQ;
+						if (qpos + len > nq) { flags |= PV3_FLAG_QUERY_OOB; break; }
+						if (e + len > R.n) { flags |= PV3_FLAG_REF_OOB; break; }
+						uint64_t const ra = e - e0a;
+						if (ra > 0xffffu) { defer = true; break; }
+						if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = qpos | ((uint32_t) ra << 8) | (len << 24);
+						++n_piece;
+					}
+					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((len << 4) | op);
+					++n_raw;
+					e += len;
+				} else if (isq) {                                                   // :95-100
+					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((len << 4) | OP_I);
+					++n_raw;
+				}
+				if (isq) { qpos += len; if (qpos > 0x10000u) qpos = 0x10000u; }
 			}
-			em.flush();
-			n_prov = em.n_out;
-			adjacent_id = em.adjacent_id;
-			if (em.overflow) defer = true;
+			if (n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
 		}
+		__syncthreads();        // staged query and target windows are complete
 
-		// ---- phase C2: one flat loop over the provisional ops, 4 bases per step: mismatch bits in query coordinates -----
+		// ---- phase C2: one flat loop over the compare pieces, 8 bases per step: mismatch bits in query coordinates -------
 		bool const work2 = work && !flags && !defer;
 		if (work2) {
 			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q);
 			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
 			uint32_t const qrel = q_lead + (uint32_t) (qoff - tq0);
 			#pragma unroll
-			for (uint32_t w = 0; w < T_MMW; ++w) sm.mm[w][tid] = 0;
-			uint32_t j = 0, remaining = 0, qpos = 0, ra = (uint32_t) (e0 - e0a), acc = 0, wcur = 0;
-			while (j < n_prov || remaining) {
+			for (uint32_t w = 0; w <= T_MMW; ++w) sm.mm[w][tid] = 0;
+			uint32_t j = 0, remaining = 0, qpos = 0, ra = 0;
+			for (;;) {
 				if (!remaining) {
-					uint32_t const v = sm.prov[j][tid]; ++j;
-					uint32_t const op = v & 0xfu, len = v >> 4;
-					if (op == OP_EQ) remaining = len;
-					else if (op == OP_I || op == OP_S) {
-						qpos += len;
-						if (qpos > 32u * T_MMW) qpos = 32u * T_MMW;           // I/S beyond |SEQ| (no compare can follow)
-						uint32_t const wn = qpos >> 5;
-						if (wn != wcur) { if (wcur < T_MMW) sm.mm[wcur][tid] = acc; acc = 0; wcur = wn; }
-					} else if (op == OP_D) ra += len;
-				} else {
-					uint32_t const n = remaining < 4u ? remaining : 4u;
-					uint32_t const rv = (ra + 8u <= T_RWIN) ? load4(rs, ra) : load4_global(R.codes + e0a + ra);   // beyond the staged window: L1
-					uint32_t bits = nonzero_bytes(load4(qs, qrel + qpos) ^ rv) & ((1u << n) - 1u);
-					uint32_t const bit = qpos & 31u;
-					acc |= bits << bit;
-					qpos += n; ra += n; remaining -= n;
-					if (bit + n >= 32u) {
-						sm.mm[wcur][tid] = acc;
-						acc = (bit + n > 32u) ? (bits >> (32u - bit)) : 0u;
-						++wcur;
-					}
+					if (j == n_piece) break;
+					uint32_t const v = sm.piece[j][tid]; ++j;
+					qpos = v & 0xffu; ra = (v >> 8) & 0xffffu; remaining = v >> 24;
 				}
+				uint32_t const n = remaining < 8u ? remaining : 8u;
+				uint32_t qlo, qhi, rlo, rhi;
+				load8(qs, qrel + qpos, qlo, qhi);
+				if (ra + 12u <= T_RWIN) load8(rs, ra, rlo, rhi);
+				else load8_global(R.codes + e0a + ra, rlo, rhi);                    // beyond the staged window: L1
+				uint32_t bits = (nonzero_bytes_hi(qlo ^ rlo) >> 28) | ((nonzero_bytes_hi(qhi ^ rhi) >> 24) & 0xf0u);
+				bits &= (1u << n) - 1u;
+				uint32_t const w = qpos >> 5, b = qpos & 31u;
+				uint64_t const placed = (uint64_t) bits << b;
+				sm.mm[w][tid] |= (uint32_t) placed;
+				sm.mm[w + 1][tid] |= (uint32_t) (placed >> 32);
+				qpos += n; ra += n; remaining -= n;
 			}
-			if (wcur < T_MMW) sm.mm[wcur][tid] = acc;
 		}
 
 		__syncthreads();        // the staged target windows are dead from here on: fin overwrites them
 
-		// ---- phase C3: final ops: provisional '=' runs are split where the mismatch bits say so ---------------------------
+		// ---- phase C3: final ops — one flat loop, one cigar_buffer::push_back (cigar.cc:61-86) site ----------------------
 		if (work2) {
-			TEmitter em; em.init(&sm.fin[0][tid]);
-			uint32_t qpos = 0;
-			for (uint32_t j = 0; j < n_prov; ++j) {
-				uint32_t const v = sm.prov[j][tid];
-				uint32_t const op = v & 0xfu, len = v >> 4;
-				if (op != OP_EQ) { em.push(op, len); if (op == OP_I || op == OP_S) qpos += len; continue; }
-				uint32_t left = len;
-				while (left) {
-					uint32_t const bit = qpos & 31u;
-					uint32_t const n = (32u - bit < left) ? (32u - bit) : left;
-					uint32_t m = (sm.mm[qpos >> 5][tid] >> bit) & ((n == 32u) ? ~0u : ((1u << n) - 1u));
-					if (!m) em.push(OP_EQ, n);
-					else {
-						uint32_t pos = 0;
-						while (pos < n) {
-							uint32_t const rest = m >> pos;
-							uint32_t l;
-							if (rest & 1u) { uint32_t const inv = ~rest; l = inv ? (uint32_t) (__ffs((int) inv) - 1) : 32u; if (l > n - pos) l = n - pos; em.push(OP_X, l); }
-							else { l = rest ? (uint32_t) (__ffs((int) rest) - 1) : 32u; if (l > n - pos) l = n - pos; em.push(OP_EQ, l); }
-							pos += l;
-						}
+			uint32_t j = 0, left = 0, qpos = 0, carry_op = OP_NONE, carry_cnt = 0;
+			bool adjacent_id = false;
+			for (;;) {
+				uint32_t op = OP_NONE, len = 0;
+				if (!left) {
+					if (j == n_raw) break;
+					uint32_t const v = sm.raw[j][tid]; ++j;
+					if (v & RAW_PASS) {
+						uint32_t const packed = __ldg(P.cig + cbase + (v & 0x7fffu));
+						op = packed & 0xfu; len = packed >> 4;
+						if (op == OP_I || op == OP_S) { qpos += len; if (qpos > 32u * T_MMW) qpos = 32u * T_MMW; }   // beyond |SEQ|: no compare can follow
+					} else {
+						op = v & 0xfu; len = v >> 4;
+						if (op == OP_EQ) left = len;
+						else if (op == OP_I) qpos += len;
 					}
-					qpos += n; left -= n;
+				}
+				if (left) {                                                         // split the compare run at the next change
+					uint32_t const w = qpos >> 5, b = qpos & 31u;
+					uint32_t const m0 = sm.mm[w][tid], m1 = sm.mm[w + 1][tid], m2 = (w + 2 <= T_MMW) ? sm.mm[w + 2][tid] : 0u;
+					uint32_t const lo = __funnelshift_r(m0, m1, b), hi = __funnelshift_r(m1, m2, b);
+					uint32_t const first = lo & 1u;
+					uint32_t const xlo = lo ^ (0u - first), xhi = hi ^ (0u - first);
+					uint32_t l = xlo ? (uint32_t) (__ffs((int) xlo) - 1) : (xhi ? 32u + (uint32_t) (__ffs((int) xhi) - 1) : 64u);
+					if (l > left) l = left;
+					op = first ? OP_X : OP_EQ; len = l;
+					left -= l; qpos += l;
+				}
+				if (len) {
+					if (carry_op == op) carry_cnt += len;
+					else {
+						if ((carry_op | op) == 3u) adjacent_id = true;                 // I next to D (N is never produced)
+						if (carry_op != OP_NONE) {
+							if (n_ops < (uint32_t) T_OUTQ) sm.fin[n_ops][tid] = (carry_cnt << 4) | carry_op;
+							++n_ops;
+						}
+						carry_op = op; carry_cnt = len;
+					}
 				}
 			}
-			em.flush();
-			n_ops = em.n_out;
-			if (em.overflow) defer = true;
+			if (carry_op != OP_NONE) {                                              // cigar_buffer::finish (cigar.cc:89-95)
+				if (n_ops < (uint32_t) T_OUTQ) sm.fin[n_ops][tid] = (carry_cnt << 4) | carry_op;
+				++n_ops;
+			}
+			if (n_ops > (uint32_t) T_OUTQ) defer = true;
 			if (!defer && P.stage == 0) {
 				if (n_ops == 0) flags |= PV3_FLAG_EMPTY_CIGAR;                                   // cigar.cc:16-18 UB
 				else if (adjacent_id) {
@@ -365,7 +363,7 @@ void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
 	}
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 	if (!n_tiles) return;
-	uint64_t blocks = (uint64_t) n_sms * 3;       // 3 CTAs of 75 KB shared memory per SM
+	uint64_t blocks = (uint64_t) n_sms * 3;       // 3 CTAs of 71 KB shared memory per SM
 	if (blocks > n_tiles) blocks = n_tiles;
 	k1_thread_kernel<<<(unsigned) blocks, TT, sizeof(TileSmem), stream>>>(P);
 }
