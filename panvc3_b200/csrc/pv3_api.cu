@@ -239,7 +239,7 @@ int pv3_index_commit(pv3_ctx *ctx)
 	std::vector <size_t> code_off(ctx->refs.size());
 	for (size_t r = 0; r < ctx->refs.size(); ++r) {
 		ref_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 512, 256);
-		code_off[r] = total; total = align_up(total + ctx->refs[r].bases.size() + 512, 256);
+		code_off[r] = total; total = align_up(total + (ctx->refs[r].bases.size() + 1) / 2 + 512, 256);
 	}
 	if (!total) total = 256;
 
@@ -267,18 +267,19 @@ int pv3_index_commit(pv3_ctx *ctx)
 	for (size_t r = 0; r < ctx->refs.size(); ++r) {
 		auto const &bases = ctx->refs[r].bases;
 		memcpy(host.data() + ref_off[r], bases.data(), bases.size());
-		uint8_t *codes = host.data() + code_off[r];
+		uint8_t *codes4 = host.data() + code_off[r];
 		for (size_t i = 0; i < bases.size(); ++i) {
 			uint8_t c;
 			switch (bases[i]) {   // dna5::assign_char (dna5.hpp:99-110); exact = byte equals dna5::to_char(rank)
 				case 'A': c = 0; break; case 'C': c = 1; break; case 'G': c = 2; break; case 'N': c = 3; break; case 'T': c = 4; break;
-				case 'a': c = 0x80; break; case 'c': c = 0x81; break; case 'g': c = 0x82; break;
-				case 't': case 'U': case 'u': c = 0x84; break;
-				default: c = 0x83; break;
+				case 'a': c = 8; break; case 'c': c = 9; break; case 'g': c = 10; break;
+				case 't': case 'U': case 'u': c = 12; break;
+				default: c = 11; break;
 			}
-			codes[i] = c;
+			if (i & 1) codes4[i >> 1] |= (uint8_t) (c << 4); else codes4[i >> 1] = c;
 		}
-		memset(codes + bases.size(), 0xff, 512);
+		if (bases.size() & 1) codes4[bases.size() >> 1] |= 0xf0;
+		memset(codes4 + (bases.size() + 1) / 2, 0xff, 512);
 	}
 
 	PV3_CUDA(ctx, ctx->index_mem.ensure(total));
@@ -299,7 +300,7 @@ int pv3_index_commit(pv3_ctx *ctx)
 	std::vector <RefDesc> fd(ctx->refs.size() ? ctx->refs.size() : 1);
 	for (size_t r = 0; r < ctx->refs.size(); ++r) {
 		fd[r].bases = (const char *) (ctx->index_mem.as <uint8_t>() + ref_off[r]);
-		fd[r].codes = ctx->index_mem.as <uint8_t>() + code_off[r];
+		fd[r].codes4 = ctx->index_mem.as <uint8_t>() + code_off[r];
 		fd[r].n = ctx->refs[r].bases.size();
 	}
 	PV3_CUDA(ctx, ctx->row_desc.ensure(rd.size() * sizeof(RowDesc)));

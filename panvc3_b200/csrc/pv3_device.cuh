@@ -34,8 +34,9 @@ struct RowDesc {
 
 struct RefDesc {
 	const char    *bases;   // raw FASTA bytes (rewrite compares raw bytes)
-	const uint8_t *codes;   // per base: dna5 rank of assign_char(byte) in bits 0-2 | 0x80 unless byte is exactly one of "ACGNT";
-	                        // (query rank == code) ⇔ (dna5::to_char(query) == byte). 512 readable pad bytes follow.
+	const uint8_t *codes4;  // two bases per byte (even base in the low nibble): dna5 rank of assign_char(byte) in bits 0-2 | 8 unless the
+	                        // byte is exactly one of "ACGNT"; (query rank == nibble) ⇔ (dna5::to_char(query) == byte). 512 readable
+	                        // pad bytes (0xff) follow.
 	uint64_t       n;
 };
 

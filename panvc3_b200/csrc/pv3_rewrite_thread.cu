@@ -15,14 +15,19 @@
 //       query coordinates
 //   C3  one iteration per output run: raw runs, '=' runs split by the mismatch bits, one cigar_buffer::push_back site
 //
+// v5: query ranks and target codes are staged as 4-bit nibbles (the query is packed while it is staged; the index holds
+// the target codes packed, RefDesc::codes4), so that one compare step covers 16 bases and the tile needs half the shared
+// memory (4 CTAs per SM instead of 3); the column walk runs on 32-bit window-relative coordinates with soft exits.
+//
 // Tile pipeline (128 threads = 128 consecutive records):
 //   A  each thread: ids, src_pos, select0/rank0 of its record → c0, e0
-//   B  cooperative, coalesced staging into shared memory: the tile's query bytes (contiguous in the batch), and per record
-//      a 208-byte window of target codes at e0
+//   B  cooperative, coalesced staging into shared memory: the tile's query bytes (contiguous in the batch) packed to
+//      nibbles, and per record a 224-base window of packed target codes at e0
 //   C1..C3 as above; run detection on the final ops (only when an I abuts a D)
 //   D  block scan of op counts → one atomic on the arena cursor → ops and per-record results written
-// Records that do not fit the fixed quotas (long reads, too many runs, windows beyond the staged data, malformed index)
-// are appended to a deferred list and handled by the warp-per-record kernel afterwards — results are bit-identical.
+// Records that do not fit the fixed quotas (long reads, too many runs, windows beyond the staged data, malformed index,
+// query ranks above 7) are appended to a deferred list and handled by the warp-per-record kernel afterwards — results
+// are bit-identical.
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
 #include "pv3_runs.cuh"
@@ -33,51 +38,69 @@ constexpr int      TT        = 128;            // threads per CTA = records per 
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
 constexpr int      T_RAWQ    = 40;             // raw runs per record (column runs + pass-through ops)
 constexpr int      T_PIECEQ  = 16;             // compare pieces per record
-constexpr uint32_t T_QSTAGE  = TT * 168;       // bytes of query staged per tile
-constexpr uint32_t T_RWIN    = 208;            // bytes of target codes staged per record (13 x 16)
+constexpr uint32_t T_QSTAGE  = TT * 168;       // query bases staged per tile
+constexpr uint32_t T_RWIN    = 224;            // target bases staged per record (7 x 16 bytes of nibbles)
+constexpr uint32_t T_RCH     = T_RWIN / 32;    // 16-byte chunks per staged target window
 constexpr uint32_t T_MMW     = 6;              // mismatch bit words per record (query coordinates): reads up to 192 bases
 constexpr uint32_t T_C1_ITERS = 192;           // bound of the column walk (long gaps / deletions go to the warp kernel)
 constexpr uint32_t RAW_PASS  = 0x8000u;        // raw entry refers to input op (entry & 0x7fff)
+constexpr uint32_t ERR_DEFER = 0x80000000u;
 
-// 71 KB ⇒ 3 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
+// 48 KB ⇒ 4 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
 struct TileSmem {
 	uint16_t raw[T_RAWQ][TT];
 	uint32_t piece[T_PIECEQ][TT];              // qpos | (target offset from the staged window start) << 8 | len << 24
 	uint32_t mm[T_MMW + 1][TT];
-	uint4    q[T_QSTAGE / 16 + 2];
+	uint2    q4[T_QSTAGE / 16 + 2];            // packed query: 16 bases per element
 	union {
-		uint4    ref[TT][T_RWIN / 16];         // [record][staged target codes]
+		uint4    ref[TT][T_RCH];               // [record][staged packed target codes]
 		uint32_t fin[T_OUTQ][TT];              // final ops
 	};
 	const uint8_t  *ref_ptr[TT];               // staging sources published by phase A
 	uint32_t scan[TT / 32];
 	unsigned long long base;
 };
-static_assert(sizeof(uint4) * (T_RWIN / 16) * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in ref");
+static_assert(sizeof(uint4) * T_RCH * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in ref");
 
 __device__ __forceinline__ uint32_t ctz64(uint64_t x) { return (uint32_t) __ffsll((long long) x) - 1u; }   // x != 0
 
-// bits 28..31 set ⇔ bytes 0..3 of t are non-zero (SWAR; no per-byte branches); callers shift
-__device__ __forceinline__ uint32_t nonzero_bytes_hi(uint32_t t)
+// 8 nibbles of t → 8 bits (bit i set ⇔ nibble i non-zero), returned in bits 24..31
+__device__ __forceinline__ uint32_t nonzero_nibbles_hi(uint32_t t)
 {
-	uint32_t const nz = (((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;
-	return nz * 0x00204081u;
+	uint32_t const nz = (((t & 0x77777777u) + 0x77777777u) | t) & 0x88888888u;     // bit 4i+3
+	uint32_t const y = nz >> 3;                                                      // bit 4i
+	uint32_t const y1 = (y | (y >> 3)) & 0x03030303u;                               // bits 8j, 8j+1
+	return y1 * 0x01041040u;                                                         // byte j → bits 24+2j, 25+2j (no carries)
 }
 
-// 8 bytes at byte offset a of a word array in shared memory (reads 3 words)
-__device__ __forceinline__ void load8(const uint32_t *base, uint32_t a, uint32_t &lo, uint32_t &hi)
+// 16 nibbles at nibble offset a of a word array in shared memory (reads 3 words)
+__device__ __forceinline__ void load16n(const uint32_t *base, uint32_t a, uint32_t &lo, uint32_t &hi)
 {
-	const uint32_t *p = base + (a >> 2);
-	uint32_t const sh = (a & 3u) * 8u;
+	const uint32_t *p = base + (a >> 3);
+	uint32_t const sh = (a & 7u) * 4u;
 	uint32_t const w0 = p[0], w1 = p[1], w2 = p[2];
 	lo = __funnelshift_r(w0, w1, sh);
 	hi = __funnelshift_r(w1, w2, sh);
 }
 
-__device__ __noinline__ void load8_global(const uint8_t *p, uint32_t &lo, uint32_t &hi)   // codes have 512 readable pad bytes
+// the same from the packed codes in global memory (512 readable pad bytes); rare: windows beyond the staged data
+__device__ __noinline__ uint2 load16n_global(const uint8_t *codes4, uint64_t nib)
 {
-	lo = (uint32_t) __ldg(p) | ((uint32_t) __ldg(p + 1) << 8) | ((uint32_t) __ldg(p + 2) << 16) | ((uint32_t) __ldg(p + 3) << 24);
-	hi = (uint32_t) __ldg(p + 4) | ((uint32_t) __ldg(p + 5) << 8) | ((uint32_t) __ldg(p + 6) << 16) | ((uint32_t) __ldg(p + 7) << 24);
+	const uint8_t *p = codes4 + (nib >> 1);
+	uint64_t v = 0;
+	#pragma unroll
+	for (int i = 0; i < 8; ++i) v |= (uint64_t) __ldg(p + i) << (8 * i);
+	if (nib & 1u) v = (v >> 4) | ((uint64_t) __ldg(p + 8) << 60);
+	return make_uint2((uint32_t) v, (uint32_t) (v >> 32));
+}
+
+// 16 query ranks (one per byte) → 16 nibbles; `bad` collects bits 3..7 of every byte (ranks the nibble compare cannot hold)
+__device__ __forceinline__ uint2 pack16(uint4 v, uint32_t &bad)
+{
+	bad |= (v.x | v.y | v.z | v.w) & 0xf8f8f8f8u;
+	uint32_t const a = (v.x | (v.x >> 4)) & 0x00ff00ffu, b = (v.y | (v.y >> 4)) & 0x00ff00ffu;
+	uint32_t const c = (v.z | (v.z >> 4)) & 0x00ff00ffu, d = (v.w | (v.w >> 4)) & 0x00ff00ffu;
+	return make_uint2(__byte_perm(a, b, 0x6420), __byte_perm(c, d, 0x6420));
 }
 
 __global__ void __launch_bounds__(TT)
@@ -99,11 +122,19 @@ k1_thread_kernel(K1Params P)
 		uint64_t const q_addr = (uint64_t) (uintptr_t) P.seq + tq0;
 		uint64_t const q_addr16 = q_addr & ~15ull;
 		uint32_t const q_lead = (uint32_t) (q_addr - q_addr16);
-		bool const tile_staged = (tq1 - tq0 + q_lead) <= (uint64_t) T_QSTAGE;
+		bool const tile_fits = (tq1 - tq0 + q_lead) <= (uint64_t) T_QSTAGE;
+
+		// ---- phase B1: the tile's query, packed to nibbles while it is staged (issued first: the loads overlap phase A) ----
+		uint32_t bad_rank = 0;
+		if (tile_fits) {
+			uint32_t const n16 = (uint32_t) ((tq1 - tq0 + q_lead + 15) / 16);
+			const uint4 *g = reinterpret_cast <const uint4 *>((uintptr_t) q_addr16);
+			for (uint32_t i = tid; i < n16; i += TT) sm.q4[i] = pack16(__ldg(g + i), bad_rank);
+		}
 
 		// ---- phase A: per-record projection of the start position ------------------------------------------------
 		uint32_t flags = 0;
-		bool defer = !tile_staged;
+		bool defer = !tile_fits;
 		RowDesc S = {}, D = {};
 		RefDesc R = {};
 		uint64_t c0 = 0, e0 = 0, spos = 0, qoff = 0, nq = 0, cbase = 0;
@@ -126,95 +157,92 @@ k1_thread_kernel(K1Params P)
 				c0 = (spos < S.n_zeros) ? select0_thread(S, spos + 1) : S.n_bits;     // rewrite_cigar.hh:51
 				e0 = rank0_thread(D, c0);                                              // :52
 				if (S.n_bits != D.n_bits || e0 > R.n || nq > 32u * T_MMW || nc >= RAW_PASS) defer = true;   // unusual: the general kernel guards it
-				if (!defer) {
-					sm.ref_ptr[tid] = R.codes + (e0 & ~15ull);
-				}
+				if (!defer) sm.ref_ptr[tid] = R.codes4 + ((e0 & ~31ull) >> 1);
 			}
 		}
-		__syncthreads();
+		// a query rank above 7 anywhere in the tile: the nibble compare cannot represent it, the general kernel takes the tile
+		if (__syncthreads_or((int) bad_rank)) defer = true;
 
-		// ---- phase B: cooperative staging -------------------------------------------------------------------------
-		if (tile_staged) {
-			uint32_t const n16 = (uint32_t) ((tq1 - tq0 + q_lead + 15) / 16);
-			const uint4 *g = reinterpret_cast <const uint4 *>((uintptr_t) q_addr16);
-			for (uint32_t i = tid; i < n16; i += TT) sm.q[i] = __ldg(g + i);
-		}
-		for (uint32_t r = warp * 32 + (lane >> 4); r < warp * 32 + 32; r += 2) {       // half-warp per record
+		// ---- phase B2: per record a window of packed target codes (8 lanes per record, 16 bytes per lane) --------------
+		for (uint32_t r = warp * 32 + (lane >> 3); r < warp * 32 + 32; r += 4) {
 			const uint8_t *rp = sm.ref_ptr[r];
-			uint32_t const l16 = lane & 15u;
-			if (rp && l16 < T_RWIN / 16) sm.ref[r][l16] = __ldg(reinterpret_cast <const uint4 *>(rp) + l16);
+			uint32_t const l8 = lane & 7u;
+			if (rp && l8 < T_RCH) sm.ref[r][l8] = __ldg(reinterpret_cast <const uint4 *>(rp) + l8);
 		}
 
 		// ---- phase C1: one flat walk over the column runs of the record's span -------------------------------------
-		// Output: raw runs ('=' stands for a compare run of unknown content) and the compare pieces.
+		// Output: raw runs ('=' stands for a compare run of unknown content) and the compare pieces. Coordinates are
+		// 32-bit: columns relative to the word of c0, target offsets relative to the staged window. Errors do not leave
+		// the loop through a branch: they end the op list (`k = nc, rem = 0`), so every lane runs the same straight body.
 		uint32_t n_raw = 0, n_piece = 0, n_ops = 0, n_runs = 0;
 		unsigned long long job_base = 0;
-		uint64_t const e0a = e0 & ~15ull;
+		uint64_t const e0a = e0 & ~31ull;
 		bool const work = active && !flags && !defer;
 		if (work) {
-			uint64_t col = c0, e = e0, wcur = ~0ull, Sinv = 0, Dinv = 0;
-			uint64_t src_left = (spos < S.n_zeros) ? (S.n_zeros - spos) : 0;
-			uint32_t qpos = 0, k = 0, rem = 0;
+			const uint64_t *Sp = S.words + (c0 >> 6), *Dp = D.words + (c0 >> 6);
+			uint64_t const r_room = R.n - e0a;                                   // e0 <= R.n
+			uint32_t const r_lim = r_room > 0x10000ull ? 0x10000u : (uint32_t) r_room, nq32 = (uint32_t) nq;
+			uint64_t const left64 = (spos < S.n_zeros) ? (S.n_zeros - spos) : 0;
+			uint32_t src_left = left64 > 0xffffffffull ? 0xffffffffu : (uint32_t) left64;   // op counts are < 2^28
+			uint32_t crel = (uint32_t) c0 & 63u, ra = (uint32_t) (e0 - e0a), qpos = 0, k = 0, rem = 0, err = 0, wcur = ~0u;
+			uint64_t Sinv = 0, Dinv = 0;
 			bool mlike = false;
 			for (uint32_t it = 0; ; ++it) {
-				if (it >= T_C1_ITERS) { defer = true; break; }
+				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
 				if (rem == 0) {                                                    // next input op
 					if (k == nc) break;
 					uint32_t const packed = __ldg(P.cig + cbase + k);
 					uint32_t const cnt = packed >> 4, op = packed & 0xfu;
-					if (op > OP_X) { flags |= PV3_FLAG_BAD_OP; break; }              // rewrite_cigar.hh:149-151
+					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; continue; }       // rewrite_cigar.hh:149-151
 					if ((0x72u >> op) & 1u) {                                          // I S H P pass through (:68-77)
 						if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) (RAW_PASS | k);
 						++n_raw;
-						if (op == OP_I || op == OP_S) { qpos += cnt; if (qpos > 0x10000u) qpos = 0x10000u; }
+						if (op == OP_I || op == OP_S) qpos = min(qpos + cnt, 0x10000u);
 						++k;
 						continue;
 					}
 					mlike = (op != OP_D && op != OP_N);
-					if (cnt > src_left) { flags |= PV3_FLAG_POS_OOB; break; }
+					if (cnt > src_left) { err = PV3_FLAG_POS_OOB; k = nc; continue; }
 					src_left -= cnt;
 					rem = cnt; ++k;
 					if (!rem) continue;
 				}
-				uint64_t const wi = col >> 6;
-				uint32_t const b = (uint32_t) col & 63u;
-				if (wi != wcur) { Sinv = ~__ldg(S.words + wi); Dinv = ~__ldg(D.words + wi); wcur = wi; }
+				uint32_t const wi = crel >> 6, b = crel & 63u;
+				if (wi != wcur) { Sinv = ~__ldg(Sp + wi); Dinv = ~__ldg(Dp + wi); wcur = wi; }
 				uint64_t const s = Sinv >> b, d = Dinv >> b;
 				uint32_t const sb = (uint32_t) s & 1u, db = (uint32_t) d & 1u;
 				uint64_t const nr = (s ^ (0ull - (uint64_t) sb)) | (d ^ (0ull - (uint64_t) db));
 				uint32_t len = nr ? ctz64(nr) : 64u;
-				if (len > 64u - b) len = 64u - b;
-				if (sb) { if (len > rem) len = rem; rem -= len; }
-				col += len;
+				len = min(len, 64u - b);
+				if (sb) { len = min(len, rem); rem -= len; }
+				crel += len;
 				bool const isq = sb && mlike;                                       // the run consumes query bases
-				if (db) {
-					uint32_t op = OP_D;                                               // :92-93, :127-137
-					if (isq) {                                                        // compare run (:102-113)
-						op = OP_EQ;
-						if (qpos + len > nq) { flags |= PV3_FLAG_QUERY_OOB; break; }
-						if (e + len > R.n) { flags |= PV3_FLAG_REF_OOB; break; }
-						uint64_t const ra = e - e0a;
-						if (ra > 0xffffu) { defer = true; break; }
-						if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = qpos | ((uint32_t) ra << 8) | (len << 24);
-						++n_piece;
-					}
+				bool const cmp = isq && db;                                         // compare run (:102-113)
+				if (cmp) {
+					uint32_t e1 = 0;
+					if (qpos + len > nq32) e1 = PV3_FLAG_QUERY_OOB;
+					else if (ra + len > r_lim) e1 = (r_room > 0x10000ull) ? ERR_DEFER : PV3_FLAG_REF_OOB;
+					if (e1) { err = e1; k = nc; rem = 0; continue; }
+					if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = qpos | (ra << 8) | (len << 24);
+					++n_piece;
+				}
+				uint32_t const op = db ? (isq ? OP_EQ : OP_D) : OP_I;             // :92-100, :127-137
+				if (db || isq) {
 					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((len << 4) | op);
 					++n_raw;
-					e += len;
-				} else if (isq) {                                                   // :95-100
-					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((len << 4) | OP_I);
-					++n_raw;
 				}
-				if (isq) { qpos += len; if (qpos > 0x10000u) qpos = 0x10000u; }
+				if (isq) qpos = min(qpos + len, 0x10000u);
+				if (db) ra = min(ra + len, 0x20000u);
 			}
-			if (n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
+			if (err == ERR_DEFER || n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
+			else flags |= err;
 		}
 		__syncthreads();        // staged query and target windows are complete
 
-		// ---- phase C2: one flat loop over the compare pieces, 8 bases per step: mismatch bits in query coordinates -------
+		// ---- phase C2: one flat loop over the compare pieces, 16 bases per step: mismatch bits in query coordinates ------
 		bool const work2 = work && !flags && !defer;
 		if (work2) {
-			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q);
+			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q4);
 			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
 			uint32_t const qrel = q_lead + (uint32_t) (qoff - tq0);
 			#pragma unroll
@@ -226,12 +254,12 @@ k1_thread_kernel(K1Params P)
 					uint32_t const v = sm.piece[j][tid]; ++j;
 					qpos = v & 0xffu; ra = (v >> 8) & 0xffffu; remaining = v >> 24;
 				}
-				uint32_t const n = remaining < 8u ? remaining : 8u;
+				uint32_t const n = min(remaining, 16u);
 				uint32_t qlo, qhi, rlo, rhi;
-				load8(qs, qrel + qpos, qlo, qhi);
-				if (ra + 12u <= T_RWIN) load8(rs, ra, rlo, rhi);
-				else load8_global(R.codes + e0a + ra, rlo, rhi);                    // beyond the staged window: L1
-				uint32_t bits = (nonzero_bytes_hi(qlo ^ rlo) >> 28) | ((nonzero_bytes_hi(qhi ^ rhi) >> 24) & 0xf0u);
+				load16n(qs, qrel + qpos, qlo, qhi);
+				if (ra + 24u <= T_RWIN) load16n(rs, ra, rlo, rhi);
+				else { uint2 const g = load16n_global(R.codes4, e0a + ra); rlo = g.x; rhi = g.y; }   // beyond the staged window
+				uint32_t bits = (nonzero_nibbles_hi(qlo ^ rlo) >> 24) | ((nonzero_nibbles_hi(qhi ^ rhi) >> 16) & 0xff00u);
 				bits &= (1u << n) - 1u;
 				uint32_t const w = qpos >> 5, b = qpos & 31u;
 				uint64_t const placed = (uint64_t) bits << b;
@@ -255,7 +283,7 @@ k1_thread_kernel(K1Params P)
 					if (v & RAW_PASS) {
 						uint32_t const packed = __ldg(P.cig + cbase + (v & 0x7fffu));
 						op = packed & 0xfu; len = packed >> 4;
-						if (op == OP_I || op == OP_S) { qpos += len; if (qpos > 32u * T_MMW) qpos = 32u * T_MMW; }   // beyond |SEQ|: no compare can follow
+						if (op == OP_I || op == OP_S) qpos = min(qpos + len, 32u * T_MMW);   // beyond |SEQ|: no compare can follow
 					} else {
 						op = v & 0xfu; len = v >> 4;
 						if (op == OP_EQ) left = len;
@@ -269,7 +297,7 @@ k1_thread_kernel(K1Params P)
 					uint32_t const first = lo & 1u;
 					uint32_t const xlo = lo ^ (0u - first), xhi = hi ^ (0u - first);
 					uint32_t l = xlo ? (uint32_t) (__ffs((int) xlo) - 1) : (xhi ? 32u + (uint32_t) (__ffs((int) xhi) - 1) : 64u);
-					if (l > left) l = left;
+					l = min(l, left);
 					op = first ? OP_X : OP_EQ; len = l;
 					left -= l; qpos += l;
 				}
@@ -363,7 +391,7 @@ void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
 	}
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 	if (!n_tiles) return;
-	uint64_t blocks = (uint64_t) n_sms * 3;       // 3 CTAs of 71 KB shared memory per SM
+	uint64_t blocks = (uint64_t) n_sms * 4;       // 4 CTAs of 48 KB shared memory per SM
 	if (blocks > n_tiles) blocks = n_tiles;
 	k1_thread_kernel<<<(unsigned) blocks, TT, sizeof(TileSmem), stream>>>(P);
 }
