@@ -75,6 +75,7 @@ struct pv3_ctx {
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
 	int          stage = 0;
+	bool         many_deferred = false;      // last batch: more than 1/16 of the records went to the warp-per-record kernel
 	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
 
 	// device work buffers
@@ -413,19 +414,31 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], stream));
 		ctx->timing.launches += 1;
-		st = fetch_counters(ctx, stream);
-		if (st) return st;
-		if (ctx->h_counters->n_deferred && !ctx->h_counters->overflow) {
+		if (ctx->many_deferred) {
+			// the previous batch deferred a large share (long reads): read the count and size the general kernel for it
+			st = fetch_counters(ctx, stream);
+			if (st) return st;
+			if (ctx->h_counters->n_deferred && !ctx->h_counters->overflow) {
+				K1Params P2 = P;
+				P2.rec_list = ctx->deferred.as <uint64_t>();
+				P2.n_list = ctx->h_counters->n_deferred;
+				launch_k1(P2, ctx->n_sms, stream);
+				PV3_CUDA(ctx, cudaGetLastError());
+				ctx->timing.launches += 1;
+			}
+		} else {
+			// usual case, a handful of deferred records: the general kernel reads the count on the device (no host round trip)
 			K1Params P2 = P;
 			P2.rec_list = ctx->deferred.as <uint64_t>();
-			P2.n_list = ctx->h_counters->n_deferred;
+			P2.n_list_dev = &ctx->counters.as <Counters>()->n_deferred;
 			launch_k1(P2, ctx->n_sms, stream);
 			PV3_CUDA(ctx, cudaGetLastError());
 			ctx->timing.launches += 1;
-			PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
-			st = fetch_counters(ctx, stream);
-			if (st) return st;
-		} else PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
+		}
+		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[1], stream));
+		st = fetch_counters(ctx, stream);
+		if (st) return st;
+		ctx->many_deferred = ctx->h_counters->n_deferred * 16 > in->n;
 	} else {
 		launch_k1(P, ctx->n_sms, stream);
 		PV3_CUDA(ctx, cudaGetLastError());

@@ -35,6 +35,7 @@ struct K1Params {
 	int             stage;       // 0 = full pipeline, 1 = rewrite only (parity probe of rewrite_cigar())
 	const uint64_t *rec_list;    // warp kernel: process records rec_list[0..n_list) instead of 0..n (null ⇒ all)
 	uint64_t        n_list;
+	const unsigned long long *n_list_dev;   // warp kernel: when set, the list length is read on the device (no host round trip)
 	uint64_t       *deferred;    // thread kernel: records it could not handle (capacity n)
 	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
 	uint64_t        rr_base;     // added to every stored rr_off

@@ -327,7 +327,7 @@ k1_rewrite_kernel(K1Params P, int group)
 	unsigned const lane = lane_id();
 	unsigned const warp_in_block = threadIdx.x >> 5;
 	uint32_t *stage = stage_all[warp_in_block];
-	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
+	uint64_t const n_items = P.n_list_dev ? (uint64_t) *P.n_list_dev : (P.rec_list ? P.n_list : P.n);
 	uint64_t const n_groups = (n_items + group - 1) / group;
 	uint64_t const warp_global = (uint64_t) blockIdx.x * K1_WARPS + warp_in_block;
 	uint64_t const n_warps = (uint64_t) gridDim.x * K1_WARPS;
@@ -375,6 +375,11 @@ k1_rewrite_kernel(K1Params P, int group)
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)
 {
+	if (P.n_list_dev) {
+		// deferred list of the thread kernel, length known only on the device: a small grid-stride launch, one record per warp
+		k1_rewrite_kernel<<<(unsigned) n_sms * 2, K1_WARPS * 32, 0, stream>>>(P, 1);
+		return;
+	}
 	uint64_t const n_items = P.rec_list ? P.n_list : P.n;
 	// few records (the deferred list of the thread kernel): one record per warp so that they spread over the SMs
 	int const group = (n_items < (uint64_t) n_sms * 8 * K1_WARPS * GROUP) ? 1 : GROUP;
