@@ -272,6 +272,8 @@ k1_thread_kernel(K1Params P)
 		__syncthreads();        // the staged target windows are dead from here on: fin overwrites them
 
 		// ---- phase C3: final ops — one flat loop, one cigar_buffer::push_back (cigar.cc:61-86) site ----------------------
+		unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
+		bool affine = false;
 		if (work2) {
 			uint32_t j = 0, left = 0, qpos = 0, carry_op = OP_NONE, carry_cnt = 0;
 			bool adjacent_id = false;
@@ -323,22 +325,42 @@ k1_thread_kernel(K1Params P)
 				else if (adjacent_id) {
 					bool has_qual = false;
 					if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);
-					bool const affine = has_qual || P.gap_open != 0;
-					unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
+					affine = has_qual || P.gap_open != 0;
 					n_runs = scan_runs <false>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, nullptr, nullptr, flags, cells, path, pool, max_pool, affine, false);
-					if (!flags && n_runs) {
-						job_base = atomicAdd(&P.counters->job_cursor, (unsigned long long) n_runs);
-						atomicAdd(&P.counters->n_realigned, 1ull);
-						atomicAdd(&P.counters->dp_cells, cells);
-						atomicAdd(&P.counters->dp_path, path);
-						atomicAdd(&P.counters->dp_pool, pool);
-						atomicMax(&P.counters->dp_max_pool, max_pool);
-						if (job_base + n_runs > P.rr_cap) atomicOr(&P.counters->overflow, 2u);
-						else {
-							uint32_t f = 0; unsigned long long a = 0, b = 0, c = 0, d = 0;
-							scan_runs <true>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, true);
-						}
-					} else n_runs = 0;
+					if (flags) n_runs = 0;
+				}
+			}
+		}
+		// Runs found: one set of atomics per WARP (per-record atomics on six shared counters serialise in L2 when most
+		// records realign), then each record writes its jobs and reported ranges behind the warp's base.
+		if (__any_sync(FULL, n_runs != 0)) {
+			uint32_t incl = n_runs;
+			unsigned long long w_cells = n_runs ? cells : 0, w_path = n_runs ? path : 0, w_pool = n_runs ? pool : 0, w_max = n_runs ? max_pool : 0;
+			uint32_t const w_recs = __popc(__ballot_sync(FULL, n_runs != 0));
+			#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { uint32_t const t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
+			#pragma unroll
+			for (int d = 16; d >= 1; d >>= 1) {
+				w_cells += shfl_u64(w_cells, (int) (lane ^ d)); w_path += shfl_u64(w_path, (int) (lane ^ d)); w_pool += shfl_u64(w_pool, (int) (lane ^ d));
+				unsigned long long const o = shfl_u64(w_max, (int) (lane ^ d)); if (o > w_max) w_max = o;
+			}
+			uint32_t const w_runs = __shfl_sync(FULL, incl, 31);
+			unsigned long long wbase = 0;
+			if (lane == 0) {
+				wbase = atomicAdd(&P.counters->job_cursor, (unsigned long long) w_runs);
+				atomicAdd(&P.counters->n_realigned, (unsigned long long) w_recs);
+				atomicAdd(&P.counters->dp_cells, w_cells);
+				atomicAdd(&P.counters->dp_path, w_path);
+				atomicAdd(&P.counters->dp_pool, w_pool);
+				atomicMax(&P.counters->dp_max_pool, w_max);
+				if (wbase + w_runs > P.rr_cap) atomicOr(&P.counters->overflow, 2u);
+			}
+			wbase = shfl_u64(wbase, 0);
+			if (n_runs) {
+				job_base = wbase + (incl - n_runs);
+				if (wbase + w_runs <= P.rr_cap) {
+					uint32_t f = 0; unsigned long long a = 0, b = 0, c = 0, d = 0;
+					scan_runs <true>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, true);
 				}
 			}
 		}
