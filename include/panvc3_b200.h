@@ -144,6 +144,10 @@ int pv3_index_query(pv3_ctx *, int op, uint64_t n, const uint32_t *row, const ui
 /* Parity probe: stage 1 stops after rewrite_cigar() (include/panvc3/rewrite_cigar.hh:19) — no run detection, no
  * realignment; stage 0 (default) is the full project_alignment. */
 int pv3_set_stage(pv3_ctx *, int stage);
+/* Parity probe: indel runs with small windows are realigned one thread per run once a batch holds at least `n` of them
+ * (default 16384), otherwise one warp per run like the large windows; 0 sends every small run to the thread-per-run kernel.
+ * Results are identical. */
+int pv3_set_dp_thread_min(pv3_ctx *, uint64_t n);
 /* Parity probe: 0 (default) = thread-per-record rewrite kernel, records beyond its quotas go to the warp-per-record
  * kernel; 1 = warp-per-record kernel for every record. Results are identical. */
 int pv3_set_kernel_path(pv3_ctx *, int path);

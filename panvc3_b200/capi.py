@@ -19,7 +19,7 @@ PV3_OK, PV3_ERR_INVALID, PV3_ERR_CUDA, PV3_ERR_CAPACITY, PV3_ERR_STATE = 0, -1, 
 EXPORTED_SYMBOLS = [
     "pv3_abi_version", "pv3_create", "pv3_destroy", "pv3_last_error", "pv3_set_stream", "pv3_index_add_row", "pv3_index_add_ref",
     "pv3_index_commit", "pv3_set_params", "pv3_set_quality_lut", "pv3_get_quality_lut", "pv3_project",
-    "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_set_kernel_path", "pv3_get_timing",
+    "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_set_kernel_path", "pv3_set_dp_thread_min", "pv3_get_timing",
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
 ]
 
@@ -78,6 +78,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_set_quality_lut.argtypes = [C.c_void_p, C.c_void_p]
     lib.pv3_get_quality_lut.argtypes = [C.c_void_p, C.c_void_p]
     lib.pv3_set_stage.argtypes = [C.c_void_p, C.c_int]
+    lib.pv3_set_dp_thread_min.argtypes = [C.c_void_p, C.c_uint64]
     lib.pv3_set_kernel_path.argtypes = [C.c_void_p, C.c_int]
     lib.pv3_project.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
     lib.pv3_project_device.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
@@ -183,6 +184,9 @@ class Context:
 
     def set_stage(self, stage: int):
         self._check(self.lib.pv3_set_stage(self.h, stage))
+
+    def set_dp_thread_min(self, n: int):
+        self._check(self.lib.pv3_set_dp_thread_min(self.h, n))
 
     def set_kernel_path(self, path: int):
         self._check(self.lib.pv3_set_kernel_path(self.h, path))

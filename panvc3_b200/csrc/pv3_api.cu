@@ -75,11 +75,12 @@ struct pv3_ctx {
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
 	int          stage = 0;
+	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all
 	bool         many_deferred = false;      // last batch: more than 1/16 of the records went to the warp-per-record kernel
 	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
 
 	// device work buffers
-	DevBuf       counters, jobs, dp_arena, pool, deferred, d_packed, d_job_qual_off;
+	DevBuf       counters, jobs, dp_arena, pool, deferred, big_list, d_packed, d_job_qual_off;
 	Job         *h_jobs = nullptr; uint64_t *h_job_qual_off = nullptr; uint64_t h_jobs_cap = 0;   // pinned (lazy QUAL)
 	uint8_t     *h_packed = nullptr; uint64_t h_packed_cap = 0;
 	Counters    *h_counters = nullptr;   // pinned
@@ -159,7 +160,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->d_packed, &ctx->d_job_qual_off,
+	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->big_list, &ctx->d_packed, &ctx->d_job_qual_off,
 			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
 			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
@@ -340,7 +341,14 @@ int pv3_set_kernel_path(pv3_ctx *ctx, int path)
 	return PV3_OK;
 }
 
-int pv3_set_stage(pv3_ctx *ctx, int stage)   // not in the public header: parity probe (1 = rewrite_cigar() only)
+int pv3_set_dp_thread_min(pv3_ctx *ctx, uint64_t n)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	ctx->dp_thread_min = n;
+	return PV3_OK;
+}
+
+int pv3_set_stage(pv3_ctx *ctx, int stage)
 {
 	if (!ctx) return PV3_ERR_INVALID;
 	ctx->stage = stage;
@@ -465,9 +473,9 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 		K3Params K;
 		memset(&K, 0, sizeof K);
 		K.k1 = P; K.n_jobs = n_jobs;
+		uint64_t grid_warps = k3_default_grid_warps(ctx->n_sms);
 		PV3_CUDA(ctx, ctx->dp_arena.ensure((c.dp_path + 1) * 4));
 		K.dp_arena = ctx->dp_arena.as <uint32_t>(); K.dp_arena_cap = c.dp_path;
-		uint64_t grid_warps = k3_default_grid_warps(ctx->n_sms);
 		if (c.dp_max_pool > k3_smem_pool_bytes()) {
 			size_t const slot = align_up((size_t) c.dp_max_pool, 256);
 			uint64_t const fit = POOL_BUDGET / slot ? POOL_BUDGET / slot : 1;
@@ -515,13 +523,28 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 				K.job_qual_off = ctx->d_job_qual_off.as <uint64_t>();
 			}
 		}
-		launch_k3(K, ctx->n_sms, grid_warps, stream);
-		PV3_CUDA(ctx, cudaGetLastError());
+		// small runs (the usual case: a few bases wide): one thread per run; the rest: one warp per run
+		// (a few thousand runs: the warp kernel alone finishes within its launch latency, a second launch only adds to it)
+		bool const use_thread_kernel = n_jobs > c.n_big_jobs && n_jobs - c.n_big_jobs >= ctx->dp_thread_min;
+		if (use_thread_kernel) {
+			if (c.n_big_jobs) {
+				PV3_CUDA(ctx, ctx->big_list.ensure(c.n_big_jobs * 8));
+				K.big_list = ctx->big_list.as <uint64_t>(); K.n_big = c.n_big_jobs;
+			}
+			launch_k3_thread(K, stream);
+			PV3_CUDA(ctx, cudaGetLastError());
+			ctx->timing.launches += 1;
+		}
+		if (c.n_big_jobs || !use_thread_kernel) {
+			launch_k3(K, ctx->n_sms, grid_warps, stream);
+			PV3_CUDA(ctx, cudaGetLastError());
+			ctx->timing.launches += 1;
+		}
 		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[2], stream));
 		launch_k4(P, n_jobs, K.dp_arena, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
+		ctx->timing.launches += 1;
 		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[3], stream));
-		ctx->timing.launches += 2;
 		st = fetch_counters(ctx, stream);
 		if (st) return st;
 		c = *ctx->h_counters;

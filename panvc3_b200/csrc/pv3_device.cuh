@@ -67,6 +67,8 @@ struct Counters {
 	unsigned long long n_deferred;     // records the thread-per-record kernel handed to the warp-per-record kernel
 	unsigned int       overflow;       // bit0: CIGAR arena, bit1: rr/jobs, bit2: DP op arena
 	unsigned int       pad;
+	unsigned long long n_big_jobs;     // runs too large for the thread-per-run DP kernel (the warp-per-run kernel takes them)
+	unsigned long long big_cursor;     // entries of the big-run list written by the thread-per-run kernel
 };
 
 // BAM op codes

@@ -50,6 +50,15 @@ __host__ __device__ inline unsigned long long dp_pool_bytes(uint32_t R, uint32_t
 	return ((rows * cols + 3) & a4) + 8 * cols + ((cols + 3) & a4) + ((cols + 3) & a4);
 }
 
+// Runs small enough for the thread-per-run DP kernel (K3T): the whole DP state of one run fits a thread's local arrays.
+// The warp-per-run kernel (K3) skips them, K3T skips the others; counters.n_big_jobs tells the host whether K3 must run.
+constexpr uint32_t K3T_MAX_DIM   = 15;
+constexpr uint32_t K3T_MAX_TRACE = 64;           // (R + 1) * (Q + 1) trace bytes: a lane waits for the largest run of its warp
+__host__ __device__ inline bool dp_job_is_small(uint32_t R, uint32_t Q)
+{
+	return R <= K3T_MAX_DIM && Q <= K3T_MAX_DIM && (R + 1) * (Q + 1) <= K3T_MAX_TRACE;
+}
+
 struct K3Params {
 	K1Params        k1;             // inputs, index, flags, counters, jobs
 	uint64_t        n_jobs;
@@ -58,6 +67,8 @@ struct K3Params {
 	int32_t         lut[84];        // quality LUT: [2*q] match, [2*q+1] mismatch
 	const uint8_t  *packed_qual;    // lazy-QUAL path: phred ranks of the runs' query windows only, run j at job_qual_off[j]
 	const uint64_t *job_qual_off;   // null ⇒ read k1.qual
+	uint64_t       *big_list;       // ids of the runs left to the warp kernel, written by the thread kernel (null ⇒ all runs)
+	uint64_t        n_big;          // length of big_list (known to the host from counters.n_big_jobs)
 };
 
 struct K4Params {
@@ -71,6 +82,7 @@ struct K4Params {
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
 void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream);   // thread per record (short records)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
+void launch_k3_thread(const K3Params &P, cudaStream_t stream);               // thread per run (small runs)
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);
 void launch_positions(const RowDesc *rows, uint32_t n_rows, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row,
 	const uint64_t *pos, uint64_t *out, cudaStream_t stream);

@@ -59,7 +59,8 @@ k3_realign_kernel(K3Params P)
 		unsigned long long jid = 0;
 		if (lane == 0) jid = atomicAdd(&B.counters->job_ticket, 1ull);
 		jid = shfl_u64(jid, 0);
-		if (jid >= P.n_jobs) break;
+		if (jid >= (P.big_list ? P.n_big : P.n_jobs)) break;
+		if (P.big_list) jid = P.big_list[jid];                     // small runs are realigned by the thread-per-run kernel
 
 		Job const job = B.jobs[jid];
 		uint64_t const rec = job.rec;
@@ -213,9 +214,10 @@ k3_realign_kernel(K3Params P)
 
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream)
 {
-	if (!P.n_jobs) return;
+	uint64_t const n = P.big_list ? P.n_big : P.n_jobs;
+	if (!n) return;
 	uint64_t warps = grid_warps ? grid_warps : k3_default_grid_warps(n_sms);
-	if (warps > P.n_jobs) warps = P.n_jobs;
+	if (warps > n) warps = n;
 	unsigned const blocks = (unsigned) ((warps + K3_WARPS - 1) / K3_WARPS);
 	k3_realign_kernel<<<blocks, K3_WARPS * 32, 0, stream>>>(P);
 }

@@ -290,11 +290,13 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 			if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);
 			bool const affine = has_qual || P.gap_open != 0;
 			unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
-			n_runs = scan_runs<false>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine, false);
+			uint32_t n_big = 0;
+			n_runs = scan_runs<false>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine, false, &n_big);
 			if (!res.flags && n_runs) {
 				if (lane == 0) {
 					job_base = atomicAdd(&P.counters->job_cursor, (unsigned long long) n_runs);
 					atomicAdd(&P.counters->n_realigned, 1ull);
+					if (n_big) atomicAdd(&P.counters->n_big_jobs, (unsigned long long) n_big);
 					atomicAdd(&P.counters->dp_cells, cells);
 					atomicAdd(&P.counters->dp_path, path);
 					atomicAdd(&P.counters->dp_pool, pool);

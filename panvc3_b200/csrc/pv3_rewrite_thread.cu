@@ -273,6 +273,7 @@ k1_thread_kernel(K1Params P)
 
 		// ---- phase C3: final ops — one flat loop, one cigar_buffer::push_back (cigar.cc:61-86) site ----------------------
 		unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
+		uint32_t n_big = 0;
 		bool affine = false;
 		if (work2) {
 			uint32_t j = 0, left = 0, qpos = 0, carry_op = OP_NONE, carry_cnt = 0;
@@ -326,7 +327,7 @@ k1_thread_kernel(K1Params P)
 					bool has_qual = false;
 					if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);
 					affine = has_qual || P.gap_open != 0;
-					n_runs = scan_runs <false>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, nullptr, nullptr, flags, cells, path, pool, max_pool, affine, false);
+					n_runs = scan_runs <false>(&sm.fin[0][tid], TT, n_ops, e0, rec, nq, R.n, nullptr, nullptr, flags, cells, path, pool, max_pool, affine, false, &n_big);
 					if (flags) n_runs = 0;
 				}
 			}
@@ -337,16 +338,19 @@ k1_thread_kernel(K1Params P)
 			uint32_t incl = n_runs;
 			unsigned long long w_cells = n_runs ? cells : 0, w_path = n_runs ? path : 0, w_pool = n_runs ? pool : 0, w_max = n_runs ? max_pool : 0;
 			uint32_t const w_recs = __popc(__ballot_sync(FULL, n_runs != 0));
+			uint32_t w_bigjobs = n_runs ? n_big : 0u;                  // runs the thread-per-run DP kernel leaves to the warp kernel
 			#pragma unroll
 			for (int d = 1; d < 32; d <<= 1) { uint32_t const t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
 			#pragma unroll
 			for (int d = 16; d >= 1; d >>= 1) {
 				w_cells += shfl_u64(w_cells, (int) (lane ^ d)); w_path += shfl_u64(w_path, (int) (lane ^ d)); w_pool += shfl_u64(w_pool, (int) (lane ^ d));
 				unsigned long long const o = shfl_u64(w_max, (int) (lane ^ d)); if (o > w_max) w_max = o;
+				w_bigjobs += __shfl_xor_sync(FULL, w_bigjobs, d);
 			}
 			uint32_t const w_runs = __shfl_sync(FULL, incl, 31);
 			unsigned long long wbase = 0;
 			if (lane == 0) {
+				if (w_bigjobs) atomicAdd(&P.counters->n_big_jobs, (unsigned long long) w_bigjobs);
 				wbase = atomicAdd(&P.counters->job_cursor, (unsigned long long) w_runs);
 				atomicAdd(&P.counters->n_realigned, (unsigned long long) w_recs);
 				atomicAdd(&P.counters->dp_cells, w_cells);

@@ -13,7 +13,8 @@ namespace pv3 {
 template <bool WRITE>
 __device__ __forceinline__ uint32_t scan_runs(const uint32_t *ops, uint32_t stride, uint32_t n_ops, uint64_t dst_pos, uint64_t rec, uint64_t nq, uint64_t ref_n,
 	Job *jobs, uint64_t *rr, uint32_t &flags, unsigned long long &cells, unsigned long long &path,
-	unsigned long long &pool, unsigned long long &max_pool, bool affine, bool i_write)
+	unsigned long long &pool, unsigned long long &max_pool, bool affine, bool i_write,
+	uint32_t *n_big = nullptr)
 {
 	uint64_t ref = dst_pos, qry = 0, run_ref = dst_pos, run_qry = 0;
 	uint32_t run_k = 0, type = 0, n_runs = 0;
@@ -51,6 +52,7 @@ __device__ __forceinline__ uint32_t scan_runs(const uint32_t *ops, uint32_t stri
 				unsigned long long const need = dp_pool_bytes((uint32_t) rlen, (uint32_t) qlen, affine);
 				pool += need;
 				if (need > max_pool) max_pool = need;
+				if (n_big && !dp_job_is_small((uint32_t) rlen, (uint32_t) qlen)) ++*n_big;
 			}
 			++n_runs;
 			type = (k < n_ops) ? type : 0;

@@ -9,31 +9,56 @@
 
 namespace pv3 {
 
-// One thread per run; the thread holding the first run of a record rebuilds that record's CIGAR.
-__global__ void k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp_arena)
+// One thread per run; the thread holding the first run of a record rebuilds that record's CIGAR. The arena space of a
+// warp's records is taken with one atomic (per-record atomics on the cursor serialise when most records realign).
+__global__ void __launch_bounds__(128)
+k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp_arena)
 {
 	uint64_t const jid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-	if (jid >= n_jobs) return;
-	uint64_t const rec = P.jobs[jid].rec;
-	if (P.rr_off[rec] != jid + P.rr_base) return;
-	uint32_t const n_runs = P.rr_len[rec];
-	if (P.flags[rec]) { P.cig_out_len[rec] = 0; P.rr_len[rec] = 0; return; }   // flagged by the DP kernel
-
-	const uint32_t *pre = P.arena + (P.cig_out_off[rec] - P.arena_off);
-	uint32_t const n_pre = P.cig_out_len[rec];
-	unsigned long long bound = n_pre;
-	for (uint32_t r = 0; r < n_runs; ++r) {
-		Job const &j = P.jobs[jid + r];
-		bound += j.out_len;
-		bound -= (j.op_end - j.op_begin);
+	unsigned const lane = lane_id();
+	uint64_t rec = 0;
+	uint32_t n_runs = 0, n_pre = 0, bound = 0;
+	const uint32_t *pre = nullptr;
+	bool owner = false;
+	if (jid < n_jobs) {
+		rec = P.jobs[jid].rec;
+		owner = (P.rr_off[rec] == jid + P.rr_base);
 	}
-	unsigned long long const base = atomicAdd(&P.counters->arena_cursor, bound);
-	if (base + bound > P.arena_cap) { atomicOr(&P.counters->overflow, 1u); P.cig_out_len[rec] = 0; return; }
+	if (owner) {
+		n_runs = P.rr_len[rec];
+		if (P.flags[rec]) { P.cig_out_len[rec] = 0; P.rr_len[rec] = 0; owner = false; }   // flagged by a DP kernel
+	}
+	if (owner) {
+		pre = P.arena + (P.cig_out_off[rec] - P.arena_off);
+		n_pre = P.cig_out_len[rec];
+		bound = n_pre;
+		for (uint32_t r = 0; r < n_runs; ++r) {
+			Job const &j = P.jobs[jid + r];
+			bound += j.out_len;
+			bound -= (j.op_end - j.op_begin);
+		}
+	}
+	uint32_t incl = bound;
+	#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) { uint32_t const t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
+	uint32_t const total = __shfl_sync(FULL, incl, 31);
+	unsigned long long wbase = 0;
+	if (lane == 0 && total) {
+		wbase = atomicAdd(&P.counters->arena_cursor, (unsigned long long) total);
+		if (wbase + total > P.arena_cap) { atomicOr(&P.counters->overflow, 1u); wbase = ~0ull; }
+	}
+	wbase = shfl_u64(wbase, 0);
+	if (!owner) return;
+	if (wbase == ~0ull) { P.cig_out_len[rec] = 0; return; }
+	unsigned long long const base = wbase + (incl - bound);
 	uint32_t *dst = P.arena + base;
-	long long w = -1;
+	// collapse_cigar_operations (cigar.cc:33-38): the open op stays in registers until a different op arrives
+	uint32_t w = 0, cur_op = OP_NONE, cur_cnt = 0;
 	auto push = [&](uint32_t v) {
-		if (w >= 0 && (dst[w] & 0xfu) == (v & 0xfu)) dst[w] += (v >> 4) << 4;   // cigar.cc:33-38
-		else dst[++w] = v;
+		uint32_t const o = v & 0xfu;
+		if (o == cur_op) { cur_cnt += v >> 4; return; }
+		if (cur_op != OP_NONE) dst[w++] = (cur_cnt << 4) | cur_op;
+		cur_op = o; cur_cnt = v >> 4;
 	};
 	uint32_t k = 0;
 	for (uint32_t r = 0; r < n_runs; ++r) {
@@ -44,8 +69,9 @@ __global__ void k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp
 		k = j.op_end;
 	}
 	for (; k < n_pre; ++k) push(pre[k]);                                // :145-148
+	if (cur_op != OP_NONE) dst[w++] = (cur_cnt << 4) | cur_op;
 	P.cig_out_off[rec] = base + P.arena_off;
-	P.cig_out_len[rec] = (uint32_t) (w + 1);
+	P.cig_out_len[rec] = w;
 }
 
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream)

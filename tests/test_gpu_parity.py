@@ -114,11 +114,12 @@ def test_random_batches_match_oracle(gpu, port, seed):
     for go, ge in [(0, -1), (0, -3), (-2, -1), (-5, -2), (3, -1)]:
         for stage in (1, 0):
             exp = oi.project_batch(b, go, ge, stage=stage)
-            for path in (0, 1):
+            for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):      # dp_min 0: small runs go to the thread-per-run DP kernel
                 idx.ctx.set_stage(stage)
                 idx.ctx.set_kernel_path(path)
+                idx.ctx.set_dp_thread_min(dp_min)
                 got = idx.project_batch(b, go, ge)
-                assert_same(got, exp, b, f"seed={seed} stage={stage} go={go} ge={ge} path={path}")
+                assert_same(got, exp, b, f"seed={seed} stage={stage} go={go} ge={ge} path={path} dp_min={dp_min}")
                 assert got.stats["n_flagged"] == int((got.flags != 0).sum())
 
 
@@ -173,10 +174,11 @@ def test_dp_modes_large_windows(gpu, port):
     b = RecordBatch.from_records(recs)
     for go, ge in [(0, -1), (-3, -1), (2, -2)]:
         exp = oi.project_batch(b, go, ge)
-        for path in (0, 1):
+        for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):
             idx.ctx.set_kernel_path(path)
+            idx.ctx.set_dp_thread_min(dp_min)
             got = idx.project_batch(b, go, ge)
-            assert_same(got, exp, b, f"large windows go={go} ge={ge} path={path}")
+            assert_same(got, exp, b, f"large windows go={go} ge={ge} path={path} dp_min={dp_min}")
         assert int(exp.rr_len.sum()) >= len(recs) - 2
 
 
@@ -293,3 +295,18 @@ def test_realistic_reads_both_paths_and_mixed_lengths(gpu, port, workflow_msa):
         for path in (0, 1):
             idx.ctx.set_kernel_path(path)
             assert_same(idx.project_batch(b, go, ge), exp, b, f"mixed go={go} path={path}")
+
+
+def test_indel_heavy_batch_thread_dp_kernel(gpu, port):
+    """configs[3]-style stress (scaled): most records realign, tens of thousands of small runs — the thread-per-run DP kernel,
+    the compact list of larger runs for the warp kernel and the warp-aggregated splice, in all three DP modes."""
+    from panvc3_b200.workload import sample_reads, synth_msa
+    msa = synth_msa(60_000, 4, seed=91, p_gap=0.01, mean_gap=6, snp=0.01, anticorrelated=0.01)
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    for with_qual, go, ge in ((True, 0, -1), (False, 0, -1), (False, -2, -1), (True, -3, -2)):
+        b = sample_reads(msa, 60_000, 150, seed=5 + int(with_qual), ins=0.001, dele=0.001, with_qual=with_qual)
+        exp = oi.project_batch(b, go, ge, n_threads=os.cpu_count() or 1)
+        got = idx.project_batch(b, go, ge)
+        assert int(exp.rr_len.sum()) > 20_000
+        assert_same(got, exp, b, f"indel-heavy qual={with_qual} go={go} ge={ge}")
