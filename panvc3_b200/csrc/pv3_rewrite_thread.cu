@@ -36,17 +36,17 @@ namespace pv3 {
 
 constexpr int      TT        = 128;            // threads per CTA = records per tile
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
-constexpr int      T_RAWQ    = 40;             // raw runs per record (column runs + pass-through ops)
-constexpr int      T_PIECEQ  = 16;             // compare pieces per record
+constexpr int      T_RAWQ    = 32;             // raw runs per record (column runs + pass-through ops)
+constexpr int      T_PIECEQ  = 12;             // compare pieces per record
 constexpr uint32_t T_QSTAGE  = TT * 168;       // query bases staged per tile
-constexpr uint32_t T_RWIN    = 224;            // target bases staged per record (7 x 16 bytes of nibbles)
+constexpr uint32_t T_RWIN    = 192;            // target bases staged per record (6 x 16 bytes of nibbles)
 constexpr uint32_t T_RCH     = T_RWIN / 32;    // 16-byte chunks per staged target window
 constexpr uint32_t T_MMW     = 6;              // mismatch bit words per record (query coordinates): reads up to 192 bases
 constexpr uint32_t T_C1_ITERS = 192;           // bound of the column walk (long gaps / deletions go to the warp kernel)
 constexpr uint32_t RAW_PASS  = 0x8000u;        // raw entry refers to input op (entry & 0x7fff)
 constexpr uint32_t ERR_DEFER = 0x80000000u;
 
-// 48 KB ⇒ 4 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
+// 41 KB ⇒ 5 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
 struct TileSmem {
 	uint16_t raw[T_RAWQ][TT];
 	uint32_t piece[T_PIECEQ][TT];              // qpos | (target offset from the staged window start) << 8 | len << 24
@@ -417,7 +417,7 @@ void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
 	}
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 	if (!n_tiles) return;
-	uint64_t blocks = (uint64_t) n_sms * 4;       // 4 CTAs of 48 KB shared memory per SM
+	uint64_t blocks = (uint64_t) n_sms * 5;       // 5 CTAs of 41 KB shared memory per SM
 	if (blocks > n_tiles) blocks = n_tiles;
 	k1_thread_kernel<<<(unsigned) blocks, TT, sizeof(TileSmem), stream>>>(P);
 }
