@@ -19,7 +19,7 @@
 // the target codes packed, RefDesc::codes4), so that one compare step covers 16 bases and the tile needs half the shared
 // memory (4 CTAs per SM instead of 3); the column walk runs on 32-bit window-relative coordinates with soft exits.
 //
-// Tile pipeline (128 threads = 128 consecutive records):
+// Tile pipeline (32 threads = 32 consecutive records; measured: 128, 64, 32 → 0.433, 0.425, 0.421 ms per 1M records):
 //   A  each thread: ids, src_pos, select0/rank0 of its record → c0, e0
 //   B  cooperative, coalesced staging into shared memory: the tile's query bytes (contiguous in the batch) packed to
 //      nibbles, and per record a 224-base window of packed target codes at e0
@@ -34,7 +34,7 @@
 
 namespace pv3 {
 
-constexpr int      TT        = 128;            // threads per CTA = records per tile
+constexpr int      TT        = 32;             // threads per CTA = records per tile (one warp: the tile barriers cost nothing)
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
 constexpr int      T_RAWQ    = 32;             // raw runs per record (column runs + pass-through ops)
 constexpr int      T_PIECEQ  = 12;             // compare pieces per record
@@ -46,7 +46,7 @@ constexpr uint32_t T_C1_ITERS = 192;           // bound of the column walk (long
 constexpr uint32_t RAW_PASS  = 0x8000u;        // raw entry refers to input op (entry & 0x7fff)
 constexpr uint32_t ERR_DEFER = 0x80000000u;
 
-// 41 KB ⇒ 5 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
+// 10 KB per one-warp tile ⇒ 19-20 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
 struct TileSmem {
 	uint16_t raw[T_RAWQ][TT];
 	uint32_t piece[T_PIECEQ][TT];              // qpos | (target offset from the staged window start) << 8 | len << 24
@@ -410,14 +410,14 @@ k1_thread_kernel(K1Params P)
 
 void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
 {
-	static bool configured = false;
-	if (!configured) {
+	static int per_sm = 0;
+	if (!per_sm) {
 		cudaFuncSetAttribute(k1_thread_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(TileSmem));
-		configured = true;
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_thread_kernel, TT, sizeof(TileSmem)) != cudaSuccess || per_sm < 1) per_sm = 1;
 	}
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 	if (!n_tiles) return;
-	uint64_t blocks = (uint64_t) n_sms * 5;       // 5 CTAs of 41 KB shared memory per SM
+	uint64_t blocks = (uint64_t) n_sms * per_sm;  // persistent: every resident CTA strides over the tiles (shared memory bounds the count)
 	if (blocks > n_tiles) blocks = n_tiles;
 	k1_thread_kernel<<<(unsigned) blocks, TT, sizeof(TileSmem), stream>>>(P);
 }
