@@ -186,6 +186,7 @@ k1_thread_kernel(K1Params P)
 			uint32_t src_left = left64 > 0xffffffffull ? 0xffffffffu : (uint32_t) left64;   // op counts are < 2^28
 			uint32_t crel = (uint32_t) c0 & 63u, ra = (uint32_t) (e0 - e0a), qpos = 0, k = 0, rem = 0, err = 0, wcur = ~0u;
 			uint64_t Sinv = 0, Dinv = 0;
+			uint64_t Snext = __ldg(Sp), Dnext = __ldg(Dp);                      // the walk starts in word 0 of the window; one word ahead
 			bool mlike = false;
 			for (uint32_t it = 0; ; ++it) {
 				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
@@ -208,7 +209,10 @@ k1_thread_kernel(K1Params P)
 					if (!rem) continue;
 				}
 				uint32_t const wi = crel >> 6, b = crel & 63u;
-				if (wi != wcur) { Sinv = ~__ldg(Sp + wi); Dinv = ~__ldg(Dp + wi); wcur = wi; }
+				if (wi != wcur) {                                                   // next word pair is already in flight
+					Sinv = ~Snext; Dinv = ~Dnext; wcur = wi;
+					Snext = __ldg(Sp + wi + 1); Dnext = __ldg(Dp + wi + 1);
+				}
 				uint64_t const s = Sinv >> b, d = Dinv >> b;
 				uint32_t const sb = (uint32_t) s & 1u, db = (uint32_t) d & 1u;
 				uint64_t const nr = (s ^ (0ull - (uint64_t) sb)) | (d ^ (0ull - (uint64_t) db));
