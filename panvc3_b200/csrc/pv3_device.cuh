@@ -18,7 +18,7 @@ namespace pv3 {
 
 constexpr int      BLK_WORDS = 8;            // 512-bit blocks
 constexpr int      BLK_BITS  = 512;
-constexpr uint32_t SEL_RATE  = 8192;
+constexpr uint32_t SEL_RATE  = 512;            // one sample per block's worth of zeros: the search below is 1-2 loads deep
 constexpr int      PAD_WORDS = 72;           // >= 64 + BLK_WORDS
 constexpr unsigned FULL      = 0xffffffffu;
 
@@ -171,18 +171,29 @@ __device__ inline uint64_t select0_thread(const RowDesc &r, uint64_t k)
 	if (k == 0 || k > r.n_zeros) return r.n_bits;
 	uint64_t const s = (k - 1) / SEL_RATE;
 	uint64_t lo = __ldg(r.sel + s), hi = __ldg(r.sel + s + 1);
-	while (lo < hi) {
+	while (hi - lo > 3) {                                           // long gap stretches only
 		uint64_t const mid = lo + (hi - lo + 1) / 2;
 		if (__ldg(r.blk_zeros + mid) < k) lo = mid; else hi = mid - 1;
 	}
-	unsigned need = (unsigned) (k - __ldg(r.blk_zeros + lo));
+	// the block is one of lo..lo+3: blk_zeros is monotone and padded with n_zeros (>= k), so entries past `hi` never count
+	uint64_t const v0 = __ldg(r.blk_zeros + lo), v1 = __ldg(r.blk_zeros + lo + 1), v2 = __ldg(r.blk_zeros + lo + 2), v3 = __ldg(r.blk_zeros + lo + 3);
+	unsigned const adv = (unsigned) (v1 < k) + (unsigned) (v2 < k) + (unsigned) (v3 < k);
+	uint64_t const base = adv == 0 ? v0 : adv == 1 ? v1 : adv == 2 ? v2 : v3;
+	uint64_t const blk = lo + adv;
+	unsigned need = (unsigned) (k - base);
+	const ulonglong2 *wp = reinterpret_cast <const ulonglong2 *>(r.words + blk * BLK_WORDS);   // 64-byte aligned
+	ulonglong2 const a = __ldg(wp), b = __ldg(wp + 1), c = __ldg(wp + 2), d = __ldg(wp + 3);
+	uint64_t const inv[BLK_WORDS] = { ~a.x, ~a.y, ~b.x, ~b.y, ~c.x, ~c.y, ~d.x, ~d.y };
+	uint64_t word = inv[BLK_WORDS - 1];
+	unsigned wi = BLK_WORDS - 1;
+	bool found = false;
+	#pragma unroll
 	for (unsigned w = 0; w < (unsigned) BLK_WORDS; ++w) {
-		uint64_t const inv = ~__ldg(r.words + lo * BLK_WORDS + w);
-		unsigned const pc = __popcll(inv);
-		if (need <= pc) return lo * BLK_BITS + w * 64 + select_in_word(inv, need);
-		need -= pc;
+		unsigned const pc = __popcll(inv[w]);
+		if (!found) { if (need <= pc) { found = true; word = inv[w]; wi = w; } else need -= pc; }
 	}
-	return r.n_bits; // unreachable for a consistent directory
+	if (!found) return r.n_bits; // unreachable for a consistent directory
+	return blk * BLK_BITS + wi * 64 + select_in_word(word, need);
 }
 
 } // namespace pv3

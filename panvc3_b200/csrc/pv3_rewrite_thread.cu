@@ -138,7 +138,7 @@ k1_thread_kernel(K1Params P)
 		RowDesc S = {}, D = {};
 		RefDesc R = {};
 		uint64_t c0 = 0, e0 = 0, spos = 0, qoff = 0, nq = 0, cbase = 0;
-		uint32_t nc = 0;
+		uint32_t nc = 0, first_op = 0;
 		sm.ref_ptr[tid] = nullptr;
 		if (active) {
 			uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec), rf = __ldg(P.dst_ref + rec);
@@ -153,6 +153,7 @@ k1_thread_kernel(K1Params P)
 				}
 				cbase = __ldg(P.cig_off + rec);
 				nc = (uint32_t) (__ldg(P.cig_off + rec + 1) - cbase);
+				if (nc) first_op = __ldg(P.cig + cbase);                             // in flight while select0/rank0 run
 				spos = __ldg(P.src_pos + rec);
 				c0 = (spos < S.n_zeros) ? select0_thread(S, spos + 1) : S.n_bits;     // rewrite_cigar.hh:51
 				e0 = rank0_thread(D, c0);                                              // :52
@@ -192,7 +193,7 @@ k1_thread_kernel(K1Params P)
 				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
 				if (rem == 0) {                                                    // next input op
 					if (k == nc) break;
-					uint32_t const packed = __ldg(P.cig + cbase + k);
+					uint32_t const packed = k ? __ldg(P.cig + cbase + k) : first_op;
 					uint32_t const cnt = packed >> 4, op = packed & 0xfu;
 					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; continue; }       // rewrite_cigar.hh:149-151
 					if ((0x72u >> op) & 1u) {                                          // I S H P pass through (:68-77)
