@@ -310,3 +310,25 @@ def test_indel_heavy_batch_thread_dp_kernel(gpu, port):
         got = idx.project_batch(b, go, ge)
         assert int(exp.rr_len.sum()) > 20_000
         assert_same(got, exp, b, f"indel-heavy qual={with_qual} go={go} ge={ge}")
+
+
+def test_large_index_parity(gpu, port):
+    """configs[2]-style scale (scaled to what the CPU oracle indexes in seconds): 20 M columns, directory and select samples
+    far beyond the caches' reach for random positions; positions, CIGARs and ranges against the oracle."""
+    from panvc3_b200.workload import sample_reads, synth_msa
+    msa = synth_msa(20_000_000, 3, seed=123, p_gap=0.002, mean_gap=8, snp=0.001)
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    b = sample_reads(msa, 40_000, 150, seed=9)
+    exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+    for path in (0, 1):
+        idx.ctx.set_kernel_path(path)
+        assert_same(idx.project_batch(b, 0, -1), exp, b, f"large index path={path}")
+    # mates: position-only projection at random positions of every founder row
+    rng = np.random.default_rng(5)
+    rows = rng.integers(1, msa.n_rows, 3_000).astype(np.uint32)
+    lens = np.asarray([msa.ungapped[r].size for r in range(msa.n_rows)], dtype=np.int64)
+    pos = (rng.random(rows.size) * (lens[rows] - 1)).astype(np.uint64)
+    got = idx.ctx.project_positions(rows, np.zeros(rows.size, np.uint32), pos)
+    expp = np.array([oi.project_position(int(a), 0, int(c)) for a, c in zip(rows, pos)], dtype=np.uint64)
+    assert np.array_equal(got, expp)
