@@ -138,6 +138,25 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def bind_to_gpu_numa_node(gpu_index: int) -> str | None:
+    """Pins this rank to the CPUs next to its GPU (NVML's affinity mask) before any pinned buffer is allocated, so that the
+    host side of every H2D/D2H copy is first-touched on the GPU's own NUMA node (one process per GPU: 8 ranks otherwise share
+    whatever node the launcher started them on)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1 and 64 * i + b < n_cpu}
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cpus"
+    except Exception as e:       # affinity is an optimisation, never a requirement
+        return f"unavailable ({type(e).__name__})"
+    return None
+
+
 def measured_peak_gbs() -> tuple[float, str]:
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -262,6 +281,7 @@ def run_gpu_arm(args) -> None:
         raise SystemExit("bench.py: no CUDA device — the panvc3_b200 hot path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_note = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -396,7 +416,8 @@ def run_gpu_arm(args) -> None:
                     "d2h_bytes_per_step": int(d2h_bytes),
                     "h2d_note": "QUAL is uploaded lazily: only the query windows of realigned runs cross PCIe (bulk upload when > 1/16 of the records realign)",
                     "ms_per_step": e2e_ms_max / args.steps, "h2d_ms": statistics.mean(h2d_ms), "d2h_ms": statistics.mean(d2h_ms),
-                    "timer": "host perf_counter around K pv3_project calls, synchronized both sides, max over ranks"},
+                    "timer": "host perf_counter around K pv3_project calls, synchronized both sides, max over ranks",
+                    "numa_binding": numa_note},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
         }

@@ -189,6 +189,18 @@ k1_thread_kernel(K1Params P)
 			uint64_t Sinv = 0, Dinv = 0;
 			uint64_t Snext = __ldg(Sp), Dnext = __ldg(Dp);                      // the walk starts in word 0 of the window; one word ahead
 			bool mlike = false;
+			uint32_t pend_op = OP_NONE, pend_len = 0, pend_q = 0, pend_ra = 0;   // the open run (not yet in the lists)
+			auto flush = [&]() {
+				if (pend_op != OP_NONE) {
+					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((pend_len << 4) | pend_op);
+					++n_raw;
+					if (pend_op == OP_EQ) {
+						if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = pend_q | (pend_ra << 8) | (pend_len << 24);
+						++n_piece;
+					}
+					pend_op = OP_NONE;
+				}
+			};
 			for (uint32_t it = 0; ; ++it) {
 				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
 				if (rem == 0) {                                                    // next input op
@@ -197,6 +209,7 @@ k1_thread_kernel(K1Params P)
 					uint32_t const cnt = packed >> 4, op = packed & 0xfu;
 					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; continue; }       // rewrite_cigar.hh:149-151
 					if ((0x72u >> op) & 1u) {                                          // I S H P pass through (:68-77)
+						flush();
 						if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) (RAW_PASS | k);
 						++n_raw;
 						if (op == OP_I || op == OP_S) qpos = min(qpos + cnt, 0x10000u);
@@ -228,17 +241,18 @@ k1_thread_kernel(K1Params P)
 					if (qpos + len > nq32) e1 = PV3_FLAG_QUERY_OOB;
 					else if (ra + len > r_lim) e1 = (r_room > 0x10000ull) ? ERR_DEFER : PV3_FLAG_REF_OOB;
 					if (e1) { err = e1; k = nc; rem = 0; continue; }
-					if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = qpos | (ra << 8) | (len << 24);
-					++n_piece;
 				}
 				uint32_t const op = db ? (isq ? OP_EQ : OP_D) : OP_I;             // :92-100, :127-137
 				if (db || isq) {
-					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((len << 4) | op);
-					++n_raw;
+					// a run that continues the pending one (across a word boundary or over columns that are gaps in both rows)
+					// extends it: fewer raw runs and compare pieces for the next two loops
+					if (op == pend_op && pend_len + len <= 250u) pend_len += len;
+					else { flush(); pend_op = op; pend_len = len; pend_q = qpos; pend_ra = ra; }
 				}
 				if (isq) qpos = min(qpos + len, 0x10000u);
 				if (db) ra = min(ra + len, 0x20000u);
 			}
+			flush();
 			if (err == ERR_DEFER || n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
 			else flags |= err;
 		}
