@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -75,6 +76,7 @@ struct pv3_ctx {
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
 	int          stage = 0;
+	uint64_t     chunk_records = 500000;     // records per chunk of the host pipeline (PV3_CHUNK_RECORDS overrides)
 	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all
 	bool         many_deferred = false;      // last batch: more than 1/16 of the records went to the warp-per-record kernel
 	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
@@ -146,6 +148,7 @@ int pv3_create(pv3_ctx **out, int device)
 	ctx->device = device;
 	ctx->n_sms = prop.multiProcessorCount;
 	default_quality_lut(ctx->lut);
+	if (const char *e = getenv("PV3_CHUNK_RECORDS")) { long long v = atoll(e); if (v >= 1024) ctx->chunk_records = (uint64_t) v; }
 	if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaStreamCreate failed"); }
 	ctx->stream = ctx->own_stream;
 	for (auto &ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaEventCreate failed"); }
@@ -608,7 +611,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	if (!n) return PV3_OK;
 
 	bool const own_streams = (ctx->stream == ctx->own_stream);
-	uint64_t n_chunks = own_streams ? (n + 125000) / 250000 : 1;
+	uint64_t n_chunks = own_streams ? (n + ctx->chunk_records / 2) / ctx->chunk_records : 1;
 	if (n_chunks < 1) n_chunks = 1;
 	if (n_chunks > 64) n_chunks = 64;
 	if (own_streams && !ctx->stream2) PV3_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
