@@ -45,6 +45,12 @@ def load_workload(n: int, rank: int = 0, workload: str = "config2"):
         msa = synth_msa(400_000, 4, seed=SEED + 11, p_gap=0.01, mean_gap=6, snp=0.01, anticorrelated=0.01)
         batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank + 1, ins=0.001, dele=0.001)
         name = "configs[3]-style indel-heavy stress: synthetic 400k-column MSA with abutting I/D columns, 150-bp reads"
+    elif workload == "long":
+        # configs[4]-style long reads (scaled): every record exceeds the thread kernel's quotas → the warp-per-record kernel
+        cols = int(os.environ.get("PV3_CHR_COLS", "20000000"))
+        msa = synth_msa(cols, 3, seed=SEED + 31, p_gap=0.002, mean_gap=8, snp=0.001)
+        batch = sample_reads(msa, n, 10_000, seed=SEED + 1000 * rank + 3, ins=0.0002, dele=0.0002)
+        name = f"configs[4]-style long reads: synthetic {cols}-column MSA, 1+3 rows, 10-kb reads with indels"
     elif workload == "chr":
         # configs[2]-style scale (bounded by host memory for the generator): index and target are not cache-resident
         cols = int(os.environ.get("PV3_CHR_COLS", "100000000"))
@@ -399,7 +405,7 @@ def run_gpu_arm(args) -> None:
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": name, "records_per_gpu_per_step": n, "read_len": READ_LEN, "gap_open": 0, "gap_ext": -1,
+            "config": {"workload": name, "records_per_gpu_per_step": n, "read_len": int(batch.seq.size // max(n, 1)), "gap_open": 0, "gap_ext": -1,
                        "l2_policy": f"inputs larger than L2: {batch.input_bytes() / 1e6:.0f} MB of input per step per GPU vs 126 MB L2",
                        "parallelism": f"{world} independent contiguous shards, index replicated per GPU, no data-path collective",
                        "realigned_runs_per_step": stats["rr_used"], "dp_cells_per_step": stats["dp_cells"],
@@ -439,7 +445,7 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config2", choices=["config2", "indel", "chr"])
+    ap.add_argument("--workload", default="config2", choices=["config2", "indel", "chr", "long"])
     ap.add_argument("--records", type=int, default=RECORDS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dp-leg", action="store_true", help="skip the realignment-throughput leg on the indel-heavy shape")
