@@ -159,6 +159,25 @@ uint64_t pv3_total_launches(const pv3_ctx *);
 void *pv3_host_alloc(size_t bytes);
 void  pv3_host_free(void *);
 
+/* -- MSA index file (host only, no GPU needed) ---------------------------------------------------------------------------
+ * The file `panvc3 index-msa` writes and `project-alignments --msa-index` reads: panvc3::msa_index through
+ * cereal::PortableBinary{Output,Input}Archive (include/panvc3/msa_index.hh:40-192; written at
+ * index-msa/input_processor.cc:186-200, loaded at project-alignments/project_alignments.cc:1457-1465). Every gap vector is
+ * an sdsl::rrr_vector<15> (lib/sdsl-lite/include/sdsl/rrr_vector_15.hpp:197-273, 389-407); pv3_index_file_open expands
+ * them to the plain words pv3_index_add_row takes (bit i of word i/64 = 1 ⇔ column i is a gap), and pv3_index_file_write
+ * produces the same bytes the reference would for the same rows. Entries come back in file order (chr ids sorted, seq ids
+ * sorted inside each). Errors: PV3_ERR_INVALID with pv3_index_file_error() (not thread-safe, like pv3_last_error(NULL)). */
+typedef struct pv3_index_file pv3_index_file;
+int pv3_index_file_open(const char *path, pv3_index_file **out);
+uint64_t pv3_index_file_entries(const pv3_index_file *);
+/* Pointers stay valid until pv3_index_file_close; any out argument may be NULL. */
+int pv3_index_file_entry(const pv3_index_file *, uint64_t i, const char **chr_id, const char **seq_id,
+                         const uint64_t **gap_words, uint64_t *n_bits);
+void pv3_index_file_close(pv3_index_file *);
+int pv3_index_file_write(const char *path, uint64_t n_entries, const char *const *chr_ids, const char *const *seq_ids,
+                         const uint64_t *const *gap_words, const uint64_t *n_bits);
+const char *pv3_index_file_error(void);
+
 #ifdef __cplusplus
 }
 #endif

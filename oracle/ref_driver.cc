@@ -315,3 +315,48 @@ void pv3o_quality_lut(int32_t *lut84)
 }
 
 } // extern "C"
+
+
+/* ---- MSA index file, written by the REFERENCE's own serialisation (golden files for the index-format tests) -----------
+ * panvc3::msa_index::serialize (include/panvc3/msa_index.hh:158-192) through cereal::PortableBinaryOutputArchive, as
+ * index-msa/input_processor.cc:117,197-200 does (entries sorted by id before they are written). Reference build only. */
+#include <cereal/archives/portable_binary.hpp>
+#include <cereal/types/string.hpp>
+#include <cereal/types/vector.hpp>
+#include <algorithm>
+#include <fstream>
+
+extern "C" {
+
+int pv3o_write_msa_index_file(const char *path, uint64_t n_entries, const char *const *chr_ids, const char *const *seq_ids,
+	const uint64_t *const *gap_words, const uint64_t *n_bits)
+{
+	panvc3::msa_index index;
+	for (uint64_t i = 0; i < n_entries; ++i) {
+		sdsl::bit_vector bv(n_bits[i], 0);
+		if (n_bits[i]) {
+			std::memcpy(bv.data(), gap_words[i], ((n_bits[i] + 63) / 64) * 8);
+			if (n_bits[i] % 64)
+				bv.data()[(n_bits[i] - 1) / 64] &= (~std::uint64_t(0)) >> (64 - n_bits[i] % 64);
+		}
+		auto it(std::find_if(index.chr_entries.begin(), index.chr_entries.end(), [&](auto const &e){ return e.chr_id == chr_ids[i]; }));
+		if (it == index.chr_entries.end()) {
+			index.chr_entries.emplace_back(std::string(chr_ids[i]));
+			it = index.chr_entries.end() - 1;
+		}
+		it->sequence_entries.emplace_back(std::string(seq_ids[i]), bv);
+	}
+	for (auto &chr : index.chr_entries)
+		std::sort(chr.sequence_entries.begin(), chr.sequence_entries.end());
+	std::sort(index.chr_entries.begin(), index.chr_entries.end());
+	std::ofstream os(path, std::ios::binary);
+	if (!os) return -1;
+	{
+		cereal::PortableBinaryOutputArchive archive(os);
+		archive(index);
+	}
+	os.flush();
+	return os ? 0 : -1;
+}
+
+} // extern "C"

@@ -21,6 +21,8 @@ EXPORTED_SYMBOLS = [
     "pv3_index_commit", "pv3_set_params", "pv3_set_quality_lut", "pv3_get_quality_lut", "pv3_project",
     "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_set_kernel_path", "pv3_set_dp_thread_min", "pv3_get_timing",
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
+    "pv3_index_file_open", "pv3_index_file_entries", "pv3_index_file_entry", "pv3_index_file_close", "pv3_index_file_write",
+    "pv3_index_file_error",
 ]
 
 
@@ -91,6 +93,16 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_host_alloc.restype = C.c_void_p
     lib.pv3_host_free.argtypes = [C.c_void_p]
     lib.pv3_host_free.restype = None
+    lib.pv3_index_file_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.pv3_index_file_entries.argtypes = [C.c_void_p]
+    lib.pv3_index_file_entries.restype = C.c_uint64
+    lib.pv3_index_file_entry.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
+                                         C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.pv3_index_file_close.argtypes = [C.c_void_p]
+    lib.pv3_index_file_close.restype = None
+    lib.pv3_index_file_write.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
+                                         C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.pv3_index_file_error.restype = C.c_char_p
     _lib = lib
     return lib
 

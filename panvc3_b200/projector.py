@@ -58,6 +58,7 @@ class SequenceEntry:
         self.seq_id = seq_id
         self.row = row
         self.n_bits = n_bits
+        self.ref_id: int | None = None                                # contig id of this entry's unaligned sequence, if loaded
 
     def aligned_position(self, pos: int) -> int:                      # msa_index.hh:239-244
         return int(self._index.ctx.index_query(1, [self.row], [pos + 1])[0])
@@ -115,6 +116,31 @@ class MsaIndex:
         for u in msa.ungapped:
             idx.add_reference(u.tobytes())
         return idx.commit()
+
+    @classmethod
+    def from_file(cls, path: str, chr_id: str, references: dict[str, bytes] | None = None, device: int = 0) -> "MsaIndex":
+        """Loads the chr entry `chr_id` of an index-msa file (project_alignments.cc:1457-1465 loads the file, :632-650 looks
+        the chr and sequence entries up by id). `references` maps seq ids to the unaligned contigs (--reference FASTA,
+        project_alignments.cc:1441-1455); each loaded contig's id is kept in SequenceEntry.ref_id. The index comes back committed."""
+        from .index_file import read_index_file
+        idx = cls(device)
+        found = False
+        for e in read_index_file(path):
+            if e.chr_id != chr_id:
+                continue
+            found = True
+            entry = idx.add_entry(e.seq_id, e.gap_words, e.n_bits)
+            if references is not None and e.seq_id in references:
+                entry.ref_id = idx.add_reference(references[e.seq_id])
+        if not found:
+            raise KeyError(f"no chr entry {chr_id!r} in {path}")   # project_alignments.cc:636-641 exits with this message
+        return idx.commit()
+
+    def entry(self, seq_id: str) -> SequenceEntry:
+        for e in self.entries:
+            if e.seq_id == seq_id:
+                return e
+        raise KeyError(seq_id)
 
     def project_batch(self, batch: RecordBatch, gap_opening_cost: int = 0, gap_extension_cost: int = -1,
                       out: ProjectedBatch | None = None) -> ProjectedBatch:

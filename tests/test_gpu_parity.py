@@ -332,3 +332,30 @@ def test_large_index_parity(gpu, port):
     got = idx.ctx.project_positions(rows, np.zeros(rows.size, np.uint32), pos)
     expp = np.array([oi.project_position(int(a), 0, int(c)) for a, c in zip(rows, pos)], dtype=np.uint64)
     assert np.array_equal(got, expp)
+
+
+def test_index_loaded_from_reference_written_file(gpu, port, workflow_msa):
+    """the index comes from the file the reference's index-msa code wrote (rrr<15> rows expanded by the
+    product's reader) instead of from the MSA; projections must equal the oracle's on the MSA-built index."""
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import sample_reads
+    refs = {name: u.tobytes() for name, u in zip(workflow_msa.names, workflow_msa.ungapped)}
+    idx = MsaIndex.from_file(os.path.join(os.path.dirname(__file__), "golden", "reference_written.msa_index"), "1", refs)
+    assert sorted(e.seq_id for e in idx.entries) == sorted(workflow_msa.names)
+    with pytest.raises(KeyError):
+        MsaIndex.from_file(os.path.join(os.path.dirname(__file__), "golden", "reference_written.msa_index"), "nope")
+    b = sample_reads(workflow_msa, 20000, 150, seed=321, ins=0.003, dele=0.003, clip_frac=0.1)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+    row_of = np.array([idx.entry(n).row for n in workflow_msa.names], dtype=np.uint32)
+    ref_of = np.array([idx.entry(n).ref_id for n in workflow_msa.names], dtype=np.uint32)
+    import copy
+    b2 = copy.copy(b)
+    b2.src_row = row_of[b.src_row]
+    b2.dst_row = row_of[b.dst_row]
+    b2.dst_ref = ref_of[b.dst_ref]
+    assert_same(idx.project_batch(b2), exp, b, "index from file")
+    for name, e in zip(workflow_msa.names, range(len(workflow_msa.names))):
+        src = idx.entry(name)
+        for pos in (0, 1, 77, 5000):
+            assert src.project_position(pos, idx.entry(workflow_msa.names[0])) == oi.project_position(e, 0, pos)
