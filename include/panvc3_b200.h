@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PV3_ABI_VERSION 2
+#define PV3_ABI_VERSION 3
 
 typedef struct pv3_ctx pv3_ctx;
 
@@ -105,7 +105,7 @@ typedef struct {
 	uint64_t launches;       /* kernels launched by the call */
 	uint64_t n_deferred;     /* records the thread-per-record rewrite kernel handed to the warp-per-record kernel */
 	float    ms_rewrite_main;/* the thread-per-record rewrite kernel alone (ms_rewrite also holds the deferred pass) */
-	float    pad_;
+	float    ms_msa_extract; /* last pv3_msa_row_extract[_device]: the extraction kernel alone */
 } pv3_timing;
 
 /* -- lifetime ------------------------------------------------------------------------------------------------------ */
@@ -158,6 +158,17 @@ uint64_t pv3_total_launches(const pv3_ctx *);
 /* -- pinned host memory for batches --------------------------------------------------------------------------------- */
 void *pv3_host_alloc(size_t bytes);
 void  pv3_host_free(void *);
+
+/* -- index-msa on the device --------------------------------------------------------------------------------------------
+ * The per-sequence work of `panvc3 index-msa` (index-msa/index_vector_builder.cc:28-50, driven from
+ * input_processor.cc:155-175): bit i of gap_words = 1 ⇔ text[i] == '-', and every other byte is appended to the unaligned
+ * sequence (what the tool prints as FASTA) — exactly the two inputs pv3_index_add_row / pv3_index_add_ref take, and, with
+ * pv3_index_file_write, the index file. gap_words holds (n + 63) / 64 words; ungapped has capacity n and may be NULL (no
+ * sequence wanted); *n_ungapped receives the number of non-gap bytes. Needs no committed index. The _device variant
+ * takes device pointers (text 16-byte aligned and readable to the next multiple of 16). */
+int pv3_msa_row_extract(pv3_ctx *, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped);
+int pv3_msa_row_extract_device(pv3_ctx *, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped,
+                               uint64_t *n_ungapped /* host */);
 
 /* -- MSA index file (host only, no GPU needed) ---------------------------------------------------------------------------
  * The file `panvc3 index-msa` writes and `project-alignments --msa-index` reads: panvc3::msa_index through

@@ -95,6 +95,29 @@ class OracleLib:
         n = self.lib.pv3o_indel_runs(ops, ops.size, ref_pos, out, ops.size + 1, fin)
         return out[:6 * max(n, 0)].reshape(-1, 6).copy(), fin, int(n)
 
+    def msa_row_extract(self, text, with_sequence: bool = True, chunk: int = 4096):
+        """index-msa's per-sequence work: (gap words, unaligned bytes or None). The port restates
+        index_vector_builder.cc:28-50; the reference build runs the reference's own index_vector_builder in `chunk`-byte
+        pieces (pv3o_msa_row_extract_ref in ref_driver.cc)."""
+        t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        n = int(t.size)
+        words = np.zeros((n + 63) // 64 + 1, dtype=np.uint64)
+        seq = np.zeros(n + 1, dtype=np.uint8) if with_sequence else None
+        n_seq = C.c_uint64(0)
+        sp = seq.ctypes.data if with_sequence else None
+        if self.kind == "reference":
+            fn = self.lib.pv3o_msa_row_extract_ref
+            fn.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+            fn.restype = C.c_int
+            rc = fn(t.ctypes.data, n, chunk, words.ctypes.data, sp, C.byref(n_seq))
+            assert rc == 0, rc
+        else:
+            fn = self.lib.pv3o_msa_row_extract
+            fn.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+            fn.restype = None
+            fn(t.ctypes.data, n, words.ctypes.data, sp, C.byref(n_seq))
+        return words[: (n + 63) // 64].copy(), (seq[: n_seq.value].copy() if with_sequence else None)
+
 
 class OracleIndex:
     def __init__(self, lib: OracleLib, gap_rows, refs):

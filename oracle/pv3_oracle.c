@@ -585,3 +585,15 @@ int pv3o_project_batch(const pv3o_index *idx, uint64_t n,
 	free(results); free(shards); free(tids);
 	return status;
 }
+
+/* ---- index-msa: gap bits + unaligned sequence of one MSA row (index-msa/index_vector_builder.cc:28-50) ---------------- */
+void pv3o_msa_row_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped)
+{
+	uint64_t non_gap = 0;
+	memset(gap_words, 0, ((n + 63) / 64) * 8);
+	for (uint64_t i = 0; i < n; ++i) {
+		if ('-' == text[i]) gap_words[i >> 6] |= 1ull << (i & 63);     /* m_bv[m_pos + i] = 1 */
+		else { if (ungapped) ungapped[non_gap] = text[i]; ++non_gap; } /* std::cout << cc */
+	}
+	if (n_ungapped) *n_ungapped = non_gap;
+}

@@ -78,6 +78,10 @@ int64_t pv3o_indel_runs(const uint32_t *ops, uint64_t n_ops, uint64_t ref_pos, u
 /* The quality LUT (align.hh:28-37 truncated to int32): lut[2*q+0]=match, lut[2*q+1]=mismatch, q=0..41 */
 void pv3o_quality_lut(int32_t *lut84);
 
+/* index-msa, one MSA row: bit i = 1 iff text[i] == '-' (index_vector_builder.cc:28-50), every other byte is copied to the
+ * unaligned sequence in order (:40-43). gap_words: (n + 63) / 64 words; ungapped: capacity n, may be NULL. */
+void pv3o_msa_row_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped);
+
 #ifdef __cplusplus
 }
 #endif

@@ -360,3 +360,43 @@ int pv3o_write_msa_index_file(const char *path, uint64_t n_entries, const char *
 }
 
 } // extern "C"
+
+/* ---- index-msa: gap bits and the unaligned sequence of one MSA row, by the REFERENCE's own builder ----------------------
+ * panvc3::msa_indices::index_vector_builder (index-msa/index_vector_builder.cc:16-63: begin_sequence, update_sequence,
+ * end_sequence), fed in `chunk`-byte pieces as build_index_vector_one_sequence (:66-97) does with st_blksize buffers. The
+ * unaligned FASTA the builder prints to std::cout (">chr/seq\n" + non-gap bytes + "\n", wrap 0) is captured; only the
+ * sequence bytes are returned. gap_words: (n + 63) / 64 words; ungapped: capacity n (may be NULL). Reference build only. */
+#include <index_vector_builder.hh>
+#include <iostream>
+#include <sstream>
+
+extern "C" {
+
+int pv3o_msa_row_extract_ref(const char *text, uint64_t n, uint64_t chunk, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped)
+{
+	bool const want_seq = ungapped != nullptr;
+	panvc3::msa_indices::index_vector_builder builder(want_seq, 0);
+	std::ostringstream captured;
+	std::streambuf *old = std::cout.rdbuf(captured.rdbuf());
+	builder.begin_sequence("c", "s", n);
+	if (!chunk) chunk = 4096;
+	for (uint64_t at = 0; at < n; at += chunk)
+		builder.update_sequence(std::span <char const>(text + at, std::min <uint64_t>(chunk, n - at)));
+	builder.end_sequence();
+	std::cout.rdbuf(old);
+	auto const &bv = builder.destination_bit_vector();
+	if (bv.size() != n) return -1;
+	std::memcpy(gap_words, bv.data(), ((n + 63) / 64) * 8);
+	if (want_seq) {
+		std::string const s = captured.str();
+		std::size_t const hdr = s.find('\n');
+		if (hdr == std::string::npos || s.empty() || s.back() != '\n') return -2;
+		std::size_t const len = s.size() - hdr - 2;
+		if (len > n) return -3;
+		std::memcpy(ungapped, s.data() + hdr + 1, len);
+		if (n_ungapped) *n_ungapped = len;
+	}
+	return 0;
+}
+
+} // extern "C"

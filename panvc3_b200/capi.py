@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = [
     "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_set_kernel_path", "pv3_set_dp_thread_min", "pv3_get_timing",
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
     "pv3_index_file_open", "pv3_index_file_entries", "pv3_index_file_entry", "pv3_index_file_close", "pv3_index_file_write",
-    "pv3_index_file_error",
+    "pv3_index_file_error", "pv3_msa_row_extract", "pv3_msa_row_extract_device",
 ]
 
 
@@ -43,7 +43,7 @@ class BatchOut(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("ms_rewrite", C.c_float), ("ms_realign", C.c_float), ("ms_splice", C.c_float), ("ms_total", C.c_float),
                 ("ms_h2d", C.c_float), ("ms_d2h", C.c_float), ("launches", C.c_uint64), ("n_deferred", C.c_uint64),
-                ("ms_rewrite_main", C.c_float), ("pad_", C.c_float)]
+                ("ms_rewrite_main", C.c_float), ("ms_msa_extract", C.c_float)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -103,6 +103,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_index_file_write.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
                                          C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.pv3_index_file_error.restype = C.c_char_p
+    for fn in (lib.pv3_msa_row_extract, lib.pv3_msa_row_extract_device):
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
     _lib = lib
     return lib
 
@@ -251,6 +253,18 @@ class Context:
         out = np.zeros(xx.size, dtype=np.uint64)
         self._check(self.lib.pv3_index_query(self.h, op, xx.size, _ptr(r), _ptr(xx), _ptr(out)))
         return out
+
+    def msa_row_extract(self, text, with_sequence: bool = True):
+        """index-msa's per-sequence work (index-msa/index_vector_builder.cc:28-50) on the GPU: (gap words, n_bits, unaligned
+        bytes or None) of one aligned row given as bytes / uint8 array."""
+        t = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) else np.ascontiguousarray(text, dtype=np.uint8)
+        n = int(t.size)
+        words = np.zeros((n + 63) // 64, dtype=np.uint64)
+        seq = np.empty(n, dtype=np.uint8) if with_sequence else None
+        n_seq = C.c_uint64(0)
+        self._check(self.lib.pv3_msa_row_extract(self.h, _ptr(t) if n else None, n, _ptr(words) if n else None,
+                                                 _ptr(seq) if with_sequence else None, C.byref(n_seq)))
+        return words, n, (seq[: n_seq.value] if with_sequence else None)
 
     def timing(self) -> dict:
         t = Timing()

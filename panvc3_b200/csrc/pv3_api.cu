@@ -83,6 +83,7 @@ struct pv3_ctx {
 
 	// device work buffers
 	DevBuf       counters, jobs, dp_arena, pool, deferred, big_list, d_packed, d_job_qual_off;
+	DevBuf       ex_text, ex_words, ex_seq, ex_status;   // pv3_msa_row_extract
 	Job         *h_jobs = nullptr; uint64_t *h_job_qual_off = nullptr; uint64_t h_jobs_cap = 0;   // pinned (lazy QUAL)
 	uint8_t     *h_packed = nullptr; uint64_t h_packed_cap = 0;
 	Counters    *h_counters = nullptr;   // pinned
@@ -164,6 +165,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->big_list, &ctx->d_packed, &ctx->d_job_qual_off,
+			&ctx->ex_text, &ctx->ex_words, &ctx->ex_seq, &ctx->ex_status,
 			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
 			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
@@ -788,6 +790,49 @@ int pv3_index_query(pv3_ctx *ctx, int op, uint64_t n, const uint32_t *row, const
 	ctx->total_launches += 1;
 	PV3_CUDA(ctx, cudaMemcpyAsync(out, ctx->out_dst_pos.p, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PV3_OK;
+}
+
+// index-msa's per-sequence work (index-msa/index_vector_builder.cc:28-50) on device-resident text
+int pv3_msa_row_extract_device(pv3_ctx *ctx, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	cudaSetDevice(ctx->device);
+	if (n && (!text || !gap_words)) return fail(ctx, PV3_ERR_INVALID, "pv3_msa_row_extract_device: NULL argument");
+	if ((uintptr_t) text % 16 || (uintptr_t) gap_words % 8 || (uintptr_t) ungapped % 4)
+		return fail(ctx, PV3_ERR_INVALID, "pv3_msa_row_extract_device: text must be 16-byte, gap_words 8-byte, ungapped 4-byte aligned");
+	PV3_CUDA(ctx, ctx->ex_status.ensure(msa_extract_scratch_words(n) * 8));
+	unsigned launches = 0;
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
+	PV3_CUDA(ctx, launch_msa_extract(text, n, gap_words, ungapped, ctx->ex_status.as <unsigned long long>(), ctx->stream, &launches));
+	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[6], ctx->stream));
+	ctx->total_launches += launches;
+	unsigned long long total = 0;
+	PV3_CUDA(ctx, cudaMemcpyAsync(&total, ctx->ex_status.as <unsigned long long>() + msa_extract_total_word(n), 8, cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	cudaEventElapsedTime(&ctx->timing.ms_msa_extract, ctx->ev[5], ctx->ev[6]);
+	if (n_ungapped) *n_ungapped = ungapped ? total : 0;
+	return PV3_OK;
+}
+
+int pv3_msa_row_extract(pv3_ctx *ctx, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	cudaSetDevice(ctx->device);
+	if (n && (!text || !gap_words)) return fail(ctx, PV3_ERR_INVALID, "pv3_msa_row_extract: NULL argument");
+	if (n_ungapped) *n_ungapped = 0;
+	if (!n) return PV3_OK;
+	uint64_t const n_words = (n + 63) / 64;
+	PV3_CUDA(ctx, ctx->ex_text.ensure(n + 16)); PV3_CUDA(ctx, ctx->ex_words.ensure(n_words * 8));
+	if (ungapped) PV3_CUDA(ctx, ctx->ex_seq.ensure(n + 16));
+	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->ex_text.p, text, n, cudaMemcpyHostToDevice, ctx->stream));
+	uint64_t total = 0;
+	int st = pv3_msa_row_extract_device(ctx, ctx->ex_text.as <char>(), n, ctx->ex_words.as <uint64_t>(), ungapped ? ctx->ex_seq.as <char>() : nullptr, &total);
+	if (st) return st;
+	PV3_CUDA(ctx, cudaMemcpyAsync(gap_words, ctx->ex_words.p, n_words * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (ungapped && total) PV3_CUDA(ctx, cudaMemcpyAsync(ungapped, ctx->ex_seq.p, total, cudaMemcpyDeviceToHost, ctx->stream));
+	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	if (n_ungapped) *n_ungapped = total;
 	return PV3_OK;
 }
 

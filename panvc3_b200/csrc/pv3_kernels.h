@@ -88,6 +88,13 @@ void launch_positions(const RowDesc *rows, uint32_t n_rows, uint64_t n, const ui
 	const uint64_t *pos, uint64_t *out, cudaStream_t stream);
 void launch_index_query(const RowDesc *rows, uint32_t n_rows, int op, uint64_t n, const uint32_t *row, const uint64_t *x,
 	uint64_t *out, cudaStream_t stream);
+// index-msa on the device (pv3_msa_build.cu): scratch of msa_extract_scratch_words(n) words; word msa_extract_total_word(n)
+// receives the non-gap count
+uint64_t msa_extract_tiles(uint64_t n);
+uint64_t msa_extract_scratch_words(uint64_t n);
+uint64_t msa_extract_total_word(uint64_t n);
+cudaError_t launch_msa_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, unsigned long long *scratch,
+	cudaStream_t stream, unsigned *launches);
 uint64_t k3_default_grid_warps(int n_sms);
 uint32_t k3_smem_pool_bytes();
 

@@ -95,6 +95,15 @@ class MsaIndex:
         words, n = bits_from_aligned_row(aligned_row)
         return self.add_entry(seq_id, words, n)
 
+    def add_entry_from_text(self, seq_id: str, text: bytes, with_reference: bool = True) -> SequenceEntry:
+        """index-msa on the device: gap bits and the unaligned contig of one aligned row in one pass over its text
+        (index-msa/index_vector_builder.cc:28-50); the contig id lands in SequenceEntry.ref_id."""
+        words, n, seq = self.ctx.msa_row_extract(text, with_reference)
+        e = self.add_entry(seq_id, words, n)
+        if with_reference:
+            e.ref_id = self.add_reference(seq.tobytes())
+        return e
+
     def add_reference(self, bases: bytes | str) -> int:
         if isinstance(bases, str):
             bases = bases.encode()

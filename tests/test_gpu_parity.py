@@ -359,3 +359,58 @@ def test_index_loaded_from_reference_written_file(gpu, port, workflow_msa):
         src = idx.entry(name)
         for pos in (0, 1, 77, 5000):
             assert src.project_position(pos, idx.entry(workflow_msa.names[0])) == oi.project_position(e, 0, pos)
+
+
+# ---------------------------------------------------------------------------------------------- index-msa on the device
+def _msa_text(rng, n, gap_p):
+    alphabet = np.frombuffer(b"ACGTNacgtn.*\n", dtype=np.uint8)
+    t = alphabet[rng.choice(len(alphabet), size=n, p=np.array([20, 20, 20, 20, 3, 2, 2, 2, 2, 1, 1, 1, 1]) / 95)]
+    gaps = (np.cumsum(rng.random(n) < 0.03) % 2 == 1) if gap_p is None else (rng.random(n) < gap_p)
+    t = t.copy(); t[gaps] = ord("-")
+    return t
+
+
+@pytest.mark.parametrize("n,gap_p", [(0, None), (1, 1.0), (1, 0.0), (15, 0.5), (16, 0.5), (17, None), (63, 0.5), (64, 1.0), (511, None),
+                                     (16383, None), (16384, 0.0), (16385, 1.0), (16384 * 3 + 5, 0.5), (1_000_003, None),
+                                     (1_000_003, 0.999), (20_000_001, 0.02)])
+def test_msa_row_extract_matches_oracle(gpu, port, n, gap_p):
+    """index-msa/index_vector_builder.cc:28-50 on the device: gap words and unaligned sequence, bit- and byte-exact; sizes
+    around the 16-byte load, the 512-byte warp segment and the 16 KiB tile, all-gap and gap-free rows, many tiles (the
+    look-back chain)."""
+    from panvc3_b200.capi import Context
+    ctx = Context(0)
+    t = _msa_text(np.random.default_rng(n + 17), n, gap_p)
+    ew, es = port.msa_row_extract(t)
+    for rep in range(2):                                      # second call reuses the work buffers
+        w, nb, s = ctx.msa_row_extract(t)
+        assert nb == n
+        np.testing.assert_array_equal(w, ew)
+        np.testing.assert_array_equal(s, es)
+    w2, _, s2 = ctx.msa_row_extract(t.tobytes(), with_sequence=False)
+    assert s2 is None
+    np.testing.assert_array_equal(w2, ew)
+
+
+def test_index_built_from_msa_text_on_device(gpu, port, workflow_msa):
+    """The whole N2 chain on the product side: MSA text → (device) gap rows + contigs → index → projections equal the
+    oracle's; and → index file bytes equal to the file the reference's serialiser wrote for the same MSA."""
+    from panvc3_b200.index_file import IndexFileEntry, read_index_file, write_index_file
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import sample_reads
+    idx = MsaIndex(0)
+    for name, row in zip(workflow_msa.names, workflow_msa.rows):
+        e = idx.add_entry_from_text(name, np.ascontiguousarray(row, dtype=np.uint8).tobytes())
+        assert e.row == e.ref_id == workflow_msa.names.index(name)
+    idx.commit()
+    b = sample_reads(workflow_msa, 20000, 150, seed=55, ins=0.003, dele=0.003, clip_frac=0.1)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    assert_same(idx.project_batch(b), oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1), b, "index from text")
+    golden = os.path.join(os.path.dirname(__file__), "golden", "reference_written.msa_index")
+    ents = [e for e in read_index_file(golden) if e.chr_id != "1"]
+    for name, row in zip(workflow_msa.names, workflow_msa.rows):
+        w, n, _ = idx.ctx.msa_row_extract(np.ascontiguousarray(row, dtype=np.uint8), with_sequence=False)
+        ents.append(IndexFileEntry("1", name, w, n))
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        write_index_file(os.path.join(d, "x"), ents)
+        assert open(os.path.join(d, "x"), "rb").read() == open(golden, "rb").read()

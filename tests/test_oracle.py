@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 import casegen
-from panvc3_b200.batch import RecordBatch, bits_from_aligned_row, format_cigar, parse_cigar
+from panvc3_b200.batch import RecordBatch, bits_from_aligned_row, format_cigar, pack_bits, parse_cigar
 from parity import assert_same, load_golden_random
 
 
@@ -128,3 +128,28 @@ def test_port_flags_error_cases(port):
     for rec, flag in cases:
         o = idx.project_batch(RecordBatch.from_records([rec]))
         assert int(o.flags[0]) == flag, (rec, int(o.flags[0]))
+
+
+# ---------------------------------------------------------------------------------------------- index-msa row builder
+def _msa_text(rng, n, gap_p):
+    """An aligned row: gap runs (state flips) over ACGTN bytes, with a few lower-case and odd bytes as a2m files have."""
+    alphabet = np.frombuffer(b"ACGTNacgtn.*\n", dtype=np.uint8)
+    t = alphabet[rng.choice(len(alphabet), size=n, p=np.array([20, 20, 20, 20, 3, 2, 2, 2, 2, 1, 1, 1, 1]) / 95)]
+    gaps = (np.cumsum(rng.random(n) < 0.03) % 2 == 1) if gap_p is None else (rng.random(n) < gap_p)
+    t = t.copy(); t[gaps] = ord("-")
+    return t
+
+
+@pytest.mark.parametrize("n,gap_p,chunk", [(0, 0.5, 4096), (1, 1.0, 1), (1, 0.0, 4096), (63, 0.5, 7), (64, 0.5, 64), (65, None, 4096),
+                                           (4096, None, 4096), (4097, 0.9, 4096), (100000, None, 4096), (100000, 0.0, 65536)])
+def test_msa_row_extract_port_matches_reference_builder(port, ref, n, gap_p, chunk):
+    """The port (index_vector_builder.cc:28-50 restated) against the reference's own index_vector_builder, fed in chunks
+    as build_index_vector_one_sequence does."""
+    t = _msa_text(np.random.default_rng(n * 31 + chunk), n, gap_p)
+    pw, ps = port.msa_row_extract(t)
+    rw, rs = ref.msa_row_extract(t, chunk=chunk)
+    np.testing.assert_array_equal(pw, rw)
+    np.testing.assert_array_equal(ps, rs)
+    np.testing.assert_array_equal(pw, pack_bits(t == ord("-"))[: pw.size])
+    np.testing.assert_array_equal(ps, t[t != ord("-")])
+    assert np.array_equal(port.msa_row_extract(t, with_sequence=False)[0], pw)
