@@ -159,6 +159,35 @@ uint64_t pv3_total_launches(const pv3_ctx *);
 void *pv3_host_alloc(size_t bytes);
 void  pv3_host_free(void *);
 
+/* -- record annotation text ------------------------------------------------------------------------------
+ * The OA entry project_task::process appends to every projected record (project-alignments/project_alignments.cc:803-845):
+ *     RNAME ',' POS ',' ('-' if FLAG & 0x10 else '+') ',' CIGAR ',' MAPQ ',' [NM] ';'
+ * with POS printed as the reference holds it (seqan3's 0-based reference_position), the ORIGINAL CIGAR as decimal count +
+ * op char, and NM only when the record had the tag. One string per record into a text arena: record i is
+ * text[text_off[i] .. text_off[i+1]), no terminators. Host buffers. PV3_ERR_CAPACITY (with *text_used = bytes needed) when
+ * text_cap is too small; calling with text_cap = 0 is the way to size the buffer. */
+typedef struct {
+	uint64_t        n;
+	const uint32_t *ref_id;    /* [n] RNAME of the source record as an index into the name table (ref_ids[ref_id], :812) */
+	const uint64_t *pos;       /* [n] src_pos (:815) */
+	const uint16_t *flag;      /* [n] SAM FLAG; only on_reverse_strand (0x10) is read (:819) */
+	const uint8_t  *mapq;      /* [n] (:830) */
+	const int32_t  *nm;        /* [n] original NM value (:835) */
+	const uint8_t  *has_nm;    /* [n] 0 = the record had no NM tag; NULL = no record has one */
+	const uint64_t *cig_off;   /* [n+1] */
+	const uint32_t *cig;       /* BAM-packed ops of the ORIGINAL alignment (the same arrays as pv3_batch_in) */
+	uint32_t        n_names;
+	const uint64_t *name_off;  /* [n_names+1] */
+	const char     *names;     /* header reference names, concatenated */
+} pv3_oa_in;
+int pv3_format_oa(pv3_ctx *, const pv3_oa_in *in, uint64_t *text_off /* [n+1] */, char *text, uint64_t text_cap,
+                  uint64_t *text_used);
+/* SAM text of n CIGARs (count + op char per op; an empty CIGAR gives an empty string, the caller prints '*'). Record i is
+ * cig[cig_off[i] .. +cig_len[i]) — the (off, len) addressing of pv3_batch_out — or, with cig_len == NULL,
+ * cig[cig_off[i] .. cig_off[i+1]). n_cig_words = size of the cig array. */
+int pv3_format_cigars(pv3_ctx *, uint64_t n, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
+                      uint64_t n_cig_words, uint64_t *text_off /* [n+1] */, char *text, uint64_t text_cap, uint64_t *text_used);
+
 /* -- index-msa on the device --------------------------------------------------------------------------------------------
  * The per-sequence work of `panvc3 index-msa` (index-msa/index_vector_builder.cc:28-50, driven from
  * input_processor.cc:155-175): bit i of gap_words = 1 ⇔ text[i] == '-', and every other byte is appended to the unaligned

@@ -95,6 +95,29 @@ class OracleLib:
         n = self.lib.pv3o_indel_runs(ops, ops.size, ref_pos, out, ops.size + 1, fin)
         return out[:6 * max(n, 0)].reshape(-1, 6).copy(), fin, int(n)
 
+    def format_oa(self, ref_id, pos, flag, mapq, nm, has_nm, cig_off, cig, names, cig_len=None):
+        """OA entries (project_alignments.cc:803-845); ref_id None ⇒ CIGAR text only. Returns (text bytes, offsets). Port only."""
+        fn = self.lib.pv3o_format_oa
+        fn.argtypes = [C.c_uint64] + [C.c_void_p] * 9 + [C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+        fn.restype = C.c_uint64
+        cig_off = np.ascontiguousarray(cig_off, dtype=np.uint64)
+        cig = np.ascontiguousarray(cig, dtype=np.uint32)
+        n = cig_off.size - (0 if cig_len is not None else 1)
+        p = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)
+        arrs = [p(ref_id, np.uint32), p(pos, np.uint64), p(flag, np.uint16), p(mapq, np.uint8), p(nm, np.int32), p(has_nm, np.uint8),
+                cig_off, p(cig_len, np.uint32), cig]
+        blob = b"".join(names) if names else b""
+        noff = np.zeros(len(names or []) + 1, dtype=np.uint64)
+        if names:
+            noff[1:] = np.cumsum([len(x) for x in names])
+        nb = np.frombuffer(blob, dtype=np.uint8) if blob else np.zeros(1, np.uint8)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        ptr = lambda a: None if a is None else a.ctypes.data
+        need = fn(n, *[ptr(a) for a in arrs], len(names or []), noff.ctypes.data, nb.ctypes.data, off.ctypes.data, None, 0)
+        text = np.zeros(max(int(need), 1), dtype=np.uint8)
+        fn(n, *[ptr(a) for a in arrs], len(names or []), noff.ctypes.data, nb.ctypes.data, off.ctypes.data, text.ctypes.data, need)
+        return text[:need].tobytes(), off
+
     def msa_row_extract(self, text, with_sequence: bool = True, chunk: int = 4096):
         """index-msa's per-sequence work: (gap words, unaligned bytes or None). The port restates
         index_vector_builder.cc:28-50; the reference build runs the reference's own index_vector_builder in `chunk`-byte

@@ -597,3 +597,38 @@ void pv3o_msa_row_extract(const char *text, uint64_t n, uint64_t *gap_words, cha
 	}
 	if (n_ungapped) *n_ungapped = non_gap;
 }
+
+/* ---- OA entry / CIGAR text of a record (project-alignments/project_alignments.cc:803-845) -----------------------------
+ * PARITY UNPINNED: the code restated here sits inside project_task::process of the CLI, which cannot be compiled in this
+ * container (seqan3 SAM I/O + libdispatch + Boost); the port follows the source line by line (ostringstream << of an
+ * std::string, std::uint64_t, char, std::uint32_t + cigar op char, int, std::int32_t). Returns the bytes written (or
+ * needed when cap is too small: nothing is written past cap). ref_id == NULL ⇒ CIGAR text only. */
+#include <stdio.h>
+uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos, const uint16_t *flag, const uint8_t *mapq,
+	const int32_t *nm, const uint8_t *has_nm, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
+	uint32_t n_names, const uint64_t *name_off, const char *names, uint64_t *text_off, char *text, uint64_t cap)
+{
+	uint64_t at = 0;
+	char buf[64];
+	#define PUT(ptr, len) do { uint64_t l_ = (len); if (at + l_ <= cap) memcpy(text + at, (ptr), l_); at += l_; } while (0)
+	for (uint64_t i = 0; i < n; ++i) {
+		text_off[i] = at;
+		if (ref_id) {
+			if (ref_id[i] < n_names) PUT(names + name_off[ref_id[i]], name_off[ref_id[i] + 1] - name_off[ref_id[i]]);   /* :812 */
+			PUT(",", 1);
+			PUT(buf, (uint64_t) snprintf(buf, sizeof buf, "%llu,", (unsigned long long) pos[i]));                          /* :815 */
+			PUT((flag[i] & 0x10) ? "-," : "+,", 2);                                                                     /* :819 */
+		}
+		uint64_t const c0 = cig_off[i], c1 = cig_len ? c0 + cig_len[i] : cig_off[i + 1];
+		for (uint64_t c = c0; c < c1; ++c)                                                                              /* :822-826 */
+			PUT(buf, (uint64_t) snprintf(buf, sizeof buf, "%u%c", cig[c] >> 4, "MIDNSHP=X???????"[cig[c] & 15]));
+		if (ref_id) {
+			PUT(buf, (uint64_t) snprintf(buf, sizeof buf, ",%d,", (int) mapq[i]));                                        /* :827-830 */
+			if (has_nm && has_nm[i]) PUT(buf, (uint64_t) snprintf(buf, sizeof buf, "%d", (int) nm[i]));                   /* :834-835 */
+			PUT(";", 1);                                                                                                /* :838 */
+		}
+	}
+	#undef PUT
+	text_off[n] = at;
+	return at;
+}

@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = [
     "pv3_project_device", "pv3_project_positions", "pv3_index_query", "pv3_set_stage", "pv3_set_kernel_path", "pv3_set_dp_thread_min", "pv3_get_timing",
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
     "pv3_index_file_open", "pv3_index_file_entries", "pv3_index_file_entry", "pv3_index_file_close", "pv3_index_file_write",
-    "pv3_index_file_error", "pv3_msa_row_extract", "pv3_msa_row_extract_device",
+    "pv3_index_file_error", "pv3_msa_row_extract", "pv3_msa_row_extract_device", "pv3_format_oa", "pv3_format_cigars",
 ]
 
 
@@ -38,6 +38,12 @@ class BatchOut(C.Structure):
                 ("rr", C.c_void_p), ("rr_cap", C.c_uint64),
                 ("cig_used", C.c_uint64), ("rr_used", C.c_uint64), ("n_flagged", C.c_uint64),
                 ("n_realigned", C.c_uint64), ("dp_cells", C.c_uint64)]
+
+
+class OaIn(C.Structure):
+    _fields_ = [("n", C.c_uint64), ("ref_id", C.c_void_p), ("pos", C.c_void_p), ("flag", C.c_void_p), ("mapq", C.c_void_p),
+                ("nm", C.c_void_p), ("has_nm", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p),
+                ("n_names", C.c_uint32), ("name_off", C.c_void_p), ("names", C.c_void_p)]
 
 
 class Timing(C.Structure):
@@ -103,6 +109,9 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_index_file_write.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
                                          C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.pv3_index_file_error.restype = C.c_char_p
+    lib.pv3_format_oa.argtypes = [C.c_void_p, C.POINTER(OaIn), C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.pv3_format_cigars.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                      C.c_uint64, C.POINTER(C.c_uint64)]
     for fn in (lib.pv3_msa_row_extract, lib.pv3_msa_row_extract_device):
         fn.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
     _lib = lib
@@ -253,6 +262,44 @@ class Context:
         out = np.zeros(xx.size, dtype=np.uint64)
         self._check(self.lib.pv3_index_query(self.h, op, xx.size, _ptr(r), _ptr(xx), _ptr(out)))
         return out
+
+    def format_oa(self, ref_id, pos, flag, mapq, nm, has_nm, cig_off, cig, names: list[bytes]):
+        """OA entries of a batch (project_alignments.cc:803-845): (text bytes, offsets[n + 1]). Sizes the arena with a first
+        call at capacity 0, as the header describes."""
+        a = dict(ref_id=np.ascontiguousarray(ref_id, dtype=np.uint32), pos=np.ascontiguousarray(pos, dtype=np.uint64),
+                 flag=np.ascontiguousarray(flag, dtype=np.uint16), mapq=np.ascontiguousarray(mapq, dtype=np.uint8),
+                 nm=None if nm is None else np.ascontiguousarray(nm, dtype=np.int32),
+                 has_nm=None if has_nm is None else np.ascontiguousarray(has_nm, dtype=np.uint8),
+                 cig_off=np.ascontiguousarray(cig_off, dtype=np.uint64), cig=np.ascontiguousarray(cig, dtype=np.uint32))
+        n = a["ref_id"].size
+        blob = np.frombuffer(b"".join(names) or b"\0", dtype=np.uint8)
+        noff = np.zeros(len(names) + 1, dtype=np.uint64)
+        if names:
+            noff[1:] = np.cumsum([len(x) for x in names])
+        oa = OaIn(n, *[_ptr(a[k]) for k in ("ref_id", "pos", "flag", "mapq", "nm", "has_nm", "cig_off", "cig")], len(names), _ptr(noff), _ptr(blob))
+        off = np.zeros(n + 1, dtype=np.uint64)
+        used = C.c_uint64(0)
+        rc = self.lib.pv3_format_oa(self.h, C.byref(oa), _ptr(off), None, 0, C.byref(used))
+        if rc not in (0, -3):
+            self._check(rc)
+        text = np.zeros(max(int(used.value), 1), dtype=np.uint8)
+        self._check(self.lib.pv3_format_oa(self.h, C.byref(oa), _ptr(off), _ptr(text), used.value, C.byref(used)))
+        return text[: used.value].tobytes(), off
+
+    def format_cigars(self, cig_off, cig, cig_len=None):
+        """SAM text of CIGARs addressed as in a ProjectedBatch (off, len) or by consecutive offsets."""
+        off_in = np.ascontiguousarray(cig_off, dtype=np.uint64)
+        ln = None if cig_len is None else np.ascontiguousarray(cig_len, dtype=np.uint32)
+        cg = np.ascontiguousarray(cig, dtype=np.uint32)
+        n = off_in.size - (0 if ln is not None else 1)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        used = C.c_uint64(0)
+        rc = self.lib.pv3_format_cigars(self.h, n, _ptr(off_in), _ptr(ln), _ptr(cg), cg.size, _ptr(off), None, 0, C.byref(used))
+        if rc not in (0, -3):
+            self._check(rc)
+        text = np.zeros(max(int(used.value), 1), dtype=np.uint8)
+        self._check(self.lib.pv3_format_cigars(self.h, n, _ptr(off_in), _ptr(ln), _ptr(cg), cg.size, _ptr(off), _ptr(text), used.value, C.byref(used)))
+        return text[: used.value].tobytes(), off
 
     def msa_row_extract(self, text, with_sequence: bool = True):
         """index-msa's per-sequence work (index-msa/index_vector_builder.cc:28-50) on the GPU: (gap words, n_bits, unaligned

@@ -84,6 +84,7 @@ struct pv3_ctx {
 	// device work buffers
 	DevBuf       counters, jobs, dp_arena, pool, deferred, big_list, d_packed, d_job_qual_off;
 	DevBuf       ex_text, ex_words, ex_seq, ex_status;   // pv3_msa_row_extract
+	DevBuf       an[16];                                 // pv3_format_oa / pv3_format_cigars
 	Job         *h_jobs = nullptr; uint64_t *h_job_qual_off = nullptr; uint64_t h_jobs_cap = 0;   // pinned (lazy QUAL)
 	uint8_t     *h_packed = nullptr; uint64_t h_packed_cap = 0;
 	Counters    *h_counters = nullptr;   // pinned
@@ -170,6 +171,7 @@ void pv3_destroy(pv3_ctx *ctx)
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
 			&ctx->out_arena, &ctx->out_rr_off, &ctx->out_rr_len, &ctx->out_rr })
 		b->release();
+	for (auto &b : ctx->an) b.release();
 	if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
 	if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
 	if (ctx->h_job_qual_off) cudaFreeHost(ctx->h_job_qual_off);
@@ -834,6 +836,106 @@ int pv3_msa_row_extract(pv3_ctx *ctx, const char *text, uint64_t n, uint64_t *ga
 	PV3_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	if (n_ungapped) *n_ungapped = total;
 	return PV3_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// Host buffers in, text + offsets out. P holds HOST pointers on entry (cig_len may be null, ref_id null ⇒ CIGAR text only).
+int format_text(pv3_ctx *ctx, const char *who, OaParams P, uint64_t n_cig_words, uint64_t names_bytes,
+	uint64_t *text_off, char *text, uint64_t text_cap, uint64_t *text_used)
+{
+	cudaSetDevice(ctx->device);
+	if (text_used) *text_used = 0;
+	if (!text_off) return fail(ctx, PV3_ERR_INVALID, "%s: NULL text_off", who);
+	text_off[0] = 0;
+	uint64_t const n = P.n;
+	if (!n) return PV3_OK;
+	cudaStream_t const st = ctx->stream;
+	int slot = 0;
+	auto up = [&](const void *src, size_t bytes, const void **dev) -> cudaError_t {
+		DevBuf &b = ctx->an[slot++];
+		cudaError_t e = b.ensure(bytes + 16);
+		if (e != cudaSuccess) return e;
+		*dev = b.p;
+		return bytes ? cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+	};
+	auto scratch = [&](size_t bytes, void **dev) -> cudaError_t {
+		DevBuf &b = ctx->an[slot++];
+		cudaError_t e = b.ensure(bytes + 16);
+		*dev = b.p;
+		return e;
+	};
+	OaParams D = P;
+	if (P.ref_id) {
+		PV3_CUDA(ctx, up(P.ref_id, n * 4, (const void **) &D.ref_id));
+		PV3_CUDA(ctx, up(P.pos, n * 8, (const void **) &D.pos));
+		PV3_CUDA(ctx, up(P.flag, n * 2, (const void **) &D.flag));
+		PV3_CUDA(ctx, up(P.mapq, n, (const void **) &D.mapq));
+		if (P.has_nm) {
+			PV3_CUDA(ctx, up(P.nm, n * 4, (const void **) &D.nm));
+			PV3_CUDA(ctx, up(P.has_nm, n, (const void **) &D.has_nm));
+		} else slot += 2;
+		PV3_CUDA(ctx, up(P.name_off, ((size_t) P.n_names + 1) * 8, (const void **) &D.name_off));
+		PV3_CUDA(ctx, up(P.names, names_bytes, (const void **) &D.names));
+	} else slot += 8;
+	PV3_CUDA(ctx, up(P.cig_off, (n + (P.cig_len ? 0 : 1)) * 8, (const void **) &D.cig_off));
+	if (P.cig_len) PV3_CUDA(ctx, up(P.cig_len, n * 4, (const void **) &D.cig_len)); else ++slot;
+	PV3_CUDA(ctx, up(P.cig, n_cig_words * 4, (const void **) &D.cig));
+	unsigned const ctas = oa_ctas(n);
+	PV3_CUDA(ctx, scratch(n * 4, (void **) &D.len));
+	PV3_CUDA(ctx, scratch(((size_t) ctas + 4) * 4, (void **) &D.cta_len));
+	PV3_CUDA(ctx, scratch(((size_t) ctas + 1) * 8, (void **) &D.cta_off));
+	PV3_CUDA(ctx, scratch((n + 1) * 8, (void **) &D.text_off));
+	launch_oa_lengths(D, st);
+	launch_scan_u32(D.cta_len, ctas, D.cta_off, st);
+	PV3_CUDA(ctx, cudaGetLastError());
+	unsigned long long total = 0;
+	PV3_CUDA(ctx, cudaMemcpyAsync(&total, D.cta_off + ctas, 8, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaStreamSynchronize(st));
+	ctx->total_launches += 2;
+	if (text_used) *text_used = total;
+	if (total > text_cap) return fail(ctx, PV3_ERR_CAPACITY, "%s: text needs %llu bytes, capacity is %llu", who, total, (unsigned long long) text_cap);
+	if (total && !text) return fail(ctx, PV3_ERR_INVALID, "%s: NULL text", who);
+	PV3_CUDA(ctx, scratch(total, (void **) &D.text));
+	launch_oa_write(D, st);
+	PV3_CUDA(ctx, cudaGetLastError());
+	ctx->total_launches += 1;
+	PV3_CUDA(ctx, cudaMemcpyAsync(text_off, D.text_off, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+	if (total) PV3_CUDA(ctx, cudaMemcpyAsync(text, D.text, total, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaStreamSynchronize(st));
+	return PV3_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int pv3_format_oa(pv3_ctx *ctx, const pv3_oa_in *in, uint64_t *text_off, char *text, uint64_t text_cap, uint64_t *text_used)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	if (!in) return fail(ctx, PV3_ERR_INVALID, "pv3_format_oa: NULL argument");
+	if (in->n && (!in->ref_id || !in->pos || !in->flag || !in->mapq || !in->cig_off || (in->has_nm && !in->nm) || !in->name_off))
+		return fail(ctx, PV3_ERR_INVALID, "pv3_format_oa: NULL array");
+	OaParams P;
+	memset(&P, 0, sizeof P);
+	P.n = in->n; P.ref_id = in->ref_id; P.pos = in->pos; P.flag = in->flag; P.mapq = in->mapq; P.nm = in->nm; P.has_nm = in->has_nm;
+	P.cig_off = in->cig_off; P.cig = in->cig; P.n_names = in->n_names; P.name_off = in->name_off; P.names = in->names;
+	uint64_t const n_cig = in->n ? in->cig_off[in->n] : 0;
+	uint64_t const names_bytes = in->n_names ? in->name_off[in->n_names] : 0;
+	return format_text(ctx, "pv3_format_oa", P, n_cig, names_bytes, text_off, text, text_cap, text_used);
+}
+
+int pv3_format_cigars(pv3_ctx *ctx, uint64_t n, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig, uint64_t n_cig_words,
+	uint64_t *text_off, char *text, uint64_t text_cap, uint64_t *text_used)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	if (n && !cig_off) return fail(ctx, PV3_ERR_INVALID, "pv3_format_cigars: NULL array");
+	OaParams P;
+	memset(&P, 0, sizeof P);
+	P.n = n; P.cig_off = cig_off; P.cig_len = cig_len; P.cig = cig;
+	return format_text(ctx, "pv3_format_cigars", P, n_cig_words, 0, text_off, text, text_cap, text_used);
 }
 
 int pv3_get_timing(const pv3_ctx *ctx, pv3_timing *out)

@@ -95,6 +95,33 @@ uint64_t msa_extract_scratch_words(uint64_t n);
 uint64_t msa_extract_total_word(uint64_t n);
 cudaError_t launch_msa_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, unsigned long long *scratch,
 	cudaStream_t stream, unsigned *launches);
+// exclusive scan of 32-bit counts into 64-bit offsets, one CTA (cnt 16-byte aligned and padded to a multiple of four; off[n] = total)
+void launch_scan_u32(const uint32_t *cnt, uint64_t n, unsigned long long *off, cudaStream_t stream);
+
+// Record annotation text (pv3_annotate.cu): the OA entry of a record, or the SAM text of a CIGAR
+struct OaParams {
+	uint64_t        n;
+	const uint32_t *ref_id;      // null ⇒ CIGAR text only
+	const uint64_t *pos;
+	const uint16_t *flag;
+	const uint8_t  *mapq;
+	const int32_t  *nm;
+	const uint8_t  *has_nm;      // may be null
+	const uint64_t *cig_off;     // [n] (with cig_len) or [n + 1]
+	const uint32_t *cig_len;     // null ⇒ cig_off[i + 1] - cig_off[i]
+	const uint32_t *cig;
+	uint32_t        n_names;
+	const uint64_t *name_off;
+	const char     *names;
+	uint32_t       *len;         // [n] scratch: text length of every record
+	uint32_t       *cta_len;     // [ceil(n / 256)] padded to 4
+	unsigned long long *cta_off; // [ceil(n / 256) + 1]
+	uint64_t       *text_off;    // [n + 1]
+	char           *text;
+};
+unsigned oa_ctas(uint64_t n);
+void launch_oa_lengths(const OaParams &P, cudaStream_t stream);   // len, cta_len
+void launch_oa_write(const OaParams &P, cudaStream_t stream);     // text_off, text (after launch_scan_u32 over cta_len)
 uint64_t k3_default_grid_warps(int n_sms);
 uint32_t k3_smem_pool_bytes();
 

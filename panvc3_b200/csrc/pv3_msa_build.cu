@@ -222,6 +222,12 @@ msa_compact_kernel(const uint32_t *__restrict__ text, uint64_t n, uint64_t n_til
 	else msa_compact_tile <false>(text, n, tile, ungapped, tile_off, comp, seg_cnt, sel_lut);
 }
 
+// cnt: 16-byte aligned, readable up to the next multiple of four entries; off: n + 1 entries
+void launch_scan_u32(const uint32_t *cnt, uint64_t n, unsigned long long *off, cudaStream_t stream)
+{
+	msa_scan_kernel<<<1, 1024, 0, stream>>>((const uint4 *) cnt, n, off);
+}
+
 uint64_t msa_extract_tiles(uint64_t n) { return (n + EX_TILE - 1) / EX_TILE; }
 
 // scratch: msa_extract_scratch_words(n) 64-bit words, 16-byte aligned — the 32-bit tile counts (padded to a multiple of

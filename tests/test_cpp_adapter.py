@@ -67,3 +67,31 @@ def test_adapter_reproduces_reference_tables(tmp_path, fixtures_json):
         n_runs += len(exp["ranges"])
     assert out[len(expected)] == "ERROR 4"                      # PV3_FLAG_QUERY_OOB → projection_error
     assert out[-1] == f"DELEGATE {n_runs} {n_runs}"
+
+
+def build_annotator_test(tmpdir) -> str:
+    from panvc3_b200 import build
+    build.build()
+    exe = os.path.join(str(tmpdir), "annotator_test")
+    libdir = os.path.join(ROOT, "panvc3_b200")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", f"-I{ROOT}/include", "-o", exe, os.path.join(CPP, "annotator_test.cc"),
+                    f"-L{libdir}", "-lpanvc3_b200", f"-Wl,-rpath,{libdir}"], check=True)
+    return exe
+
+
+def test_record_annotator_host_logic(tmp_path):
+    """Tag filter against the preserved set, realigned-range tag arrays, record index (project_alignments.cc:774-800, 848-868)."""
+    res = subprocess.run([build_annotator_test(tmp_path)], capture_output=True, text=True, timeout=60)
+    assert res.returncode == 0 and res.stdout.strip() == "ok", res.stderr
+
+
+@pytest.mark.gpu
+def test_record_annotator_oa_entries(tmp_path):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    lines = ["0 99 16 42 3 5S100M3I", "1 0 0 0 . 45=2X", "2 1099511627776 1 255 -7 1D7N2H9P", "0 5 0 7 0 150M"]
+    res = subprocess.run([build_annotator_test(tmp_path), "oa"], input="\n".join(lines) + "\n", capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    assert res.stdout.split("\n")[:4] == ["1,99,-,5S100M3I,42,3;", "chrB,0,+,45=2X,0,;", "a_longer_name,1099511627776,+,1D7N2H9P,255,-7;",
+                                          "1,5,+,150M,7,0;"]

@@ -414,3 +414,56 @@ def test_index_built_from_msa_text_on_device(gpu, port, workflow_msa):
     with tempfile.TemporaryDirectory() as d:
         write_index_file(os.path.join(d, "x"), ents)
         assert open(os.path.join(d, "x"), "rb").read() == open(golden, "rb").read()
+
+
+# ---------------------------------------------------------------------------------------------- record annotation text (N1)
+def _oa_inputs(rng, n, names):
+    n_ops = rng.integers(0, 12, n)
+    n_ops[rng.random(n) < 0.02] = 300                          # long-read style CIGARs
+    cig_off = np.zeros(n + 1, np.uint64); cig_off[1:] = np.cumsum(n_ops)
+    total = int(cig_off[-1])
+    lens = rng.choice([1, 9, 10, 99, 100, 150, 12345, 999999, 1000000, (1 << 28) - 1], total)
+    cig = (lens.astype(np.uint32) << 4) | rng.integers(0, 9, total).astype(np.uint32)
+    pos = rng.choice([0, 9, 10, 99999, 100000, 2 ** 32 - 1, 2 ** 32, 10 ** 15, 2 ** 63], n).astype(np.uint64)
+    return dict(ref_id=rng.integers(0, len(names), n).astype(np.uint32), pos=pos, flag=rng.integers(0, 4096, n).astype(np.uint16),
+                mapq=rng.integers(0, 256, n).astype(np.uint8),
+                nm=rng.choice([0, 1, 9, 10, 150, -1, -2147483648, 2147483647], n).astype(np.int32),
+                has_nm=(rng.random(n) < 0.8).astype(np.uint8), cig_off=cig_off, cig=cig)
+
+
+@pytest.mark.parametrize("n", [0, 1, 255, 256, 257, 5000, 300_000])
+def test_format_oa_matches_oracle(gpu, port, n):
+    """project_alignments.cc:803-845 on the device, byte-exact against the port: digit-count boundaries of every integer
+    field, empty CIGARs, missing NM, names of different lengths (one empty), many CTAs."""
+    from panvc3_b200.capi import Context
+    ctx = Context(0)
+    names = [b"1", b"chr10_random_contig_with_a_long_name", b"", b"REF"]
+    a = _oa_inputs(np.random.default_rng(n + 3), n, names)
+    et, eo = port.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], a["nm"], a["has_nm"], a["cig_off"], a["cig"], names)
+    t, o = ctx.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], a["nm"], a["has_nm"], a["cig_off"], a["cig"], names)
+    np.testing.assert_array_equal(o, eo)
+    assert t == et
+    # no record has NM
+    et, eo = port.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], None, None, a["cig_off"], a["cig"], names)
+    t, o = ctx.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], None, None, a["cig_off"], a["cig"], names)
+    np.testing.assert_array_equal(o, eo)
+    assert t == et
+
+
+def test_format_cigars_of_projected_batch(gpu, port, workflow_msa):
+    """SAM text of the projected CIGARs, addressed (off, len) in the output arena as pv3_project leaves them."""
+    from panvc3_b200.workload import sample_reads
+    idx = device_index(workflow_msa)
+    b = sample_reads(workflow_msa, 5000, 150, seed=77, ins=0.003, dele=0.003, clip_frac=0.1)
+    out = idx.project_batch(b)
+    t, o = idx.ctx.format_cigars(out.cig_off, out.cig, out.cig_len)
+    et, eo = port.format_oa(None, None, None, None, None, None, out.cig_off, out.cig, None, cig_len=out.cig_len)
+    np.testing.assert_array_equal(o, eo)
+    assert t == et
+    for i in (0, 1, 4999):
+        ops = out.cig[int(out.cig_off[i]): int(out.cig_off[i]) + int(out.cig_len[i])]
+        assert t[int(o[i]):int(o[i + 1])].decode() == format_cigar(ops)
+    # consecutive offsets (the input batch's own CIGARs)
+    t, o = idx.ctx.format_cigars(b.cig_off, b.cig)
+    et, eo = port.format_oa(None, None, None, None, None, None, b.cig_off, b.cig, None)
+    assert t == et and np.array_equal(o, eo)

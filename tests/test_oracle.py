@@ -153,3 +153,17 @@ def test_msa_row_extract_port_matches_reference_builder(port, ref, n, gap_p, chu
     np.testing.assert_array_equal(pw, pack_bits(t == ord("-"))[: pw.size])
     np.testing.assert_array_equal(ps, t[t != ord("-")])
     assert np.array_equal(port.msa_row_extract(t, with_sequence=False)[0], pw)
+
+
+# ---------------------------------------------------------------------------------------------- OA entry (N1)
+def test_format_oa_known_answers(port):
+    """Hand-derived from project_alignments.cc:803-845: RNAME,POS,strand,CIGAR,MAPQ,NM; — POS as stored (0-based), NM empty
+    when the record had no NM tag, '-' only for FLAG & 0x10."""
+    cig = np.array([(5 << 4) | 4, (100 << 4) | 0, (3 << 4) | 1, (45 << 4) | 7, (2 << 4) | 8, (1 << 4) | 2, (7 << 4) | 3,
+                    (2 << 4) | 5, (4294967295 >> 4 << 4) | 6], np.uint32)
+    text, off = port.format_oa([1, 0, 0], [12345, 0, 2 ** 40], [16, 0, 0x10 | 0x1], [42, 0, 255], [3, -2, -2147483648], [1, 0, 1],
+                               [0, 3, 5, 9], cig, [b"chr1", b"seqB"])
+    recs = [text[int(off[i]):int(off[i + 1])] for i in range(3)]
+    assert recs == [b"seqB,12345,-,5S100M3I,42,3;", b"chr1,0,+,45=2X,0,;", b"chr1,1099511627776,-,1D7N2H268435455P,255,-2147483648;"]
+    text, off = port.format_oa(None, None, None, None, None, None, [0, 3, 3, 5], cig[:5], None)
+    assert [text[int(off[i]):int(off[i + 1])] for i in range(3)] == [b"5S100M3I", b"", b"45=2X"]
