@@ -151,6 +151,17 @@ class MsaIndex:
                 return e
         raise KeyError(seq_id)
 
+    def convert_bed_intervals(self, src: SequenceEntry, dst: SequenceEntry, starts, ends):
+        """`panvc3 convert-bed-positions` for a batch of half-open BED intervals (convert-bed-positions/main.cc:60-73,
+        88-98): both ends go through convert_position, which is rank0_dst(1 + c) + dst[c] - 1 with c = select0_src(1 + p) —
+        in either case of dst[c] the same number as rank0_dst(c), i.e. project_position, so one launch of the position
+        kernel over the 2 n ends does it."""
+        s = np.ascontiguousarray(starts, dtype=np.uint64)
+        e = np.ascontiguousarray(ends, dtype=np.uint64)
+        pos = np.concatenate([s, e])
+        out = self.ctx.project_positions(np.full(pos.size, src.row, np.uint32), np.full(pos.size, dst.row, np.uint32), pos)
+        return out[: s.size], out[s.size:]
+
     def project_batch(self, batch: RecordBatch, gap_opening_cost: int = 0, gap_extension_cost: int = -1,
                       out: ProjectedBatch | None = None) -> ProjectedBatch:
         self.ctx.set_params(gap_opening_cost, gap_extension_cost)

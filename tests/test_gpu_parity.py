@@ -467,3 +467,19 @@ def test_format_cigars_of_projected_batch(gpu, port, workflow_msa):
     t, o = idx.ctx.format_cigars(b.cig_off, b.cig)
     et, eo = port.format_oa(None, None, None, None, None, None, b.cig_off, b.cig, None)
     assert t == et and np.array_equal(o, eo)
+
+
+def test_convert_bed_intervals(gpu, port, workflow_msa):
+    """convert-bed-positions/main.cc:60-98 for a batch of intervals, against the tool's own formula on the oracle."""
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    rng = np.random.default_rng(12)
+    for src, dst in ((1, 0), (0, 3), (4, 2)):
+        n_src = int(workflow_msa.ungapped[src].size)
+        starts = rng.integers(0, n_src - 1, 500)
+        ends = np.minimum(starts + rng.integers(1, 2000, 500), n_src - 1)
+        s, e = idx.convert_bed_intervals(idx.entries[src], idx.entries[dst], starts, ends)
+        for k in range(500):
+            for got, p in ((s[k], starts[k]), (e[k], ends[k])):
+                c = oi.select0(src, 1 + int(p))
+                assert int(got) == oi.rank0(dst, 1 + c) + oi.access(dst, c) - 1

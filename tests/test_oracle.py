@@ -167,3 +167,24 @@ def test_format_oa_known_answers(port):
     assert recs == [b"seqB,12345,-,5S100M3I,42,3;", b"chr1,0,+,45=2X,0,;", b"chr1,1099511627776,-,1D7N2H268435455P,255,-2147483648;"]
     text, off = port.format_oa(None, None, None, None, None, None, [0, 3, 3, 5], cig[:5], None)
     assert [text[int(off[i]):int(off[i + 1])] for i in range(3)] == [b"5S100M3I", b"", b"45=2X"]
+
+
+# ---------------------------------------------------------------------------------------------- convert-bed-positions (N4)
+def _convert_position(oi, src, dst, p):
+    """convert-bed-positions/main.cc:60-73, on the oracle's primitives."""
+    c = oi.select0(src, 1 + p)
+    return oi.rank0(dst, 1 + c) + oi.access(dst, c) - 1
+
+
+@pytest.mark.parametrize("kind", ["port", "reference"])
+def test_convert_bed_position_equals_project_position(kind, port, request, workflow_msa):
+    """The BED tool's convert_position and msa_index::project_position (msa_index.hh:253-258) are the same function; checked
+    on the port and on the compiled reference's own rrr rank / select / access."""
+    lib = port if kind == "port" else request.getfixturevalue("ref")
+    oi = lib.make_index(*casegen.index_inputs(workflow_msa))
+    rng = np.random.default_rng(4)
+    for src in range(workflow_msa.n_rows):
+        n_src = int(workflow_msa.ungapped[src].size)
+        for p in [0, 1, n_src - 1, *rng.integers(0, n_src, 60).tolist()]:
+            for dst in (0, (src + 1) % workflow_msa.n_rows):
+                assert _convert_position(oi, src, dst, int(p)) == oi.project_position(src, dst, int(p))
