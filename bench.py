@@ -359,15 +359,40 @@ def run_gpu_arm(args) -> None:
     e2e_s = time.perf_counter() - t0
     barrier()
     clocks = sampler.stop()
+
+    # ---- the same with SEQ as a BAM file holds it (4-bit packed, pv3_batch_in.seq_len): half the SEQ bytes over PCIe -----
+    bam4_s, bam4_bytes = None, None
+    if not args.no_bam4_leg:
+        packed = batch.to_bam4()
+        pin_in4 = PinnedArena(lib, packed.input_bytes() + 16 * 4096)
+        p4 = RecordBatch.__new__(RecordBatch)
+        for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
+            a = getattr(packed, k)
+            if a is not None:
+                q = pin_in4.take(a.shape, a.dtype); q[...] = a; a = q
+            setattr(p4, k, a)
+        pin_out4 = PinnedArena(lib, n * 36 + cig_cap * 4 + rr_cap * 32 + 16 * 4096)
+        pout4 = alloc_output(n, cig_cap, rr_cap, pin_out4)
+        for _ in range(max(args.warmup, 1)):
+            pout4 = ctx.project(p4, pout4)
+        assert np.array_equal(pout4.dst_pos, pout.dst_pos) and pout4.stats["cig_used"] == pout.stats["cig_used"]
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pout4 = ctx.project(p4, pout4)
+        torch.cuda.synchronize(dev)
+        bam4_s = time.perf_counter() - t0
+        barrier()
+        bam4_bytes = int(packed.input_bytes() - (packed.qual.nbytes if packed.qual_off is not None else 0) + 0)
     d2h_bytes = n * 36 + pout.stats["cig_used"] * 4 + pout.stats["rr_used"] * 32
     rr_all = pout.rr[:pout.stats["rr_used"]]
     lazy_qual_bytes = int(rr_all[:, 3].sum()) if (batch.qual_off is not None and pout.stats["rr_used"] * 16 <= n) else (batch.qual.nbytes if batch.qual_off is not None else 0)
 
     # ---- max over ranks ---------------------------------------------------------------------------------------------
-    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches)], dtype=torch.float64, device=dev)
+    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches), (bam4_s or 0.0) * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_ms_max = float(times[0]), float(times[1])
+    dev_ms_max, e2e_ms_max, bam4_ms_max = float(times[0]), float(times[1]), float(times[3])
 
     # ---- ordered gather over NVLink (N>1): results of one step to rank 0 in input order, timed separately -----------
     gather_ms = None
@@ -427,6 +452,10 @@ def run_gpu_arm(args) -> None:
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
         }
+        if bam4_s is not None:
+            line["e2e_bam4_seq"] = {"value": total_records / (bam4_ms_max * 1e-3), "unit": UNIT, "ms_per_step": bam4_ms_max / args.steps,
+                                    "h2d_bytes_per_step": bam4_bytes + lazy_qual_bytes, "d2h_bytes_per_step": int(d2h_bytes),
+                                    "what": "same records, same call, SEQ passed 4-bit packed as a BAM file stores it (pv3_batch_in.seq_len); results checked equal to the e2e run's"}
         if gather_ms is not None:
             line["ordered_gather"] = {"ms": gather_ms, "ms_device_only": gather_dev_ms, "backend": "nccl",
                                       "what": "one step's results of all ranks to rank 0 in input order (ms: into the writer's pinned host memory; ms_device_only: collectives + merge on the GPU)"}
@@ -448,6 +477,7 @@ def main() -> None:
     ap.add_argument("--workload", default="config2", choices=["config2", "indel", "chr", "long"])
     ap.add_argument("--records", type=int, default=RECORDS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bam4-leg", action="store_true", help="skip the e2e leg with 4-bit packed SEQ input")
     ap.add_argument("--no-dp-leg", action="store_true", help="skip the realignment-throughput leg on the indel-heavy shape")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PV3_ABI_VERSION 3
+#define PV3_ABI_VERSION 4
 
 typedef struct pv3_ctx pv3_ctx;
 
@@ -70,6 +70,11 @@ typedef struct {
 	const uint8_t  *qual;      /* phred42 ranks */
 	const uint64_t *cig_off;   /* [n+1] */
 	const uint32_t *cig;       /* BAM-packed ops                                                          — cigar_seq */
+	const uint32_t *seq_len;   /* NULL (default): seq as above. Non-NULL: SEQ as a BAM file stores it — 4-bit codes "=ACMGRSVTWYHKDBN",
+	                              two bases per byte, first base in the high nibble, every record starting on a byte; seq_off
+	                              then counts BYTES and seq_len[i] is the record's number of bases. Codes other than A C G T are
+	                              read as N, as seqan3 does when it reads a BAM SEQ into dna5 (no unpacking on
+	                              the host, half the bytes over PCIe). */
 } pv3_batch_in;
 
 /* Output batch. CIGARs and realigned ranges live in arenas and are addressed per record by (off, len); arena order

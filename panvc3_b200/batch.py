@@ -104,6 +104,7 @@ class RecordBatch:
     cig: np.ndarray
     qual_off: np.ndarray | None = None
     qual: np.ndarray | None = None
+    seq_len: np.ndarray | None = None     # set ⇒ seq is BAM 4-bit packed, seq_off counts bytes (pv3_batch_in.seq_len)
 
     def __post_init__(self) -> None:
         self.src_row = np.ascontiguousarray(self.src_row, dtype=np.uint32)
@@ -117,8 +118,11 @@ class RecordBatch:
         if self.qual_off is not None:
             self.qual_off = np.ascontiguousarray(self.qual_off, dtype=np.uint64)
             self.qual = np.ascontiguousarray(self.qual if self.qual is not None else np.zeros(0), dtype=np.uint8)
+        if self.seq_len is not None:
+            self.seq_len = np.ascontiguousarray(self.seq_len, dtype=np.uint32)
         n = self.n
         assert self.dst_row.size == n and self.dst_ref.size == n and self.src_pos.size == n
+        assert self.seq_len is None or self.seq_len.size == n
         assert self.seq_off.size == n + 1 and self.cig_off.size == n + 1
         assert self.qual_off is None or self.qual_off.size == n + 1
 
@@ -171,10 +175,33 @@ class RecordBatch:
             qo = int(self.qual_off[begin])
             kw["qual_off"] = self.qual_off[begin:end + 1] - np.uint64(qo)
             kw["qual"] = self.qual[qo:int(self.qual_off[end])]
+        if self.seq_len is not None:
+            kw["seq_len"] = self.seq_len[begin:end]
         return RecordBatch(**kw)
+
+    def to_bam4(self) -> "RecordBatch":
+        """The same records with SEQ as a BAM file stores it: 4-bit codes (A=1 C=2 G=4 T=8 N=15), two bases per byte, first
+        base in the high nibble, records byte-aligned; seq_off counts bytes and seq_len bases."""
+        assert self.seq_len is None
+        n = self.n
+        lens = np.diff(self.seq_off).astype(np.uint64)
+        nbytes = (lens + np.uint64(1)) // np.uint64(2)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        off[1:] = np.cumsum(nbytes)
+        codes = np.array([1, 2, 4, 15, 8, 15, 15, 15], dtype=np.uint8)[np.minimum(self.seq, 7)]
+        padded = np.zeros(2 * int(off[-1]), dtype=np.uint8)                      # every record padded to an even length
+        if self.seq.size:
+            shift = (2 * off[:-1]).astype(np.int64) - self.seq_off[:-1].astype(np.int64)
+            padded[np.arange(self.seq.size, dtype=np.int64) + np.repeat(shift, lens.astype(np.int64))] = codes
+        packed = (padded[0::2] << 4) | padded[1::2]
+        return RecordBatch(src_row=self.src_row, dst_row=self.dst_row, dst_ref=self.dst_ref, src_pos=self.src_pos, seq_off=off,
+                           seq=packed, cig_off=self.cig_off, cig=self.cig, qual_off=self.qual_off, qual=self.qual,
+                           seq_len=lens.astype(np.uint32))
 
     def input_bytes(self) -> int:
         tot = sum(a.nbytes for a in (self.src_row, self.dst_row, self.dst_ref, self.src_pos, self.seq_off, self.seq, self.cig_off, self.cig))
+        if self.seq_len is not None:
+            tot += self.seq_len.nbytes
         if self.qual_off is not None:
             tot += self.qual_off.nbytes + self.qual.nbytes
         return tot

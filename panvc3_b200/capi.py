@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
 class BatchIn(C.Structure):
     _fields_ = [("n", C.c_uint64), ("src_row", C.c_void_p), ("dst_row", C.c_void_p), ("dst_ref", C.c_void_p),
                 ("src_pos", C.c_void_p), ("seq_off", C.c_void_p), ("seq", C.c_void_p), ("qual_off", C.c_void_p),
-                ("qual", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p)]
+                ("qual", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p), ("seq_len", C.c_void_p)]
 
 
 class BatchOut(C.Structure):
@@ -225,7 +225,7 @@ class Context:
         n = batch.n
         bi = BatchIn(n, _ptr(batch.src_row), _ptr(batch.dst_row), _ptr(batch.dst_ref), _ptr(batch.src_pos), _ptr(batch.seq_off),
                      _ptr(batch.seq), _ptr(batch.qual_off), _ptr(batch.qual) if batch.qual_off is not None else None,
-                     _ptr(batch.cig_off), _ptr(batch.cig))
+                     _ptr(batch.cig_off), _ptr(batch.cig), _ptr(batch.seq_len))
         if out is None:
             out = alloc_output(n, int(batch.cig.size) * 3 + n * 8 + 1024, n // 8 + 1024)
         for _ in range(8):

@@ -5,6 +5,7 @@
 // vectors become device buffers owned here and reused across batches; the loaded msa_index and the reference contigs
 // (sequence_buffer_store) become one immutable device-resident index.
 // There is no CPU fallback: every entry point fails with PV3_ERR_CUDA if the device is unusable.
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -45,12 +46,12 @@ struct HostRef { std::string bases; };
 
 // One of two buffer sets of the chunked host pipeline (device mirrors of a chunk's inputs and outputs).
 struct HostSet {
-	DevBuf   in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig;
+	DevBuf   in_src_row, in_dst_row, in_dst_ref, in_src_pos, in_seq_off, in_seq, in_qual_off, in_qual, in_cig_off, in_cig, in_seq_len;
 	DevBuf   out_dst_pos, out_flags, out_cig_off, out_cig_len, out_arena, out_rr_off, out_rr_len, out_rr;
 	uint64_t arena_cap_hint = 0, rr_cap_hint = 0;
 	void release()
 	{
-		for (DevBuf *b : { &in_src_row, &in_dst_row, &in_dst_ref, &in_src_pos, &in_seq_off, &in_seq, &in_qual_off, &in_qual, &in_cig_off, &in_cig,
+		for (DevBuf *b : { &in_src_row, &in_dst_row, &in_dst_ref, &in_src_pos, &in_seq_off, &in_seq, &in_qual_off, &in_qual, &in_cig_off, &in_cig, &in_seq_len,
 				&out_dst_pos, &out_flags, &out_cig_off, &out_cig_len, &out_arena, &out_rr_off, &out_rr_len, &out_rr }) b->release();
 	}
 };
@@ -77,6 +78,7 @@ struct pv3_ctx {
 	int32_t      lut[84];
 	int          stage = 0;
 	uint64_t     chunk_records = 500000;     // records per chunk of the host pipeline (PV3_CHUNK_RECORDS overrides)
+	uint64_t     chunk_edge = 125000;        // records of the first and the last chunk: a short pipeline fill and drain (PV3_CHUNK_EDGE; 0 = equal chunks)
 	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all
 	bool         many_deferred = false;      // last batch: more than 1/16 of the records went to the warp-per-record kernel
 	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
@@ -151,6 +153,7 @@ int pv3_create(pv3_ctx **out, int device)
 	ctx->n_sms = prop.multiProcessorCount;
 	default_quality_lut(ctx->lut);
 	if (const char *e = getenv("PV3_CHUNK_RECORDS")) { long long v = atoll(e); if (v >= 1024) ctx->chunk_records = (uint64_t) v; }
+	if (const char *e = getenv("PV3_CHUNK_EDGE")) { long long v = atoll(e); if (v >= 0) ctx->chunk_edge = (uint64_t) v; }
 	if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaStreamCreate failed"); }
 	ctx->stream = ctx->own_stream;
 	for (auto &ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) { delete ctx; return fail(nullptr, PV3_ERR_CUDA, "cudaEventCreate failed"); }
@@ -374,7 +377,7 @@ K1Params make_k1(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	memset(&P, 0, sizeof P);
 	P.n = in->n;
 	P.src_row = in->src_row; P.dst_row = in->dst_row; P.dst_ref = in->dst_ref; P.src_pos = in->src_pos;
-	P.seq_off = in->seq_off; P.seq = in->seq; P.qual_off = in->qual_off; P.qual = in->qual;
+	P.seq_off = in->seq_off; P.seq = in->seq; P.seq_len = in->seq_len; P.qual_off = in->qual_off; P.qual = in->qual;
 	P.cig_off = in->cig_off; P.cig = in->cig;
 	P.rows = ctx->row_desc.as <RowDesc>(); P.n_rows = (uint32_t) ctx->rows.size();
 	P.refs = ctx->ref_desc.as <RefDesc>(); P.n_refs = (uint32_t) ctx->refs.size();
@@ -388,9 +391,27 @@ K1Params make_k1(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	return P;
 }
 
+// Small transfers between pinned host memory and the device done by a kernel (the pointers of cudaMallocHost memory are
+// valid on the device under unified addressing). A cudaMemcpyAsync of a few hundred bytes would queue on the copy engine
+// behind the OTHER stream's bulk chunk transfer and hold this chunk's next kernel for a millisecond; these loads and
+// stores go over PCIe directly.
+__global__ void small_copy_kernel(unsigned long long *dst, const unsigned long long *src, size_t n_words)
+{
+	for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t) gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+cudaError_t small_copy(void *dst, const void *src, size_t bytes, cudaStream_t stream)   // bytes rounded up to 8: buffers have the slack
+{
+	size_t const n_words = (bytes + 7) / 8;
+	if (!n_words) return cudaSuccess;
+	unsigned const blocks = (unsigned) std::min <size_t>((n_words + 255) / 256, 64);
+	small_copy_kernel<<<blocks, 256, 0, stream>>>((unsigned long long *) dst, (const unsigned long long *) src, n_words);
+	return cudaGetLastError();
+}
+
 int fetch_counters(pv3_ctx *ctx, cudaStream_t stream)
 {
-	PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, stream));
+	PV3_CUDA(ctx, small_copy(ctx->h_counters, ctx->counters.p, sizeof(Counters), stream));
 	PV3_CUDA(ctx, cudaStreamSynchronize(stream));
 	return PV3_OK;
 }
@@ -506,7 +527,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_jobs, ctx->h_jobs_cap * sizeof(Job)));
 					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_job_qual_off, ctx->h_jobs_cap * 8));
 				}
-				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->h_jobs, ctx->jobs.p, n_jobs * sizeof(Job), cudaMemcpyDeviceToHost, stream));
+				PV3_CUDA(ctx, small_copy(ctx->h_jobs, ctx->jobs.p, n_jobs * sizeof(Job), stream));
 				PV3_CUDA(ctx, cudaStreamSynchronize(stream));
 				uint64_t need = 0;
 				for (uint64_t j = 0; j < n_jobs; ++j) need += ctx->h_jobs[j].qry_len;
@@ -524,8 +545,8 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 				}
 				PV3_CUDA(ctx, ctx->d_packed.ensure(w + 16));
 				PV3_CUDA(ctx, ctx->d_job_qual_off.ensure(n_jobs * 8));
-				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->d_packed.p, ctx->h_packed, w, cudaMemcpyHostToDevice, stream));
-				PV3_CUDA(ctx, cudaMemcpyAsync(ctx->d_job_qual_off.p, ctx->h_job_qual_off, n_jobs * 8, cudaMemcpyHostToDevice, stream));
+				PV3_CUDA(ctx, small_copy(ctx->d_packed.p, ctx->h_packed, w, stream));
+				PV3_CUDA(ctx, small_copy(ctx->d_job_qual_off.p, ctx->h_job_qual_off, n_jobs * 8, stream));
 				K.packed_qual = ctx->d_packed.as <uint8_t>();
 				K.job_qual_off = ctx->d_job_qual_off.as <uint64_t>();
 			}
@@ -623,8 +644,26 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	for (int k = 0; k < 2; ++k) for (int e = 0; e < 4; ++e)
 		if (!ctx->cev[k][e]) PV3_CUDA(ctx, cudaEventCreate(&ctx->cev[k][e]));
 
-	auto chunk_begin = [&](uint64_t c) { return (n * c / n_chunks) / 128 * 128; };   // tile-aligned cuts
-	auto chunk_end = [&](uint64_t c) { return c + 1 == n_chunks ? n : (n * (c + 1) / n_chunks) / 128 * 128; };
+	// Chunk cuts (tile-aligned). Only the first chunk's upload and the last chunk's kernels and download are not hidden
+	// behind other chunks' transfers, so those two chunks are small and the ones between them large.
+	uint64_t cuts[67];
+	{
+		uint64_t const edge = (n_chunks >= 2 && ctx->chunk_edge && n > 4 * ctx->chunk_edge) ? ctx->chunk_edge : 0;
+		if (edge) {
+			uint64_t n_mid = (n - 2 * edge + ctx->chunk_records / 2) / ctx->chunk_records;
+			if (n_mid < 1) n_mid = 1;
+			if (n_mid > 62) n_mid = 62;
+			n_chunks = n_mid + 2;
+			cuts[0] = 0;
+			for (uint64_t c = 0; c <= n_mid; ++c) cuts[c + 1] = (edge + (n - 2 * edge) * c / n_mid) / 128 * 128;
+			cuts[n_chunks] = n;
+		} else {
+			for (uint64_t c = 0; c < n_chunks; ++c) cuts[c] = (n * c / n_chunks) / 128 * 128;
+			cuts[n_chunks] = n;
+		}
+	}
+	auto chunk_begin = [&](uint64_t c) { return cuts[c]; };
+	auto chunk_end = [&](uint64_t c) { return cuts[c + 1]; };
 
 	// H2D of chunk c into buffer set c % 2 (QUAL bytes are not copied)
 	auto enqueue_h2d = [&](uint64_t c) -> int {
@@ -638,6 +677,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 			{ &hs.in_src_pos, in->src_pos + b, m * 8 }, { &hs.in_seq_off, in->seq_off + b, (m + 1) * 8 }, { &hs.in_seq, in->seq + s0, s1 - s0 },
 			{ &hs.in_qual_off, in->qual_off ? in->qual_off + b : nullptr, in->qual_off ? (m + 1) * 8 : 0 },
 			{ &hs.in_cig_off, in->cig_off + b, (m + 1) * 8 }, { &hs.in_cig, in->cig + c0, (c1 - c0) * 4 },
+			{ &hs.in_seq_len, in->seq_len ? in->seq_len + b : nullptr, in->seq_len ? m * 4 : 0 },
 		};
 		for (auto const &cp : copies) PV3_CUDA(ctx, cp.buf->ensure((cp.bytes ? cp.bytes : 16) + 32));
 		if (in->qual_off) PV3_CUDA(ctx, hs.in_qual.ensure(in->qual_off[e] - in->qual_off[b] + 32));
@@ -684,6 +724,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		din.qual = in->qual_off ? hs.in_qual.as <uint8_t>() - in->qual_off[b] : nullptr;
 		din.cig_off = hs.in_cig_off.as <uint64_t>();
 		din.cig = hs.in_cig.as <uint32_t>() - in->cig_off[b];
+		din.seq_len = in->seq_len ? hs.in_seq_len.as <uint32_t>() : nullptr;
 
 		PV3_CUDA(ctx, hs.out_dst_pos.ensure(m * 8)); PV3_CUDA(ctx, hs.out_flags.ensure(m * 4));
 		PV3_CUDA(ctx, hs.out_cig_off.ensure(m * 8)); PV3_CUDA(ctx, hs.out_cig_len.ensure(m * 4));

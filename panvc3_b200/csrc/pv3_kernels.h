@@ -15,6 +15,7 @@ struct K1Params {
 	const uint32_t *src_row, *dst_row, *dst_ref;
 	const uint64_t *src_pos, *seq_off;
 	const uint8_t  *seq;
+	const uint32_t *seq_len;     // null: seq holds one dna5 rank per byte; else seq is BAM 4-bit packed, seq_off counts bytes, seq_len bases
 	const uint64_t *qual_off;    // may be null
 	const uint8_t  *qual;
 	const uint64_t *cig_off;
@@ -40,6 +41,24 @@ struct K1Params {
 	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
 	uint64_t        rr_base;     // added to every stored rr_off
 };
+
+// BAM 4-bit base code ("=ACMGRSVTWYHKDBN") → seqan3::dna5 rank, as seqan3 converts when it reads a BAM SEQ into dna5
+// (A C G T keep their letter, everything else becomes N): a 16 x 4-bit table.
+__host__ __device__ inline uint32_t bam4_to_rank(uint32_t code) { return (uint32_t) (0x3333333433323103ull >> (4 * (code & 15u))) & 15u; }
+
+#ifdef __CUDACC__
+// rank of base i of the record whose SEQ starts at seq_off value qbase
+__device__ __forceinline__ uint8_t query_rank(K1Params const &P, uint64_t qbase, uint64_t i)
+{
+	if (!P.seq_len) return __ldg(P.seq + qbase + i);
+	uint32_t const b = __ldg(P.seq + qbase + (i >> 1));
+	return (uint8_t) bam4_to_rank((i & 1u) ? b : (b >> 4));
+}
+__device__ __forceinline__ uint64_t query_length(K1Params const &P, uint64_t rec)
+{
+	return P.seq_len ? (uint64_t) __ldg(P.seq_len + rec) : __ldg(P.seq_off + rec + 1) - __ldg(P.seq_off + rec);
+}
+#endif
 
 // Scratch bytes one DP job needs: byte trace (Q+1)x(R+1), strip boundary arrays (H, up: int32; tup: byte), staged
 // reference ranks.

@@ -67,7 +67,7 @@ k3_realign_kernel(K3Params P)
 		uint32_t const R = job.ref_len, Q = job.qry_len;
 		uint32_t const cols = R + 1;
 		const char *rbase = B.refs[__ldg(B.dst_ref + rec)].bases + job.ref_loc;
-		const uint8_t *qptr = B.seq + __ldg(B.seq_off + rec) + job.qry_loc;
+		uint64_t const qbase = __ldg(B.seq_off + rec), qloc = job.qry_loc;
 		bool has_qual = false;
 		const uint8_t *qlptr = nullptr;
 		if (B.qual_off) {
@@ -102,7 +102,7 @@ k3_realign_kernel(K3Params P)
 			uint32_t const i = i0 + 1 + lane;
 			bool const row_ok = i <= Q;
 			uint32_t const nl = (Q - i0 < 32u) ? (Q - i0) : 32u;
-			uint8_t const qi = row_ok ? __ldg(qptr + i - 1) : 0;
+			uint8_t const qi = row_ok ? query_rank(B, qbase, qloc + i - 1) : 0;
 			int32_t s_match, s_mis;
 			if (edit) { s_match = 0; s_mis = 1; }
 			else if (has_qual) {
@@ -176,7 +176,7 @@ k3_realign_kernel(K3Params P)
 			if (cur_op != OP_NONE) { --wp; if (lane == 0) out[wp] = (cur_cnt << 4) | cur_op; }
 			cur_op = op; cur_cnt = 1;
 		};
-		auto diag_op = [&]() -> uint32_t { return (rs[j - 1] == __ldg(qptr + i - 1)) ? OP_EQ : OP_X; };   // align.hh:104-107
+		auto diag_op = [&]() -> uint32_t { return (rs[j - 1] == query_rank(B, qbase, qloc + i - 1)) ? OP_EQ : OP_X; };   // align.hh:104-107
 
 		if (edit) {
 			while (i > 0 || j > 0) {

@@ -80,7 +80,7 @@ k3_thread_kernel(K3Params P)
 
 	uint32_t const cols = R + 1;
 	const char *rbase = B.refs[__ldg(B.dst_ref + rec)].bases + ref_loc;
-	const uint8_t *qptr = B.seq + __ldg(B.seq_off + rec) + qry_loc;
+	uint64_t const qbase = __ldg(B.seq_off + rec);
 	bool has_qual = false;
 	const uint8_t *qlptr = nullptr;
 	if (B.qual_off) {
@@ -111,7 +111,7 @@ k3_thread_kernel(K3Params P)
 		uint32_t const n_cells = R * Q;
 		for (uint32_t c = 0; c < n_cells; ++c) {
 			if (j == 1) {                                                                 // row start
-				qi = __ldg(qptr + i - 1);
+				qi = query_rank(B, qbase, qry_loc + i - 1);
 				if (edit) { s_match = 0; s_mis = 1; Hcur = (int32_t) i; }
 				else {
 					if (has_qual) { uint32_t ql = __ldg(qlptr + i - 1); if (ql > 41) ql = 41; s_match = P.lut[2 * ql]; s_mis = P.lut[2 * ql + 1]; }
@@ -164,7 +164,7 @@ k3_thread_kernel(K3Params P)
 				uint32_t const t = (i > 0 && j > 0) ? T[i * cols + j] : 0u;
 				if (j > 0 && (i == 0 || (t & 1u))) { op = OP_D; --j; }                      // Left  ⇒ gap in query ⇒ D
 				else if (i > 0 && (j == 0 || (t & 2u))) { op = OP_I; --i; }                 // Up    ⇒ gap in reference ⇒ I
-				else { op = (rs[j - 1] == __ldg(qptr + i - 1)) ? OP_EQ : OP_X; --i; --j; }   // align.hh:104-107
+				else { op = (rs[j - 1] == query_rank(B, qbase, qry_loc + i - 1)) ? OP_EQ : OP_X; --i; --j; }   // align.hh:104-107
 			} else {
 				if (tr == 0) break;
 				if ((dir == TD_UP && i == 0) || (dir == TD_LEFT && j == 0) || (dir == TD_DIAG && (i == 0 || j == 0))
@@ -172,7 +172,7 @@ k3_thread_kernel(K3Params P)
 				uint32_t const old = tr;
 				if (dir == TD_UP) { op = OP_I; --i; tr = T[i * cols + j]; if (old & TT_UO) dir = pick(tr); }
 				else if (dir == TD_LEFT) { op = OP_D; --j; tr = T[i * cols + j]; if (old & TT_LO) dir = pick(tr); }
-				else { op = (rs[j - 1] == __ldg(qptr + i - 1)) ? OP_EQ : OP_X; --i; --j; tr = T[i * cols + j]; dir = pick(tr); }
+				else { op = (rs[j - 1] == query_rank(B, qbase, qry_loc + i - 1)) ? OP_EQ : OP_X; --i; --j; tr = T[i * cols + j]; dir = pick(tr); }
 			}
 			if (op == cur_op) ++cur_cnt;
 			else {

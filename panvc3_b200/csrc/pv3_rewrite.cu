@@ -131,7 +131,7 @@ __device__ RecordResult rewrite_record(const K1Params &P, uint64_t rec, uint32_t
 	RowDesc const D = P.rows[dr];
 	RefDesc const R = P.refs[rf];
 	uint64_t const qbase = __ldg(P.seq_off + rec);
-	uint64_t const nq = __ldg(P.seq_off + rec + 1) - qbase;
+	uint64_t const nq = query_length(P, rec);
 	if (P.qual_off) {
 		uint64_t const ql = __ldg(P.qual_off + rec + 1) - __ldg(P.qual_off + rec);
 		if (ql && ql != nq) res.flags |= PV3_FLAG_BAD_QUAL;
@@ -204,7 +204,7 @@ __device__ RecordResult rewrite_record(const K1Params &P, uint64_t rec, uint32_t
 								uint64_t const ei = ecur + __popc(dz & lt);
 								if (qi >= nq) lane_err |= PV3_FLAG_QUERY_OOB;          // :102
 								else if (ei >= R.n) lane_err |= PV3_FLAG_REF_OOB;       // :103
-								else code = (dna5_to_char(__ldg(P.seq + qbase + qi)) == __ldg(R.bases + ei)) ? OP_EQ : OP_X;
+								else code = (dna5_to_char(query_rank(P, qbase, qi)) == __ldg(R.bases + ei)) ? OP_EQ : OP_X;
 							} else code = OP_D;
 						} else if (mlike) code = OP_I;
 					} else if (dz & bit) code = OP_D;
@@ -284,7 +284,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 		if (res.n_ops == 0) res.flags |= PV3_FLAG_EMPTY_CIGAR;            // cigar.cc:16-18 UB
 		else if (res.adjacent_id) {
 			__syncwarp();
-			uint64_t const nq = __ldg(P.seq_off + rec + 1) - __ldg(P.seq_off + rec);
+			uint64_t const nq = query_length(P, rec);
 			uint64_t const ref_n = P.refs[__ldg(P.dst_ref + rec)].n;
 			bool has_qual = false;
 			if (P.qual_off) has_qual = __ldg(P.qual_off + rec + 1) > __ldg(P.qual_off + rec);

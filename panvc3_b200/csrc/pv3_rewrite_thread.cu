@@ -103,6 +103,18 @@ __device__ __forceinline__ uint2 pack16(uint4 v, uint32_t &bad)
 	return make_uint2(__byte_perm(a, b, 0x6420), __byte_perm(c, d, 0x6420));
 }
 
+// 8 BAM 4-bit codes (first base in the HIGH nibble of each byte) → 8 dna5 ranks, first base in the lowest nibble.
+// One-hot codes 1 2 4 8 (A C G T) become code >> 1 = 0 1 2 4; every other code becomes 3 (N), see bam4_to_rank.
+__device__ __forceinline__ uint32_t bam4_word_to_ranks(uint32_t w)
+{
+	uint32_t const x = ((w & 0x0f0f0f0fu) << 4) | ((w >> 4) & 0x0f0f0f0fu);
+	uint32_t const cnt = x - ((x >> 1) & 0x77777777u) - ((x >> 2) & 0x33333333u) - ((x >> 3) & 0x11111111u);   // bits set per nibble
+	uint32_t const t = cnt ^ 0x11111111u;
+	uint32_t const one = (~(((t & 0x77777777u) + 0x77777777u) | t) & 0x88888888u) >> 3;                           // 1 where exactly one bit
+	uint32_t const m = one * 15u;
+	return ((x >> 1) & 0x77777777u & m) | (0x33333333u & ~m);
+}
+
 __global__ void __launch_bounds__(TT)
 k1_thread_kernel(K1Params P)
 {
@@ -122,14 +134,20 @@ k1_thread_kernel(K1Params P)
 		uint64_t const q_addr = (uint64_t) (uintptr_t) P.seq + tq0;
 		uint64_t const q_addr16 = q_addr & ~15ull;
 		uint32_t const q_lead = (uint32_t) (q_addr - q_addr16);
-		bool const tile_fits = (tq1 - tq0 + q_lead) <= (uint64_t) T_QSTAGE;
+		bool const packed = P.seq_len != nullptr;                           // BAM 4-bit input: offsets count bytes, two bases each
+		bool const tile_fits = ((tq1 - tq0 + q_lead) << (packed ? 1 : 0)) <= (uint64_t) T_QSTAGE;
 
 		// ---- phase B1: the tile's query, packed to nibbles while it is staged (issued first: the loads overlap phase A) ----
 		uint32_t bad_rank = 0;
 		if (tile_fits) {
 			uint32_t const n16 = (uint32_t) ((tq1 - tq0 + q_lead + 15) / 16);
 			const uint4 *g = reinterpret_cast <const uint4 *>((uintptr_t) q_addr16);
-			for (uint32_t i = tid; i < n16; i += TT) sm.q4[i] = pack16(__ldg(g + i), bad_rank);
+			if (!packed) for (uint32_t i = tid; i < n16; i += TT) sm.q4[i] = pack16(__ldg(g + i), bad_rank);
+			else for (uint32_t i = tid; i < n16; i += TT) {
+				uint4 const v = __ldg(g + i);
+				sm.q4[2 * i] = make_uint2(bam4_word_to_ranks(v.x), bam4_word_to_ranks(v.y));
+				sm.q4[2 * i + 1] = make_uint2(bam4_word_to_ranks(v.z), bam4_word_to_ranks(v.w));
+			}
 		}
 
 		// ---- phase A: per-record projection of the start position ------------------------------------------------
@@ -146,7 +164,7 @@ k1_thread_kernel(K1Params P)
 			else {
 				S = P.rows[sr]; D = P.rows[dr]; R = P.refs[rf];
 				qoff = __ldg(P.seq_off + rec);
-				nq = __ldg(P.seq_off + rec + 1) - qoff;
+				nq = packed ? (uint64_t) __ldg(P.seq_len + rec) : __ldg(P.seq_off + rec + 1) - qoff;
 				if (P.qual_off) {
 					uint64_t const ql = __ldg(P.qual_off + rec + 1) - __ldg(P.qual_off + rec);
 					if (ql && ql != nq) flags |= PV3_FLAG_BAD_QUAL;
@@ -263,7 +281,7 @@ k1_thread_kernel(K1Params P)
 		if (work2) {
 			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q4);
 			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
-			uint32_t const qrel = q_lead + (uint32_t) (qoff - tq0);
+			uint32_t const qrel = (q_lead + (uint32_t) (qoff - tq0)) << (packed ? 1 : 0);
 			#pragma unroll
 			for (uint32_t w = 0; w <= T_MMW; ++w) sm.mm[w][tid] = 0;
 			uint32_t j = 0, remaining = 0, qpos = 0, ra = 0;

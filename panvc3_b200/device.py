@@ -30,13 +30,15 @@ class DeviceBatch:
         if self.has_qual:
             self.t["qual_off"] = _to_dev(batch.qual_off, self.device)
             self.t["qual"] = _to_dev(batch.qual if batch.qual.size else np.zeros(1, np.uint8), self.device)
+        if batch.seq_len is not None:
+            self.t["seq_len"] = _to_dev(batch.seq_len, self.device)
         self.cig_words = int(batch.cig.size)
         self.nbytes = batch.input_bytes()
 
     def struct(self) -> BatchIn:
         p = lambda k: self.t[k].data_ptr() if k in self.t else None
         return BatchIn(self.n, p("src_row"), p("dst_row"), p("dst_ref"), p("src_pos"), p("seq_off"), p("seq"), p("qual_off"), p("qual"),
-                       p("cig_off"), p("cig"))
+                       p("cig_off"), p("cig"), p("seq_len"))
 
 
 class DeviceOutput:

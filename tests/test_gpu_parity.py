@@ -483,3 +483,61 @@ def test_convert_bed_intervals(gpu, port, workflow_msa):
             for got, p in ((s[k], starts[k]), (e[k], ends[k])):
                 c = oi.select0(src, 1 + int(p))
                 assert int(got) == oi.rank0(dst, 1 + c) + oi.access(dst, c) - 1
+
+
+# ---------------------------------------------------------------------------------------------- BAM 4-bit SEQ input (N3)
+def test_to_bam4_layout():
+    b = RecordBatch.from_records([dict(src_row=0, dst_row=0, src_pos=0, seq="ACGTN", cigar="5M"),
+                                  dict(src_row=0, dst_row=0, src_pos=0, seq="", cigar="1D"),
+                                  dict(src_row=0, dst_row=0, src_pos=0, seq="TTGA", cigar="4M")])
+    p = b.to_bam4()
+    assert p.seq.tolist() == [0x12, 0x48, 0xF0, 0x88, 0x41] and p.seq_off.tolist() == [0, 3, 3, 5] and p.seq_len.tolist() == [5, 0, 4]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_bam4_packed_seq_random_batches(gpu, port, seed):
+    """pv3_batch_in.seq_len: the same records with SEQ in BAM's 4-bit packing give the same results (oracle on the unpacked
+    batch), in both rewrite kernels, both DP kernels, rewrite-only stage, odd and even read lengths, empty reads."""
+    n_cols = [64, 300, 1500, 6000][seed % 4]
+    msa, b = casegen.random_batch(4000 + seed, 1500, n_cols=n_cols, max_len=[12, 40][seed % 2])
+    if int(b.seq.max(initial=0)) > 4:
+        b.seq = np.minimum(b.seq, 4)
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    p = b.to_bam4()
+    for go, ge in [(0, -1), (-2, -1), (3, -1)]:
+        for stage in (1, 0):
+            exp = oi.project_batch(b, go, ge, stage=stage)
+            for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):
+                idx.ctx.set_stage(stage); idx.ctx.set_kernel_path(path); idx.ctx.set_dp_thread_min(dp_min)
+                assert_same(idx.project_batch(p, go, ge), exp, b, f"bam4 seed={seed} stage={stage} go={go} ge={ge} path={path} dp_min={dp_min}")
+
+
+def test_bam4_packed_seq_realistic_and_long_reads(gpu, port, workflow_msa):
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.workload import sample_reads
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    for kw in (dict(n=30000, length=150, seed=41, ins=0.003, dele=0.003, clip_frac=0.1),
+               dict(n=30000, length=151, seed=42, ins=0.002, dele=0.002, with_qual=False),
+               dict(n=300, length=3001, seed=43, cigar_style="EQX", sub=0.02)):
+        b = sample_reads(workflow_msa, kw.pop("n"), kw.pop("length"), **kw)
+        p = b.to_bam4()
+        exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+        assert_same(idx.project_batch(p), exp, b, "bam4 host path")
+        got = project_device(idx.ctx, DeviceBatch(p)).to_host()
+        assert_same(got, exp, b, "bam4 device path")
+    # IUPAC codes other than A C G T read as N (what seqan3 makes of them in a dna5 record)
+    b = sample_reads(workflow_msa, 2000, 100, seed=44)
+    p = b.to_bam4()
+    rng = np.random.default_rng(3)
+    at = rng.integers(0, p.seq.size, 400)
+    p.seq[at] = (p.seq[at] & 0x0F) | (rng.choice([0, 3, 5, 6, 7, 9, 10, 11, 12, 13, 14], 400).astype(np.uint8) << 4)
+    hi = np.zeros(b.seq.size, bool)
+    base_idx = (np.repeat(np.arange(b.n), np.diff(b.seq_off).astype(np.int64)))
+    within = np.arange(b.seq.size) - b.seq_off[:-1].astype(np.int64)[base_idx]
+    byte_of = p.seq_off[:-1].astype(np.int64)[base_idx] + within // 2
+    changed = np.isin(byte_of, at) & ((within & 1) == 0)
+    b2 = RecordBatch(src_row=b.src_row, dst_row=b.dst_row, dst_ref=b.dst_ref, src_pos=b.src_pos, seq_off=b.seq_off,
+                     seq=np.where(changed, 3, b.seq).astype(np.uint8), cig_off=b.cig_off, cig=b.cig, qual_off=b.qual_off, qual=b.qual)
+    assert_same(idx.project_batch(p), oi.project_batch(b2, 0, -1), b2, "bam4 ambiguity codes")
