@@ -193,6 +193,26 @@ int pv3_format_oa(pv3_ctx *, const pv3_oa_in *in, uint64_t *text_off /* [n+1] */
 int pv3_format_cigars(pv3_ctx *, uint64_t n, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
                       uint64_t n_cig_words, uint64_t *text_off /* [n+1] */, char *text, uint64_t text_cap, uint64_t *text_used);
 
+/* -- recalculate-mapq: the two per-record computations ------------------------------------------------------
+ * pv3_rescore_alignments: cigar_alignment_scorer::calculate_score (recalculate-mapq/main.cc:190-283) — the alignment score
+ * of every record from its CIGAR (= and X, not M), base qualities, N bases of the query and the N positions of the reference
+ * (the XN tag, a bit per aligned reference position); penalties per quality rank as fill_penalties builds them (:181-186).
+ * score[i] is what the reference assigns to AS (a double holding an integer). Flags: PV3_FLAG_BAD_OP (an M or unknown op:
+ * libbio_fail :274-277), PV3_FLAG_REF_OOB (an X base beyond the XN bitmap: libbio_always_assert_lt :264),
+ * PV3_FLAG_QUERY_OOB / PV3_FLAG_BAD_QUAL (SEQ or QUAL shorter than the CIGAR consumes: out-of-range reads in the reference).
+ * Host buffers; refn_off == NULL when no record has the XN tag. */
+typedef struct {
+	int32_t min_mismatch_penalty, max_mismatch_penalty, n_penalty, gap_opening_penalty, gap_extension_penalty;   /* cmdline.ggo: 2 6 1 5 3 */
+} pv3_scoring;
+int pv3_rescore_alignments(pv3_ctx *, const pv3_scoring *, uint64_t n, const uint64_t *seq_off, const uint8_t *seq,
+                           const uint64_t *qual_off, const uint8_t *qual, const uint64_t *cig_off, const uint32_t *cig,
+                           const uint64_t *refn_off, const uint8_t *refn, double *score /* [n] */, uint32_t *flags /* [n] */);
+/* pv3_calculate_mapq: bowtie2_v2_score_calculator::calculate_mapq (main.cc:455-565, tables :378-430) for n independent
+ * (read length, mate length or 0, score, next best score or -DBL_MAX) tuples, in f64 with the reference's operation order
+ * and no fused multiply-add. PV3_FLAG_TRACE_UB marks tuples for which the reference indexes before its table (next > score). */
+int pv3_calculate_mapq(pv3_ctx *, uint64_t n, const uint32_t *read_len, const uint32_t *other_len, const double *score,
+                       const double *next_score, uint8_t *mapq /* [n] */, uint32_t *flags /* [n] */);
+
 /* -- index-msa on the device --------------------------------------------------------------------------------------------
  * The per-sequence work of `panvc3 index-msa` (index-msa/index_vector_builder.cc:28-50, driven from
  * input_processor.cc:155-175): bit i of gap_words = 1 ⇔ text[i] == '-', and every other byte is appended to the unaligned

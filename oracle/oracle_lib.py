@@ -118,6 +118,33 @@ class OracleLib:
         fn(n, *[ptr(a) for a in arrs], len(names or []), noff.ctypes.data, nb.ctypes.data, off.ctypes.data, text.ctypes.data, need)
         return text[:need].tobytes(), off
 
+    def rescore_alignments(self, scoring5, seq_off, seq, qual_off, qual, cig_off, cig, refn_off=None, refn=None):
+        fn = self.lib.pv3o_rescore_alignments
+        fn.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 10
+        fn.restype = None
+        sc = np.ascontiguousarray(scoring5, dtype=np.int32)
+        a = [np.ascontiguousarray(x, dtype=dt) for x, dt in ((seq_off, np.uint64), (seq, np.uint8), (qual_off, np.uint64), (qual, np.uint8),
+                                                             (cig_off, np.uint64), (cig, np.uint32))]
+        n = a[0].size - 1
+        ro = None if refn_off is None else np.ascontiguousarray(refn_off, dtype=np.uint64)
+        rn = None if refn_off is None else np.ascontiguousarray(refn if len(refn) else np.zeros(1, np.uint8), dtype=np.uint8)
+        score, flags = np.zeros(n, np.float64), np.zeros(n, np.uint32)
+        ptr = lambda x: None if x is None else (x.ctypes.data if x.size else np.zeros(1, x.dtype).ctypes.data)
+        keep = [x if x.size else np.zeros(1, x.dtype) for x in a]
+        fn(sc.ctypes.data, n, *[k.ctypes.data for k in keep], None if ro is None else ro.ctypes.data, None if rn is None else rn.ctypes.data,
+           score.ctypes.data, flags.ctypes.data)
+        return score, flags
+
+    def calculate_mapq(self, read_len, other_len, score, next_score):
+        fn = self.lib.pv3o_calculate_mapq
+        fn.argtypes = [C.c_uint64] + [C.c_void_p] * 6
+        fn.restype = None
+        rl, ol = np.ascontiguousarray(read_len, dtype=np.uint32), np.ascontiguousarray(other_len, dtype=np.uint32)
+        s, ns = np.ascontiguousarray(score, dtype=np.float64), np.ascontiguousarray(next_score, dtype=np.float64)
+        mapq, flags = np.zeros(rl.size, np.uint8), np.zeros(rl.size, np.uint32)
+        fn(rl.size, rl.ctypes.data, ol.ctypes.data, s.ctypes.data, ns.ctypes.data, mapq.ctypes.data, flags.ctypes.data)
+        return mapq, flags
+
     def msa_row_extract(self, text, with_sequence: bool = True, chunk: int = 4096):
         """index-msa's per-sequence work: (gap words, unaligned bytes or None). The port restates
         index_vector_builder.cc:28-50; the reference build runs the reference's own index_vector_builder in `chunk`-byte

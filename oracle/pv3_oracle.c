@@ -632,3 +632,115 @@ uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos,
 	text_off[n] = at;
 	return at;
 }
+
+/* ---- recalculate-mapq: alignment rescoring and the Bowtie 2 (v2) MAPQ formula -----------------------------------------
+ * PARITY UNPINNED: both functions live in recalculate-mapq/main.cc (an anonymous namespace of the CLI's translation unit,
+ * which needs Boost.Iostreams and the gengetopt-generated cmdline.h — not buildable here); restated line by line. */
+#include <float.h>
+
+static void fill_penalties(int32_t *penalties, int32_t min, int32_t max)               /* main.cc:181-186 */
+{
+	for (size_t i = 0; i < 256; ++i) penalties[i] = (int32_t) ((i < 40 ? i : 40) / (double) 40 * (max - min) + min);
+}
+
+/* cigar_alignment_scorer::calculate_score, main.cc:190-283. flags[i] != 0 where the reference aborts or reads out of range
+ * (1 bad op, 4 SEQ too short, 8 X base beyond the XN bitmap, 0x40 QUAL too short). */
+void pv3o_rescore_alignments(const int32_t *scoring5, uint64_t n, const uint64_t *seq_off, const uint8_t *seq,
+	const uint64_t *qual_off, const uint8_t *qual, const uint64_t *cig_off, const uint32_t *cig,
+	const uint64_t *refn_off, const uint8_t *refn, double *score, uint32_t *flags)
+{
+	int32_t mm[256], np[256];
+	fill_penalties(mm, scoring5[0], scoring5[1]);
+	fill_penalties(np, scoring5[2], scoring5[2]);
+	int32_t const gap_open = scoring5[3], gap_ext = scoring5[4];
+	for (uint64_t i = 0; i < n; ++i) {
+		const uint8_t *q = seq + seq_off[i], *ql = qual + qual_off[i];
+		uint64_t const nq = seq_off[i + 1] - seq_off[i], nl = qual_off[i + 1] - qual_off[i];
+		const uint8_t *rn = refn_off ? refn + refn_off[i] : NULL;
+		uint64_t const nn = refn_off ? refn_off[i + 1] - refn_off[i] : 0;
+		uint64_t query_pos = 0, ref_pos = 0;
+		char prev_op = 0;
+		double retval = 0;
+		uint32_t f = 0;
+		for (uint64_t c = cig_off[i]; c < cig_off[i + 1] && !f; ++c) {
+			uint32_t const count = cig[c] >> 4;
+			char const op = "MIDNSHP=X???????"[cig[c] & 15];
+			switch (op) {
+				case 'H': case 'P': break;
+				case 'N': ref_pos += count; break;
+				case 'I':
+					if (!('I' == prev_op || 'D' == prev_op)) retval -= gap_open;
+					retval -= count * gap_ext;                  /* uint32_t * int32_t: unsigned, as in the reference */
+					query_pos += count; prev_op = op; break;
+				case 'D':
+					if (!('I' == prev_op || 'D' == prev_op)) retval -= gap_open;
+					retval -= count * gap_ext;
+					ref_pos += count; prev_op = op; break;
+				case 'S': query_pos += count; prev_op = op; break;
+				case '=':
+					for (uint64_t k = 0; k < count; ++k) {
+						if (query_pos + k >= nq) { f = 4; break; }
+						if (3 == q[query_pos + k]) {
+							if (query_pos + k >= nl) { f = 0x40; break; }
+							retval -= np[ql[query_pos + k]];
+						}
+					}
+					query_pos += count; ref_pos += count; prev_op = op; break;
+				case 'X':
+					for (uint64_t k = 0; k < count; ++k) {
+						uint64_t const qp = query_pos + k, rp = ref_pos + k;
+						if (qp >= nq) { f = 4; break; }
+						if (qp >= nl) { f = 0x40; break; }
+						if (rp / 8 >= nn) { f = 8; break; }
+						if (3 == q[qp] || ((0x1 << (rp % 8)) & rn[rp / 8])) retval -= np[ql[qp]];
+						else retval -= mm[ql[qp]];
+					}
+					query_pos += count; ref_pos += count; prev_op = op; break;
+				default: f = 1; break;
+			}
+		}
+		score[i] = retval; flags[i] = f;
+	}
+}
+
+static double read_min_score(uint32_t read_length) { if (!read_length) return 0; return -0.6 + (-0.6 * read_length); }   /* :455-460 */
+
+typedef struct { double diff, score; uint8_t mapq; } nu_entry;
+static const struct { double thr; uint8_t mapq; } unique_scores[7] = { {0.0, 0}, {0.3, 3}, {0.4, 8}, {0.5, 23}, {0.6, 24}, {0.7, 40}, {0.8, 42} };
+static const nu_entry non_unique_scores[30] = {
+	{0.0, 0.0, 2}, {0.0, 0.67, 6}, {0.1, 0.0, 0}, {0.1, 0.67, 7}, {0.1, 0.88, 12}, {0.1, 1.0, 30}, {0.2, 0.0, 0}, {0.2, 0.67, 11},
+	{0.2, 0.88, 17}, {0.2, 1.0, 31}, {0.3, 0.0, 3}, {0.3, 0.67, 15}, {0.3, 0.88, 18}, {0.3, 1.0, 32}, {0.4, 0.0, 4}, {0.4, 0.68, 14},
+	{0.4, 0.84, 21}, {0.4, 1.0, 34}, {0.5, 0.0, 5}, {0.5, 0.68, 16}, {0.5, 0.84, 25}, {0.5, 1.0, 35}, {0.6, 0.0, 22}, {0.6, 1.0, 36},
+	{0.7, 0.0, 26}, {0.7, 1.0, 37}, {0.8, 0.0, 27}, {0.8, 1.0, 38}, {0.9, 0.0, 33}, {0.9, 1.0, 39} };
+
+/* bowtie2_v2_score_calculator::calculate_mapq, main.cc:479-565. flags 0x10 where the reference would index before its table. */
+void pv3o_calculate_mapq(uint64_t n, const uint32_t *read_len, const uint32_t *other_len, const double *score_in, const double *next_in,
+	uint8_t *mapq, uint32_t *flags)
+{
+	for (uint64_t i = 0; i < n; ++i) {
+		double const score = score_in[i];
+		double const min_score = read_min_score(read_len[i]) + read_min_score(other_len[i]);
+		double const max_score = 0;
+		double const range0 = max_score - min_score;
+		double const score_range = 1.0 < range0 ? range0 : 1.0;
+		mapq[i] = 0; flags[i] = 0;
+		if (score < min_score) continue;
+		double const next_score = min_score < next_in[i] ? next_in[i] : min_score;
+		double const nsq = (score - min_score) / score_range;
+		double const diff_next = score - next_score;
+		double const dnq = diff_next / score_range;
+		if (-DBL_MAX == next_score) {
+			int k = 0;
+			while (k < 7 && !(nsq < unique_scores[k].thr)) ++k;
+			if (!k) flags[i] = 0x10; else mapq[i] = unique_scores[k - 1].mapq;
+		} else if (diff_next) {
+			int it = 0;
+			while (it < 30 && !(dnq < non_unique_scores[it].diff)) ++it;
+			if (!it) { flags[i] = 0x10; continue; }
+			double const thr = non_unique_scores[it - 1].diff;
+			int k = 0;
+			while (k < it && !(thr < non_unique_scores[k].diff || (!(non_unique_scores[k].diff < thr) && nsq < non_unique_scores[k].score))) ++k;
+			if (!k) flags[i] = 0x10; else mapq[i] = non_unique_scores[k - 1].mapq;
+		} else mapq[i] = nsq >= 0.67 ? 1 : 0;
+	}
+}

@@ -86,6 +86,14 @@ uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos,
 	const int32_t *nm, const uint8_t *has_nm, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
 	uint32_t n_names, const uint64_t *name_off, const char *names, uint64_t *text_off, char *text, uint64_t cap);
 
+/* recalculate-mapq (recalculate-mapq/main.cc:181-283 and :455-565). Port only (PARITY UNPINNED, see pv3_oracle.c).
+ * scoring5 = min/max mismatch, N, gap opening, gap extension penalty. */
+void pv3o_rescore_alignments(const int32_t *scoring5, uint64_t n, const uint64_t *seq_off, const uint8_t *seq,
+	const uint64_t *qual_off, const uint8_t *qual, const uint64_t *cig_off, const uint32_t *cig,
+	const uint64_t *refn_off, const uint8_t *refn, double *score, uint32_t *flags);
+void pv3o_calculate_mapq(uint64_t n, const uint32_t *read_len, const uint32_t *other_len, const double *score, const double *next_score,
+	uint8_t *mapq, uint32_t *flags);
+
 void pv3o_msa_row_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, uint64_t *n_ungapped);
 
 #ifdef __cplusplus

@@ -23,6 +23,7 @@ EXPORTED_SYMBOLS = [
     "pv3_total_launches", "pv3_host_alloc", "pv3_host_free",
     "pv3_index_file_open", "pv3_index_file_entries", "pv3_index_file_entry", "pv3_index_file_close", "pv3_index_file_write",
     "pv3_index_file_error", "pv3_msa_row_extract", "pv3_msa_row_extract_device", "pv3_format_oa", "pv3_format_cigars",
+    "pv3_rescore_alignments", "pv3_calculate_mapq",
 ]
 
 
@@ -112,6 +113,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_format_oa.argtypes = [C.c_void_p, C.POINTER(OaIn), C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.pv3_format_cigars.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                       C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.pv3_rescore_alignments.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64] + [C.c_void_p] * 10
+    lib.pv3_calculate_mapq.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 6
     for fn in (lib.pv3_msa_row_extract, lib.pv3_msa_row_extract_device):
         fn.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
     _lib = lib
@@ -300,6 +303,29 @@ class Context:
         text = np.zeros(max(int(used.value), 1), dtype=np.uint8)
         self._check(self.lib.pv3_format_cigars(self.h, n, _ptr(off_in), _ptr(ln), _ptr(cg), cg.size, _ptr(off), _ptr(text), used.value, C.byref(used)))
         return text[: used.value].tobytes(), off
+
+    def rescore_alignments(self, scoring5, seq_off, seq, qual_off, qual, cig_off, cig, refn_off=None, refn=None):
+        """recalculate-mapq's cigar_alignment_scorer (main.cc:190-283): (scores float64, flags). scoring5 = min / max mismatch,
+        N, gap opening, gap extension penalty."""
+        sc = np.ascontiguousarray(scoring5, dtype=np.int32)
+        so, sq = np.ascontiguousarray(seq_off, dtype=np.uint64), np.ascontiguousarray(seq, dtype=np.uint8)
+        qo, ql = np.ascontiguousarray(qual_off, dtype=np.uint64), np.ascontiguousarray(qual, dtype=np.uint8)
+        co, cg = np.ascontiguousarray(cig_off, dtype=np.uint64), np.ascontiguousarray(cig, dtype=np.uint32)
+        ro = None if refn_off is None else np.ascontiguousarray(refn_off, dtype=np.uint64)
+        rn = None if refn_off is None else np.ascontiguousarray(refn, dtype=np.uint8)
+        n = so.size - 1
+        score, flags = np.zeros(n, np.float64), np.zeros(n, np.uint32)
+        self._check(self.lib.pv3_rescore_alignments(self.h, _ptr(sc), n, _ptr(so), _ptr(sq), _ptr(qo), _ptr(ql), _ptr(co), _ptr(cg),
+                                                    _ptr(ro), _ptr(rn), _ptr(score), _ptr(flags)))
+        return score, flags
+
+    def calculate_mapq(self, read_len, other_len, score, next_score):
+        """recalculate-mapq's bowtie2_v2_score_calculator::calculate_mapq (main.cc:479-565) for n tuples: (mapq uint8, flags)."""
+        rl, ol = np.ascontiguousarray(read_len, dtype=np.uint32), np.ascontiguousarray(other_len, dtype=np.uint32)
+        s, ns = np.ascontiguousarray(score, dtype=np.float64), np.ascontiguousarray(next_score, dtype=np.float64)
+        mapq, flags = np.zeros(rl.size, np.uint8), np.zeros(rl.size, np.uint32)
+        self._check(self.lib.pv3_calculate_mapq(self.h, rl.size, _ptr(rl), _ptr(ol), _ptr(s), _ptr(ns), _ptr(mapq), _ptr(flags)))
+        return mapq, flags
 
     def msa_row_extract(self, text, with_sequence: bool = True):
         """index-msa's per-sequence work (index-msa/index_vector_builder.cc:28-50) on the GPU: (gap words, n_bits, unaligned

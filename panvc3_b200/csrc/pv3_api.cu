@@ -695,8 +695,16 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	float ms_main = 0;
 	int pending_d2h[2] = { 0, 0 };
 
+	bool const trace = getenv("PV3_TRACE") != nullptr;     // timeline of the chunks on stderr, ms since the call began
+	if (trace) cudaEventRecord(ctx->ev[7], streams[0]);
+	auto since = [&](cudaEvent_t e) { float t = -1; cudaEventElapsedTime(&t, ctx->ev[7], e); return t; };
 	auto harvest_copy_times = [&](int k) {
 		float t = 0;
+		if (trace) {
+			fprintf(stderr, "[pv3 trace] set %d: h2d %.3f-%.3f  kernels %.3f-%.3f", k, since(ctx->cev[k][0]), since(ctx->cev[k][1]), since(ctx->ev[0]), since(ctx->ev[1]));
+			if (pending_d2h[k]) fprintf(stderr, "  | previous d2h of this set %.3f-%.3f", since(ctx->cev[k][2]), since(ctx->cev[k][3]));
+			fprintf(stderr, "\n");
+		}
 		if (cudaEventElapsedTime(&t, ctx->cev[k][0], ctx->cev[k][1]) == cudaSuccess) ms_h2d += t;
 		if (pending_d2h[k] && cudaEventElapsedTime(&t, ctx->cev[k][2], ctx->cev[k][3]) == cudaSuccess) ms_d2h += t;
 		pending_d2h[k] = 0;
@@ -785,7 +793,10 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 	}
 	PV3_CUDA(ctx, cudaStreamSynchronize(streams[0]));
 	if (own_streams) PV3_CUDA(ctx, cudaStreamSynchronize(streams[1]));
-	for (int k = 0; k < 2; ++k) if (pending_d2h[k]) { float t = 0; if (cudaEventElapsedTime(&t, ctx->cev[k][2], ctx->cev[k][3]) == cudaSuccess) ms_d2h += t; }
+	for (int k = 0; k < 2; ++k) if (pending_d2h[k]) {
+		float t = 0; if (cudaEventElapsedTime(&t, ctx->cev[k][2], ctx->cev[k][3]) == cudaSuccess) ms_d2h += t;
+		if (trace) fprintf(stderr, "[pv3 trace] set %d: last d2h %.3f-%.3f\n", k, since(ctx->cev[k][2]), since(ctx->cev[k][3]));
+	}
 
 	out->cig_used = arena_off; out->rr_used = rr_base;
 	ctx->timing.ms_rewrite = ms_k[0]; ctx->timing.ms_realign = ms_k[1]; ctx->timing.ms_splice = ms_k[2]; ctx->timing.ms_total = ms_k[3];
@@ -966,6 +977,83 @@ int pv3_format_oa(pv3_ctx *ctx, const pv3_oa_in *in, uint64_t *text_off, char *t
 	uint64_t const n_cig = in->n ? in->cig_off[in->n] : 0;
 	uint64_t const names_bytes = in->n_names ? in->name_off[in->n_names] : 0;
 	return format_text(ctx, "pv3_format_oa", P, n_cig, names_bytes, text_off, text, text_cap, text_used);
+}
+
+// recalculate-mapq/main.cc:181-186 — cut-off at 40 like Bowtie 2; the double expression is truncated to int32
+static void fill_penalties(int32_t *penalties, int32_t const min, int32_t const max)
+{
+	for (size_t i = 0; i < 256; ++i) penalties[i] = (int32_t) (std::min(i, size_t(40)) / double(40) * (max - min) + min);
+}
+
+int pv3_rescore_alignments(pv3_ctx *ctx, const pv3_scoring *sc, uint64_t n, const uint64_t *seq_off, const uint8_t *seq,
+	const uint64_t *qual_off, const uint8_t *qual, const uint64_t *cig_off, const uint32_t *cig,
+	const uint64_t *refn_off, const uint8_t *refn, double *score, uint32_t *flags)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	cudaSetDevice(ctx->device);
+	if (!n) return PV3_OK;
+	if (!sc || !seq_off || !qual_off || !cig_off || !score || !flags) return fail(ctx, PV3_ERR_INVALID, "pv3_rescore_alignments: NULL argument");
+	cudaStream_t const st = ctx->stream;
+	int32_t lut[512];
+	fill_penalties(lut, sc->min_mismatch_penalty, sc->max_mismatch_penalty);
+	fill_penalties(lut + 256, sc->n_penalty, sc->n_penalty);
+	int slot = 0;
+	auto up = [&](const void *src, size_t bytes, const void **dev) -> cudaError_t {
+		DevBuf &b = ctx->an[slot++];
+		cudaError_t e = b.ensure(bytes + 16);
+		if (e != cudaSuccess) return e;
+		*dev = b.p;
+		return bytes ? cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess;
+	};
+	RescoreParams P;
+	memset(&P, 0, sizeof P);
+	P.n = n; P.gap_open = sc->gap_opening_penalty; P.gap_ext = sc->gap_extension_penalty;
+	const void *d_lut = nullptr;
+	PV3_CUDA(ctx, up(seq_off, (n + 1) * 8, (const void **) &P.seq_off));
+	PV3_CUDA(ctx, up(seq, seq_off[n], (const void **) &P.seq));
+	PV3_CUDA(ctx, up(qual_off, (n + 1) * 8, (const void **) &P.qual_off));
+	PV3_CUDA(ctx, up(qual, qual_off[n], (const void **) &P.qual));
+	PV3_CUDA(ctx, up(cig_off, (n + 1) * 8, (const void **) &P.cig_off));
+	PV3_CUDA(ctx, up(cig, cig_off[n] * 4, (const void **) &P.cig));
+	if (refn_off) {
+		PV3_CUDA(ctx, up(refn_off, (n + 1) * 8, (const void **) &P.refn_off));
+		PV3_CUDA(ctx, up(refn, refn_off[n], (const void **) &P.refn));
+	} else slot += 2;
+	PV3_CUDA(ctx, up(lut, sizeof lut, &d_lut));
+	P.mismatch_penalties = (const int32_t *) d_lut; P.n_penalties = (const int32_t *) d_lut + 256;
+	PV3_CUDA(ctx, ctx->an[slot].ensure(n * 8)); P.score = ctx->an[slot++].as <double>();
+	PV3_CUDA(ctx, ctx->an[slot].ensure(n * 4)); P.flags = ctx->an[slot++].as <uint32_t>();
+	launch_rescore(P, st);
+	PV3_CUDA(ctx, cudaGetLastError());
+	ctx->total_launches += 1;
+	PV3_CUDA(ctx, cudaMemcpyAsync(score, P.score, n * 8, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaMemcpyAsync(flags, P.flags, n * 4, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaStreamSynchronize(st));     // also keeps `lut` alive until its upload is done
+	return PV3_OK;
+}
+
+int pv3_calculate_mapq(pv3_ctx *ctx, uint64_t n, const uint32_t *read_len, const uint32_t *other_len, const double *score,
+	const double *next_score, uint8_t *mapq, uint32_t *flags)
+{
+	if (!ctx) return PV3_ERR_INVALID;
+	cudaSetDevice(ctx->device);
+	if (!n) return PV3_OK;
+	if (!read_len || !other_len || !score || !next_score || !mapq || !flags) return fail(ctx, PV3_ERR_INVALID, "pv3_calculate_mapq: NULL argument");
+	cudaStream_t const st = ctx->stream;
+	struct { const void *src; size_t bytes; } const ins[4] = { { read_len, n * 4 }, { other_len, n * 4 }, { score, n * 8 }, { next_score, n * 8 } };
+	for (int k = 0; k < 4; ++k) {
+		PV3_CUDA(ctx, ctx->an[k].ensure(ins[k].bytes));
+		PV3_CUDA(ctx, cudaMemcpyAsync(ctx->an[k].p, ins[k].src, ins[k].bytes, cudaMemcpyHostToDevice, st));
+	}
+	PV3_CUDA(ctx, ctx->an[4].ensure(n)); PV3_CUDA(ctx, ctx->an[5].ensure(n * 4));
+	launch_mapq(n, ctx->an[0].as <uint32_t>(), ctx->an[1].as <uint32_t>(), ctx->an[2].as <double>(), ctx->an[3].as <double>(),
+		ctx->an[4].as <uint8_t>(), ctx->an[5].as <uint32_t>(), st);
+	PV3_CUDA(ctx, cudaGetLastError());
+	ctx->total_launches += 1;
+	PV3_CUDA(ctx, cudaMemcpyAsync(mapq, ctx->an[4].p, n, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaMemcpyAsync(flags, ctx->an[5].p, n * 4, cudaMemcpyDeviceToHost, st));
+	PV3_CUDA(ctx, cudaStreamSynchronize(st));
+	return PV3_OK;
 }
 
 int pv3_format_cigars(pv3_ctx *ctx, uint64_t n, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig, uint64_t n_cig_words,

@@ -114,6 +114,22 @@ uint64_t msa_extract_scratch_words(uint64_t n);
 uint64_t msa_extract_total_word(uint64_t n);
 cudaError_t launch_msa_extract(const char *text, uint64_t n, uint64_t *gap_words, char *ungapped, unsigned long long *scratch,
 	cudaStream_t stream, unsigned *launches);
+// recalculate-mapq (pv3_mapq.cu)
+struct RescoreParams {
+	uint64_t        n;
+	const uint64_t *seq_off;  const uint8_t *seq;       // dna5 ranks
+	const uint64_t *qual_off; const uint8_t *qual;      // phred ranks
+	const uint64_t *cig_off;  const uint32_t *cig;
+	const uint64_t *refn_off; const uint8_t *refn;      // XN tag: bit (p % 8) of byte p / 8 set ⇔ reference position p of the alignment is N; refn_off null ⇒ no record has it
+	const int32_t  *mismatch_penalties, *n_penalties;   // [256] by quality rank
+	int32_t         gap_open, gap_ext;
+	double         *score;
+	uint32_t       *flags;
+};
+void launch_rescore(const RescoreParams &P, cudaStream_t stream);
+void launch_mapq(uint64_t n, const uint32_t *read_len, const uint32_t *other_len, const double *score, const double *next_score,
+	uint8_t *mapq, uint32_t *flags, cudaStream_t stream);
+
 // exclusive scan of 32-bit counts into 64-bit offsets, one CTA (cnt 16-byte aligned and padded to a multiple of four; off[n] = total)
 void launch_scan_u32(const uint32_t *cnt, uint64_t n, unsigned long long *off, cudaStream_t stream);
 

@@ -188,3 +188,38 @@ def test_convert_bed_position_equals_project_position(kind, port, request, workf
         for p in [0, 1, n_src - 1, *rng.integers(0, n_src, 60).tolist()]:
             for dst in (0, (src + 1) % workflow_msa.n_rows):
                 assert _convert_position(oi, src, dst, int(p)) == oi.project_position(src, dst, int(p))
+
+
+# ---------------------------------------------------------------------------------------------- recalculate-mapq (N4)
+def test_calculate_mapq_known_answers(port):
+    """Hand-evaluated from recalculate-mapq/main.cc:479-565 (min score -0.6 - 0.6 L, tables :378-430): a perfect unique hit
+    (next clamped to the minimum: diff quotient 1.0 → last group → 39), equal scores, below the minimum, two close hits, a pair."""
+    mapq, flags = port.calculate_mapq([100, 100, 100, 100, 100, 100], [0, 0, 0, 0, 100, 0], [0.0, -30.0, -61.0, -10.0, -20.0, -30.0],
+                                      [-1.7976931348623157e308, -30.0, -70.0, -12.0, -50.0, -20.0])
+    assert mapq.tolist() == [39, 0, 0, 6, 11, 0] and flags.tolist() == [0, 0, 0, 0, 0, 0x10]
+
+
+def test_rescore_known_answers(port):
+    """main.cc:190-283 with the default penalties (2..6 by quality, N 1, gap 5 + 3 per base): 3S 10= 2X 1I 1D 5= ; one X at
+    quality 40 (6) and one at quality 0 (2); I directly followed by D opens once; N in the query inside '=' costs 1."""
+    def rec(cigar, seq, qual, refn=b"\\0\\0\\0\\0"):
+        return parse_cigar(cigar), np.frombuffer(seq.encode(), np.uint8), np.array(qual, np.uint8), np.frombuffer(refn, np.uint8)
+    from panvc3_b200.batch import ranks_from_ascii
+    cases = [("3S10=2X1I1D5=", "ACG" + "ACGTACGTAC" + "GT" + "A" + "CCNCC", [30] * 13 + [40, 0] + [10] * 6, -(6 + 2) - (5 + 3 + 3) - 1),
+             ("4=1I2=1I1=", "ACGTACGTA", [20] * 9, -(5 + 3) - (5 + 3)),
+             ("2H3=2N2X", "ACGTT", [41, 41, 41, 20, 41], None),      # second X base: reference position 6 is N in the bitmap below
+             ("5M", "ACGTA", [1] * 5, None)]
+    seqs = [ranks_from_ascii(c[1]) for c in cases]
+    cigs = [parse_cigar(c[0]) for c in cases]
+    quals = [np.array(c[2], np.uint8) for c in cases]
+    refn = [np.zeros(4, np.uint8), np.zeros(2, np.uint8), np.array([0x40], np.uint8), np.zeros(1, np.uint8)]
+    off = lambda parts: np.concatenate([[0], np.cumsum([len(p) for p in parts])]).astype(np.uint64)
+    score, flags = port.rescore_alignments([2, 6, 1, 5, 3], off(seqs), np.concatenate(seqs), off(quals), np.concatenate(quals),
+                                           off(cigs), np.concatenate(cigs), off(refn), np.concatenate(refn))
+    assert score[0] == cases[0][3] and score[1] == cases[1][3] and flags[:2].tolist() == [0, 0]
+    assert score[2] == -(int(20 / 40 * 4 + 2)) - 1 and flags[2] == 0          # X at quality 20 → 4; X on a reference N → 1
+    assert flags[3] == 1                                                      # 'M' is an error in the reference
+    # no XN tag at all: the first X base trips the reference's assertion
+    _, flags = port.rescore_alignments([2, 6, 1, 5, 3], off(seqs), np.concatenate(seqs), off(quals), np.concatenate(quals),
+                                       off(cigs), np.concatenate(cigs))
+    assert flags.tolist() == [8, 0, 8, 1]
