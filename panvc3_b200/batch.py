@@ -179,6 +179,32 @@ class RecordBatch:
             kw["seq_len"] = self.seq_len[begin:end]
         return RecordBatch(**kw)
 
+    def take(self, order) -> "RecordBatch":
+        """The records in the given order (a permutation or any index list), variable-length fields regathered."""
+        order = np.asarray(order, dtype=np.int64)
+
+        def regather(off, data):
+            lens = (off[1:] - off[:-1])[order].astype(np.int64)
+            new_off = np.zeros(order.size + 1, dtype=np.uint64)
+            new_off[1:] = np.cumsum(lens)
+            src = np.repeat(off[:-1][order].astype(np.int64) - new_off[:-1].astype(np.int64), lens) + np.arange(int(new_off[-1]), dtype=np.int64)
+            return new_off, data[src]
+
+        seq_off, seq = regather(self.seq_off, self.seq)
+        cig_off, cig = regather(self.cig_off, self.cig)
+        kw = dict(src_row=self.src_row[order], dst_row=self.dst_row[order], dst_ref=self.dst_ref[order], src_pos=self.src_pos[order],
+                  seq_off=seq_off, seq=seq, cig_off=cig_off, cig=cig)
+        if self.qual_off is not None:
+            kw["qual_off"], kw["qual"] = regather(self.qual_off, self.qual)
+        if self.seq_len is not None:
+            kw["seq_len"] = self.seq_len[order]
+        return RecordBatch(**kw)
+
+    def coordinate_sorted(self) -> "RecordBatch":
+        """Sorted by (source row, source position): the order `samtools sort` gives the BAM that project_alignments reads in
+        the reference's workflow (test-workflow/Snakefile: alignments.sorted.bam)."""
+        return self.take(np.lexsort((self.src_pos, self.src_row)))
+
     def to_bam4(self) -> "RecordBatch":
         """The same records with SEQ as a BAM file stores it: 4-bit codes (A=1 C=2 G=4 T=8 N=15), two bases per byte, first
         base in the high nibble, records byte-aligned; seq_off counts bytes and seq_len bases."""

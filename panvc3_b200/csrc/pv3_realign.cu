@@ -45,6 +45,7 @@ __device__ __forceinline__ int trace_pick(uint32_t t)
 uint32_t k3_smem_pool_bytes() { return SMEM_POOL; }
 uint64_t k3_default_grid_warps(int n_sms) { return (uint64_t) n_sms * 4 * K3_WARPS; }
 
+template <bool PACKED>   // PACKED: SEQ in BAM's 4-bit packing (K1Params::seq_len)
 __global__ void __launch_bounds__(K3_WARPS * 32)
 k3_realign_kernel(K3Params P)
 {
@@ -67,7 +68,13 @@ k3_realign_kernel(K3Params P)
 		uint32_t const R = job.ref_len, Q = job.qry_len;
 		uint32_t const cols = R + 1;
 		const char *rbase = B.refs[__ldg(B.dst_ref + rec)].bases + job.ref_loc;
-		uint64_t const qbase = __ldg(B.seq_off + rec), qloc = job.qry_loc;
+		uint32_t const qloc = job.qry_loc;
+		const uint8_t *qptr = B.seq + __ldg(B.seq_off + rec) + (PACKED ? 0u : qloc);
+		auto qrank = [&](uint32_t w) -> uint8_t {                       // rank of base w of the run's query window
+			if (!PACKED) return __ldg(qptr + w);
+			uint32_t const g = qloc + w, b = __ldg(qptr + (g >> 1));
+			return (uint8_t) bam4_to_rank((g & 1u) ? b : (b >> 4));
+		};
 		bool has_qual = false;
 		const uint8_t *qlptr = nullptr;
 		if (B.qual_off) {
@@ -102,7 +109,7 @@ k3_realign_kernel(K3Params P)
 			uint32_t const i = i0 + 1 + lane;
 			bool const row_ok = i <= Q;
 			uint32_t const nl = (Q - i0 < 32u) ? (Q - i0) : 32u;
-			uint8_t const qi = row_ok ? query_rank(B, qbase, qloc + i - 1) : 0;
+			uint8_t const qi = row_ok ? qrank(i - 1) : 0;
 			int32_t s_match, s_mis;
 			if (edit) { s_match = 0; s_mis = 1; }
 			else if (has_qual) {
@@ -176,7 +183,7 @@ k3_realign_kernel(K3Params P)
 			if (cur_op != OP_NONE) { --wp; if (lane == 0) out[wp] = (cur_cnt << 4) | cur_op; }
 			cur_op = op; cur_cnt = 1;
 		};
-		auto diag_op = [&]() -> uint32_t { return (rs[j - 1] == query_rank(B, qbase, qloc + i - 1)) ? OP_EQ : OP_X; };   // align.hh:104-107
+		auto diag_op = [&]() -> uint32_t { return (rs[j - 1] == qrank(i - 1)) ? OP_EQ : OP_X; };   // align.hh:104-107
 
 		if (edit) {
 			while (i > 0 || j > 0) {
@@ -219,7 +226,8 @@ void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t s
 	uint64_t warps = grid_warps ? grid_warps : k3_default_grid_warps(n_sms);
 	if (warps > n) warps = n;
 	unsigned const blocks = (unsigned) ((warps + K3_WARPS - 1) / K3_WARPS);
-	k3_realign_kernel<<<blocks, K3_WARPS * 32, 0, stream>>>(P);
+	if (P.k1.seq_len) k3_realign_kernel <true><<<blocks, K3_WARPS * 32, 0, stream>>>(P);
+	else k3_realign_kernel <false><<<blocks, K3_WARPS * 32, 0, stream>>>(P);
 }
 
 } // namespace pv3

@@ -37,6 +37,7 @@ __device__ __forceinline__ int pick(uint32_t t)
 
 } // namespace
 
+template <bool PACKED>   // PACKED: SEQ in BAM's 4-bit packing (K1Params::seq_len)
 __global__ void __launch_bounds__(128)
 k3_thread_kernel(K3Params P)
 {
@@ -80,7 +81,12 @@ k3_thread_kernel(K3Params P)
 
 	uint32_t const cols = R + 1;
 	const char *rbase = B.refs[__ldg(B.dst_ref + rec)].bases + ref_loc;
-	uint64_t const qbase = __ldg(B.seq_off + rec);
+	const uint8_t *qptr = B.seq + __ldg(B.seq_off + rec) + (PACKED ? 0u : qry_loc);
+	auto qrank = [&](uint32_t w) -> uint8_t {                       // rank of base w of the run's query window
+		if (!PACKED) return __ldg(qptr + w);
+		uint32_t const g = qry_loc + w, b = __ldg(qptr + (g >> 1));
+		return (uint8_t) bam4_to_rank((g & 1u) ? b : (b >> 4));
+	};
 	bool has_qual = false;
 	const uint8_t *qlptr = nullptr;
 	if (B.qual_off) {
@@ -111,7 +117,7 @@ k3_thread_kernel(K3Params P)
 		uint32_t const n_cells = R * Q;
 		for (uint32_t c = 0; c < n_cells; ++c) {
 			if (j == 1) {                                                                 // row start
-				qi = query_rank(B, qbase, qry_loc + i - 1);
+				qi = qrank(i - 1);
 				if (edit) { s_match = 0; s_mis = 1; Hcur = (int32_t) i; }
 				else {
 					if (has_qual) { uint32_t ql = __ldg(qlptr + i - 1); if (ql > 41) ql = 41; s_match = P.lut[2 * ql]; s_mis = P.lut[2 * ql + 1]; }
@@ -164,7 +170,7 @@ k3_thread_kernel(K3Params P)
 				uint32_t const t = (i > 0 && j > 0) ? T[i * cols + j] : 0u;
 				if (j > 0 && (i == 0 || (t & 1u))) { op = OP_D; --j; }                      // Left  ⇒ gap in query ⇒ D
 				else if (i > 0 && (j == 0 || (t & 2u))) { op = OP_I; --i; }                 // Up    ⇒ gap in reference ⇒ I
-				else { op = (rs[j - 1] == query_rank(B, qbase, qry_loc + i - 1)) ? OP_EQ : OP_X; --i; --j; }   // align.hh:104-107
+				else { op = (rs[j - 1] == qrank(i - 1)) ? OP_EQ : OP_X; --i; --j; }   // align.hh:104-107
 			} else {
 				if (tr == 0) break;
 				if ((dir == TD_UP && i == 0) || (dir == TD_LEFT && j == 0) || (dir == TD_DIAG && (i == 0 || j == 0))
@@ -172,7 +178,7 @@ k3_thread_kernel(K3Params P)
 				uint32_t const old = tr;
 				if (dir == TD_UP) { op = OP_I; --i; tr = T[i * cols + j]; if (old & TT_UO) dir = pick(tr); }
 				else if (dir == TD_LEFT) { op = OP_D; --j; tr = T[i * cols + j]; if (old & TT_LO) dir = pick(tr); }
-				else { op = (rs[j - 1] == query_rank(B, qbase, qry_loc + i - 1)) ? OP_EQ : OP_X; --i; --j; tr = T[i * cols + j]; dir = pick(tr); }
+				else { op = (rs[j - 1] == qrank(i - 1)) ? OP_EQ : OP_X; --i; --j; tr = T[i * cols + j]; dir = pick(tr); }
 			}
 			if (op == cur_op) ++cur_cnt;
 			else {
@@ -196,7 +202,8 @@ void launch_k3_thread(const K3Params &P, cudaStream_t stream)
 	if (!P.n_jobs) return;
 	unsigned const threads = 128;
 	unsigned const blocks = (unsigned) ((P.n_jobs + threads - 1) / threads);
-	k3_thread_kernel<<<blocks, threads, 0, stream>>>(P);
+	if (P.k1.seq_len) k3_thread_kernel <true><<<blocks, threads, 0, stream>>>(P);
+	else k3_thread_kernel <false><<<blocks, threads, 0, stream>>>(P);
 }
 
 } // namespace pv3

@@ -130,7 +130,8 @@ __device__ RecordResult rewrite_record(const K1Params &P, uint64_t rec, uint32_t
 	RowDesc const S = P.rows[sr];
 	RowDesc const D = P.rows[dr];
 	RefDesc const R = P.refs[rf];
-	uint64_t const qbase = __ldg(P.seq_off + rec);
+	const uint8_t *qptr = P.seq + __ldg(P.seq_off + rec);
+	bool const seq_packed = P.seq_len != nullptr;                      // SEQ in BAM's 4-bit packing
 	uint64_t const nq = query_length(P, rec);
 	if (P.qual_off) {
 		uint64_t const ql = __ldg(P.qual_off + rec + 1) - __ldg(P.qual_off + rec);
@@ -204,7 +205,7 @@ __device__ RecordResult rewrite_record(const K1Params &P, uint64_t rec, uint32_t
 								uint64_t const ei = ecur + __popc(dz & lt);
 								if (qi >= nq) lane_err |= PV3_FLAG_QUERY_OOB;          // :102
 								else if (ei >= R.n) lane_err |= PV3_FLAG_REF_OOB;       // :103
-								else code = (dna5_to_char(query_rank(P, qbase, qi)) == __ldg(R.bases + ei)) ? OP_EQ : OP_X;
+								else code = (dna5_to_char(seq_packed ? (uint8_t) bam4_to_rank((qi & 1u) ? __ldg(qptr + (qi >> 1)) : (uint32_t) (__ldg(qptr + (qi >> 1)) >> 4)) : __ldg(qptr + qi)) == __ldg(R.bases + ei)) ? OP_EQ : OP_X;
 							} else code = OP_D;
 						} else if (mlike) code = OP_I;
 					} else if (dz & bit) code = OP_D;
