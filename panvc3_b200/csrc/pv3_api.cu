@@ -412,6 +412,7 @@ cudaError_t small_copy(void *dst, const void *src, size_t bytes, cudaStream_t st
 int fetch_counters(pv3_ctx *ctx, cudaStream_t stream)
 {
 	PV3_CUDA(ctx, small_copy(ctx->h_counters, ctx->counters.p, sizeof(Counters), stream));
+	ctx->timing.launches += 1;
 	PV3_CUDA(ctx, cudaStreamSynchronize(stream));
 	return PV3_OK;
 }
@@ -528,6 +529,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 					PV3_CUDA(ctx, cudaMallocHost((void **) &ctx->h_job_qual_off, ctx->h_jobs_cap * 8));
 				}
 				PV3_CUDA(ctx, small_copy(ctx->h_jobs, ctx->jobs.p, n_jobs * sizeof(Job), stream));
+				ctx->timing.launches += 1;
 				PV3_CUDA(ctx, cudaStreamSynchronize(stream));
 				uint64_t need = 0;
 				for (uint64_t j = 0; j < n_jobs; ++j) need += ctx->h_jobs[j].qry_len;
@@ -547,6 +549,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 				PV3_CUDA(ctx, ctx->d_job_qual_off.ensure(n_jobs * 8));
 				PV3_CUDA(ctx, small_copy(ctx->d_packed.p, ctx->h_packed, w, stream));
 				PV3_CUDA(ctx, small_copy(ctx->d_job_qual_off.p, ctx->h_job_qual_off, n_jobs * 8, stream));
+				ctx->timing.launches += (w ? 1 : 0) + 1;
 				K.packed_qual = ctx->d_packed.as <uint8_t>();
 				K.job_qual_off = ctx->d_job_qual_off.as <uint64_t>();
 			}
