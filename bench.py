@@ -303,7 +303,7 @@ def run_reference_arm(args) -> None:
                              "sample": f"{n} records per step, {cores} threads, one projector per thread"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_gpu_arm(args) -> None:
@@ -500,12 +500,33 @@ def run_gpu_arm(args) -> None:
             line["realign_dp"] = realign_dp_leg(ctx, dev, 250_000, 3)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(msa, batch)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def claim_stdout() -> None:
+    """stdout must carry exactly ONE JSON line, but libraries write there too (NCCL prints its version banner with printf when
+    NCCL_DEBUG is set on the box): keep the real stdout aside for the result and point fd 1 at stderr for everything else."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main() -> None:
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
