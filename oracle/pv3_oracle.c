@@ -634,8 +634,9 @@ uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos,
 }
 
 /* ---- recalculate-mapq: alignment rescoring and the Bowtie 2 (v2) MAPQ formula -----------------------------------------
- * PARITY UNPINNED: both functions live in recalculate-mapq/main.cc (an anonymous namespace of the CLI's translation unit,
- * which needs Boost.Iostreams and the gengetopt-generated cmdline.h — not buildable here); restated line by line. */
+ * PINNED: both functions live in the first part of recalculate-mapq/main.cc; the CLI's translation unit is not buildable
+ * here, but `make ref` cuts that part out of the file where it lies and compiles it (oracle/ref_driver_mapq.cc), and
+ * tests/test_oracle.py::test_rescore_and_mapq_port_match_the_reference_code compares this restatement with it. */
 #include <float.h>
 
 static void fill_penalties(int32_t *penalties, int32_t min, int32_t max)               /* main.cc:181-186 */

@@ -86,7 +86,8 @@ uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos,
 	const int32_t *nm, const uint8_t *has_nm, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
 	uint32_t n_names, const uint64_t *name_off, const char *names, uint64_t *text_off, char *text, uint64_t cap);
 
-/* recalculate-mapq (recalculate-mapq/main.cc:181-283 and :455-565). Port only (PARITY UNPINNED, see pv3_oracle.c).
+/* recalculate-mapq (recalculate-mapq/main.cc:181-283 and :455-565). Port: pv3_oracle.c; reference: ref_driver_mapq.cc (the
+ * reference's own code, excerpted at build time). In the reference build flags are 0xffffffff where the reference aborted.
  * scoring5 = min/max mismatch, N, gap opening, gap extension penalty. */
 void pv3o_rescore_alignments(const int32_t *scoring5, uint64_t n, const uint64_t *seq_off, const uint8_t *seq,
 	const uint64_t *qual_off, const uint8_t *qual, const uint64_t *cig_off, const uint32_t *cig,

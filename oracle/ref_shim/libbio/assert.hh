@@ -5,7 +5,7 @@
  * lib/libbio/include/libbio/assert.hh:9-10, needs boost/stacktrace.hpp which this image lacks).
  * It provides only the macros the hot-path sources use:
  *   rewrite_cigar.hh:102-103,150; msa_index.hh:23,223; cigar.hh:146; indel_run_checker.cc:97.
- * Failures print a message and abort(), like libbio_fail in the reference.
+ * Failures print a message and abort(), like libbio_fail in the reference (or throw, with PV3_SHIM_FAIL_THROWS).
  */
 #ifndef PV3_REF_SHIM_LIBBIO_ASSERT_HH
 #define PV3_REF_SHIM_LIBBIO_ASSERT_HH
@@ -14,6 +14,8 @@
 #include <iostream>
 
 namespace libbio { namespace shim {
+	struct failure {};
+
 	template <typename... t_args>
 	[[noreturn]] void fail(char const *file, int line, t_args const &... args)
 	{
@@ -22,9 +24,21 @@ namespace libbio { namespace shim {
 		std::cerr << std::endl;
 		std::abort();
 	}
+
+	// For drivers that report the reference's aborts as per-record flags (oracle/ref_driver_mapq.cc). A separate name: the
+	// two behaviours live in one shared object.
+	template <typename... t_args>
+	[[noreturn]] void fail_throwing(char const *, int, t_args const &...)
+	{
+		throw failure{};
+	}
 }}
 
+#ifdef PV3_SHIM_FAIL_THROWS
+#	define libbio_fail(...)			::libbio::shim::fail_throwing(__FILE__, __LINE__, __VA_ARGS__)
+#else
 #define libbio_fail(...)				::libbio::shim::fail(__FILE__, __LINE__, __VA_ARGS__)
+#endif
 #define libbio_always_assert(X)			do { if (!(X)) libbio_fail("assertion failed: ", #X); } while (false)
 #define libbio_always_assert_lt(A, B)	libbio_always_assert((A) < (B))
 #define libbio_always_assert_lte(A, B)	libbio_always_assert((A) <= (B))

@@ -106,3 +106,50 @@ def random_pairs(seed: int, n: int, max_len: int = 40, similar: float = 0.7):
         qual = rng.integers(0, 42, q.size).astype(np.uint8)
         out.append((r, q, qual))
     return out
+
+
+# ---- recalculate-mapq: random records for the rescoring kernel (CIGARs of = X I D S H P N, QUAL, XN bitmaps) -----------------
+def rescore_inputs(rng, n, with_errors=False):
+    seqs, quals, cigs, refns = [], [], [], []
+    for i in range(n):
+        ops, qlen, rlen = [], 0, 0
+        for _ in range(int(rng.integers(1, 9))):
+            op = int(rng.choice([7, 7, 7, 8, 8, 1, 2, 4, 5, 6, 3]))
+            cnt = int(rng.integers(1, 40))
+            ops.append((cnt << 4) | op)
+            qlen += cnt if op in (7, 8, 1, 4) else 0
+            rlen += cnt if op in (7, 8, 2, 3) else 0
+        if with_errors and i % 17 == 0:
+            ops.append((3 << 4) | 0)                                  # an M
+        seq = rng.choice([0, 1, 2, 3, 4], qlen, p=[.24, .24, .24, .04, .24]).astype(np.uint8)
+        qual = rng.integers(0, 42, qlen).astype(np.uint8)
+        refn = (rng.random((rlen + 7) // 8 + 1) < 0.05).astype(np.uint8) * rng.integers(1, 256, (rlen + 7) // 8 + 1).astype(np.uint8)
+        if with_errors and i % 13 == 0:
+            seq = seq[: max(qlen - 3, 0)]
+        if with_errors and i % 11 == 0:
+            qual = qual[: max(qlen - 2, 0)]
+        if with_errors and i % 7 == 0:
+            refn = refn[:1]
+        seqs.append(seq); quals.append(qual); cigs.append(np.array(ops, np.uint32)); refns.append(refn)
+    off = lambda parts: np.concatenate([[0], np.cumsum([len(p) for p in parts])]).astype(np.uint64)
+    cat = lambda parts, dt: np.concatenate(parts).astype(dt) if sum(len(p) for p in parts) else np.zeros(0, dt)
+    return (off(seqs), cat(seqs, np.uint8), off(quals), cat(quals, np.uint8), off(cigs), cat(cigs, np.uint32), off(refns), cat(refns, np.uint8))
+
+
+def mapq_inputs(rng, n):
+    """(read_len, other_len, score, next_score) tuples for calculate_mapq: random scores, scores that put the quotients on and
+    one ulp around every table threshold, next scores at -DBL_MAX, equal to, below and (2 %) above the score."""
+    rl = rng.choice([0, 1, 36, 100, 150, 151, 250, 10_000], n).astype(np.uint32)
+    ol = np.where(rng.random(n) < 0.5, 0, rng.choice([0, 100, 150, 250], n)).astype(np.uint32)
+    min_score = np.where(rl > 0, -0.6 + -0.6 * rl, 0.0) + np.where(ol > 0, -0.6 + -0.6 * ol, 0.0)
+    score = np.round(min_score * rng.random(n) * 1.05)
+    nxt = np.where(rng.random(n) < 0.3, -np.finfo(np.float64).max, np.minimum(score, np.round(min_score * rng.random(n) * 1.2)))
+    rngs = np.maximum(1.0, -min_score)
+    t = rng.choice([0.0, 0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.67, 0.68, 0.7, 0.8, 0.84, 0.88, 0.9, 1.0], n)
+    exact = min_score + t * rngs
+    pick = rng.random(n) < 0.3
+    score = np.where(pick, np.nextafter(exact, rng.choice([-np.inf, np.inf], n)), score)
+    score = np.where(rng.random(n) < 0.1, exact, score)
+    nxt = np.where(rng.random(n) < 0.2, score - t * rngs, nxt)
+    nxt = np.where(rng.random(n) < 0.02, score + 1.0, nxt)
+    return rl, ol, score, nxt

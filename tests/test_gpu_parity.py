@@ -544,40 +544,13 @@ def test_bam4_packed_seq_realistic_and_long_reads(gpu, port, workflow_msa):
 
 
 # ---------------------------------------------------------------------------------------------- recalculate-mapq (N4)
-def _rescore_inputs(rng, n, with_errors=False):
-    seqs, quals, cigs, refns = [], [], [], []
-    for i in range(n):
-        ops, qlen, rlen = [], 0, 0
-        for _ in range(int(rng.integers(1, 9))):
-            op = int(rng.choice([7, 7, 7, 8, 8, 1, 2, 4, 5, 6, 3]))
-            cnt = int(rng.integers(1, 40))
-            ops.append((cnt << 4) | op)
-            qlen += cnt if op in (7, 8, 1, 4) else 0
-            rlen += cnt if op in (7, 8, 2, 3) else 0
-        if with_errors and i % 17 == 0:
-            ops.append((3 << 4) | 0)                                  # an M
-        seq = rng.choice([0, 1, 2, 3, 4], qlen, p=[.24, .24, .24, .04, .24]).astype(np.uint8)
-        qual = rng.integers(0, 42, qlen).astype(np.uint8)
-        refn = (rng.random((rlen + 7) // 8 + 1) < 0.05).astype(np.uint8) * rng.integers(1, 256, (rlen + 7) // 8 + 1).astype(np.uint8)
-        if with_errors and i % 13 == 0:
-            seq = seq[: max(qlen - 3, 0)]
-        if with_errors and i % 11 == 0:
-            qual = qual[: max(qlen - 2, 0)]
-        if with_errors and i % 7 == 0:
-            refn = refn[:1]
-        seqs.append(seq); quals.append(qual); cigs.append(np.array(ops, np.uint32)); refns.append(refn)
-    off = lambda parts: np.concatenate([[0], np.cumsum([len(p) for p in parts])]).astype(np.uint64)
-    cat = lambda parts, dt: np.concatenate(parts).astype(dt) if sum(len(p) for p in parts) else np.zeros(0, dt)
-    return (off(seqs), cat(seqs, np.uint8), off(quals), cat(quals, np.uint8), off(cigs), cat(cigs, np.uint32), off(refns), cat(refns, np.uint8))
-
-
 @pytest.mark.parametrize("scoring", [[2, 6, 1, 5, 3], [0, 0, 0, 0, 0], [1, 9, 4, 11, 2], [6, 2, 3, 1, 7]])
 def test_rescore_alignments_matches_oracle(gpu, port, scoring):
     """cigar_alignment_scorer::calculate_score (recalculate-mapq/main.cc:190-283): scores equal as doubles, same error flags."""
     from panvc3_b200.capi import Context
     ctx = Context(0)
     for with_errors in (False, True):
-        a = _rescore_inputs(np.random.default_rng(sum(scoring) + int(with_errors)), 5000, with_errors)
+        a = casegen.rescore_inputs(np.random.default_rng(sum(scoring) + int(with_errors)), 5000, with_errors)
         es, ef = port.rescore_alignments(scoring, *a)
         s, f = ctx.rescore_alignments(scoring, *a)
         np.testing.assert_array_equal(f, ef)
@@ -585,7 +558,7 @@ def test_rescore_alignments_matches_oracle(gpu, port, scoring):
         np.testing.assert_array_equal(s[ok], es[ok])
         assert with_errors == bool((ef != 0).any())
     # no record has the XN tag
-    a = _rescore_inputs(np.random.default_rng(99), 2000)
+    a = casegen.rescore_inputs(np.random.default_rng(99), 2000)
     es, ef = port.rescore_alignments(scoring, *a[:6])
     s, f = ctx.rescore_alignments(scoring, *a[:6])
     np.testing.assert_array_equal(f, ef)
@@ -597,22 +570,7 @@ def test_calculate_mapq_matches_oracle(gpu, port):
     including scores that put the quotients exactly on and one ulp around the table thresholds."""
     from panvc3_b200.capi import Context
     ctx = Context(0)
-    rng = np.random.default_rng(8)
-    n = 400_000
-    rl = rng.choice([0, 1, 36, 100, 150, 151, 250, 10_000], n).astype(np.uint32)
-    ol = np.where(rng.random(n) < 0.5, 0, rng.choice([0, 100, 150, 250], n)).astype(np.uint32)
-    min_score = np.where(rl > 0, -0.6 + -0.6 * rl, 0.0) + np.where(ol > 0, -0.6 + -0.6 * ol, 0.0)
-    score = np.round(min_score * rng.random(n) * 1.05)
-    nxt = np.where(rng.random(n) < 0.3, -np.finfo(np.float64).max, np.minimum(score, np.round(min_score * rng.random(n) * 1.2)))
-    # thresholds: score = min + t * range, nudged by an ulp either way
-    rngs = np.maximum(1.0, -min_score)
-    t = rng.choice([0.0, 0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.67, 0.68, 0.7, 0.8, 0.84, 0.88, 0.9, 1.0], n)
-    exact = min_score + t * rngs
-    pick = rng.random(n) < 0.3
-    score = np.where(pick, np.nextafter(exact, rng.choice([-np.inf, np.inf], n)), score)
-    score = np.where(rng.random(n) < 0.1, exact, score)
-    nxt = np.where(rng.random(n) < 0.2, score - t * rngs, nxt)
-    nxt = np.where(rng.random(n) < 0.02, score + 1.0, nxt)            # next above score: flagged
+    rl, ol, score, nxt = casegen.mapq_inputs(np.random.default_rng(8), 400_000)
     em, ef = port.calculate_mapq(rl, ol, score, nxt)
     m, f = ctx.calculate_mapq(rl, ol, score, nxt)
     np.testing.assert_array_equal(f, ef)

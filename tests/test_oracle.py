@@ -223,3 +223,32 @@ def test_rescore_known_answers(port):
     _, flags = port.rescore_alignments([2, 6, 1, 5, 3], off(seqs), np.concatenate(seqs), off(quals), np.concatenate(quals),
                                        off(cigs), np.concatenate(cigs))
     assert flags.tolist() == [8, 0, 8, 1]
+
+
+def test_rescore_and_mapq_port_match_the_reference_code(port, ref):
+    """PINS the N4 port: the same inputs through the reference's own cigar_alignment_scorer::calculate_score and
+    bowtie2_v2_score_calculator::calculate_mapq (recalculate-mapq/main.cc, compiled from an excerpt cut at build time,
+    oracle/ref_driver_mapq.cc). Scores and MAPQs equal; the reference's aborts (an M op, an X base beyond the XN bitmap)
+    coincide with the port's flags."""
+    for scoring in ([2, 6, 1, 5, 3], [1, 9, 4, 11, 2], [6, 2, 3, 1, 7]):
+        for with_errors in (False, True):
+            a = casegen.rescore_inputs(np.random.default_rng(sum(scoring) + int(with_errors)), 3000, with_errors)
+            ps, pf = port.rescore_alignments(scoring, *a)
+            rs, rf = ref.rescore_alignments(scoring, *a)
+            np.testing.assert_array_equal(pf != 0, rf != 0)
+            aborted = rf == 0xFFFFFFFF
+            assert set(np.unique(pf[aborted]).tolist()) <= {1, 8}
+            ok = rf == 0
+            np.testing.assert_array_equal(ps[ok], rs[ok])
+            assert with_errors == bool(aborted.any())
+    a = casegen.rescore_inputs(np.random.default_rng(5), 1000)
+    ps, pf = port.rescore_alignments([2, 6, 1, 5, 3], *a[:6])        # no XN tag: every record with an X aborts in the reference
+    rs, rf = ref.rescore_alignments([2, 6, 1, 5, 3], *a[:6])
+    np.testing.assert_array_equal(pf != 0, rf != 0)
+    np.testing.assert_array_equal(ps[rf == 0], rs[rf == 0])
+    rl, ol, score, nxt = casegen.mapq_inputs(np.random.default_rng(21), 300_000)
+    pm, pf = port.calculate_mapq(rl, ol, score, nxt)
+    rm, rf = ref.calculate_mapq(rl, ol, score, nxt)
+    np.testing.assert_array_equal(pf, rf)
+    np.testing.assert_array_equal(pm[pf == 0], rm[pf == 0])
+    assert len(np.unique(rm)) > 25
