@@ -118,6 +118,19 @@ class OracleLib:
         fn(n, *[ptr(a) for a in arrs], len(names or []), noff.ctypes.data, nb.ctypes.data, off.ctypes.data, text.ctypes.data, need)
         return text[:need].tobytes(), off
 
+    def filter_tags(self, tags, additional):
+        """Reference build only: project_alignments.cc:774-800 on a record holding `tags` (16-bit values); returns (kept mask,
+        number of removals counted)."""
+        fn = self.lib.pv3o_filter_tags
+        fn.argtypes = [C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+        fn.restype = None
+        t = np.ascontiguousarray(tags, dtype=np.uint16)
+        a = np.ascontiguousarray(sorted(additional), dtype=np.uint16)
+        kept = np.zeros(t.size, np.uint8)
+        total = C.c_uint64(0)
+        fn(t.size, t.ctypes.data, a.size, a.ctypes.data if a.size else None, kept.ctypes.data, C.byref(total))
+        return kept.astype(bool), int(total.value)
+
     def rescore_alignments(self, scoring5, seq_off, seq, qual_off, qual, cig_off, cig, refn_off=None, refn=None):
         fn = self.lib.pv3o_rescore_alignments
         fn.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 10

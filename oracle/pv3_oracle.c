@@ -599,10 +599,11 @@ void pv3o_msa_row_extract(const char *text, uint64_t n, uint64_t *gap_words, cha
 }
 
 /* ---- OA entry / CIGAR text of a record (project-alignments/project_alignments.cc:803-845) -----------------------------
- * PARITY UNPINNED: the code restated here sits inside project_task::process of the CLI, which cannot be compiled in this
- * container (seqan3 SAM I/O + libdispatch + Boost); the port follows the source line by line (ostringstream << of an
- * std::string, std::uint64_t, char, std::uint32_t + cigar op char, int, std::int32_t). Returns the bytes written (or
- * needed when cap is too small: nothing is written past cap). ref_id == NULL ⇒ CIGAR text only. */
+ * PINNED: the code restated here sits inside project_task::process of the CLI, which cannot be built in this container,
+ * but `make ref` cuts those statements (project_alignments.cc:762-845) out of the file where it lies and compiles them as a
+ * function body (oracle/ref_driver_annotate.cc); tests/test_oracle.py compares this restatement with them. One difference
+ * of type: POS is the int32 of seqan3's reference_position() in the reference, a uint64 here (equal for every valid POS).
+ * Returns the bytes written (or needed when cap is too small: nothing is written past cap). ref_id == NULL ⇒ CIGAR text only. */
 #include <stdio.h>
 uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos, const uint16_t *flag, const uint8_t *mapq,
 	const int32_t *nm, const uint8_t *has_nm, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,

@@ -80,8 +80,8 @@ void pv3o_quality_lut(int32_t *lut84);
 
 /* index-msa, one MSA row: bit i = 1 iff text[i] == '-' (index_vector_builder.cc:28-50), every other byte is copied to the
  * unaligned sequence in order (:40-43). gap_words: (n + 63) / 64 words; ungapped: capacity n, may be NULL. */
-/* OA entry of every record (project_alignments.cc:803-845), or with ref_id == NULL the SAM text of every CIGAR. Port only
- * (PARITY UNPINNED, see pv3_oracle.c). Returns the bytes needed; text_off has n + 1 entries. */
+/* OA entry of every record (project_alignments.cc:803-845), or with ref_id == NULL the SAM text of every CIGAR (port only).
+ * Reference build: the reference's own statements, ref_driver_annotate.cc (also pv3o_filter_tags, :774-800). Returns the bytes needed; text_off has n + 1 entries. */
 uint64_t pv3o_format_oa(uint64_t n, const uint32_t *ref_id, const uint64_t *pos, const uint16_t *flag, const uint8_t *mapq,
 	const int32_t *nm, const uint8_t *has_nm, const uint64_t *cig_off, const uint32_t *cig_len, const uint32_t *cig,
 	uint32_t n_names, const uint64_t *name_off, const char *names, uint64_t *text_off, char *text, uint64_t cap);

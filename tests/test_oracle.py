@@ -2,9 +2,13 @@
 import numpy as np
 import pytest
 
+import os
+
 import casegen
 from panvc3_b200.batch import RecordBatch, bits_from_aligned_row, format_cigar, pack_bits, parse_cigar
 from parity import assert_same, load_golden_random
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _pair_index(lib, src, dst):
@@ -252,3 +256,61 @@ def test_rescore_and_mapq_port_match_the_reference_code(port, ref):
     np.testing.assert_array_equal(pf, rf)
     np.testing.assert_array_equal(pm[pf == 0], rm[pf == 0])
     assert len(np.unique(rm)) > 25
+
+
+def test_format_oa_port_matches_the_reference_statements(port, ref):
+    """PINS the N1 port: the OA entry built by the reference's own statements (project_alignments.cc:762-845 cut out at build
+    time and compiled as a function body, oracle/ref_driver_annotate.cc) for random records: every digit-count boundary of
+    POS (int32 in the reference), counts, MAPQ and NM, both strands, missing NM, empty and long CIGARs, names of all lengths."""
+    rng = np.random.default_rng(77)
+    n = 20000
+    names = [b"1", b"chr10_random_contig_with_a_long_name", b"", b"REF"]
+    n_ops = rng.integers(0, 12, n)
+    n_ops[rng.random(n) < 0.02] = 300
+    cig_off = np.zeros(n + 1, np.uint64); cig_off[1:] = np.cumsum(n_ops)
+    total = int(cig_off[-1])
+    cig = (rng.choice([1, 9, 10, 99, 100, 150, 12345, 999999, 1000000, (1 << 28) - 1], total).astype(np.uint32) << 4) \
+        | rng.integers(0, 9, total).astype(np.uint32)
+    a = dict(ref_id=rng.integers(0, len(names), n), pos=rng.choice([0, 9, 10, 99999, 100000, 2 ** 31 - 1], n),
+             flag=rng.integers(0, 4096, n), mapq=rng.integers(0, 256, n),
+             nm=rng.choice([0, 1, 9, 10, 150, -1, -2147483648, 2147483647], n), has_nm=(rng.random(n) < 0.8))
+    pt, po = port.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], a["nm"], a["has_nm"], cig_off, cig, names)
+    rt, ro = ref.format_oa(a["ref_id"], a["pos"], a["flag"], a["mapq"], a["nm"], a["has_nm"], cig_off, cig, names)
+    np.testing.assert_array_equal(po, ro)
+    assert pt == rt and len(rt) > 30 * n
+
+
+def test_tag_filter_header_matches_the_reference_statements(ref, tmp_path):
+    """include/panvc3_b200/record_annotator.hh:filter_tags against the reference's own removal loop and preserved table
+    (project_alignments.cc:53-87, 774-800): same survivors for every two-letter tag the SAM spec allows."""
+    import subprocess
+    tag = lambda s: ord(s[0]) * 256 + ord(s[1])
+    first = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz"
+    tags = [tag(a + b) for a in first for b in first + "0123456789"]
+    additional = [tag("XS"), tag("ZZ"), tag("NM"), tag("a1")]
+    kept, removed = ref.filter_tags(tags, additional)
+    assert removed == len(tags) - int(kept.sum())
+    src = tmp_path / "f.cc"
+    src.write_text("""
+#include <cstdio>
+#include <map>
+#include <vector>
+#include <panvc3_b200/record_annotator.hh>
+int main(int argc, char **argv) {
+	std::map <panvc3_b200::sam_tag_type, int> tags; unsigned v; std::vector <panvc3_b200::sam_tag_type> add;
+	for (int i = 1; i < argc; ++i) { sscanf(argv[i], "%u", &v); add.push_back(v); }
+	std::sort(add.begin(), add.end());
+	while (1 == scanf("%u", &v)) tags[v] = 1;
+	std::map <panvc3_b200::sam_tag_type, unsigned long> removed;
+	panvc3_b200::filter_tags(tags, add, removed);
+	for (auto const &kv : tags) printf("%u\\n", (unsigned) kv.first);
+	return 0;
+}
+""")
+    exe = tmp_path / "f"
+    # the header only needs the C declarations of panvc3_b200.h for oa_batch; nothing is linked for the filter
+    subprocess.run(["g++", "-std=c++17", "-O1", f"-I{ROOT}/include", "-o", str(exe), str(src), "-Wl,--unresolved-symbols=ignore-all"], check=True)
+    res = subprocess.run([str(exe), *[str(t) for t in additional]], input="\n".join(str(t) for t in tags), capture_output=True, text=True, check=True)
+    ours = sorted(int(x) for x in res.stdout.split())
+    assert ours == sorted(t for t, k in zip(tags, kept) if k)
+    assert len(ours) == 25 + 4                                   # the preserved table plus the four additional tags
