@@ -576,3 +576,27 @@ def test_calculate_mapq_matches_oracle(gpu, port):
     np.testing.assert_array_equal(f, ef)
     np.testing.assert_array_equal(m[ef == 0], em[ef == 0])
     assert len(np.unique(em)) > 25 and (ef != 0).any()
+
+
+def test_pinned_host_batch(gpu, port, workflow_msa):
+    """pv3_project with the caller's arrays in pinned memory (pv3_host_alloc), the way bench.py's e2e leg and a BAM reader
+    that decodes into the arena call it: same results as the oracle, quality-aware scoring included (the lazy QUAL gather
+    reads the pinned array), and as the pageable path."""
+    from panvc3_b200.capi import PinnedArena
+    from panvc3_b200.workload import sample_reads
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    b = sample_reads(workflow_msa, 300_000, 150, seed=71, ins=0.004, dele=0.004, clip_frac=0.1)
+    arena = PinnedArena(idx.ctx.lib, b.input_bytes() + 64 * 4096)
+    pb = RecordBatch.__new__(RecordBatch)
+    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
+        a = getattr(b, k)
+        if a is not None:
+            q = arena.take(a.shape, a.dtype); q[...] = a; a = q
+        setattr(pb, k, a)
+    for go, ge in ((0, -1), (-3, -2)):
+        exp = oi.project_batch(b, go, ge, n_threads=os.cpu_count() or 1)
+        assert int(exp.rr_len.sum()) > 1000
+        got_pinned = idx.project_batch(pb, go, ge)
+        assert_same(got_pinned, exp, b, f"pinned go={go}")
+        assert_same(idx.project_batch(b, go, ge), exp, b, f"pageable go={go}")
