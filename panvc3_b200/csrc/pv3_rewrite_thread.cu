@@ -31,14 +31,15 @@
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
 #include "pv3_runs.cuh"
+#include <cstdlib>
+#include <cstdio>
 
 namespace pv3 {
 
 constexpr int      TT        = 32;             // threads per CTA = records per tile (one warp: the tile barriers cost nothing)
 constexpr int      T_OUTQ    = 24;             // staged output ops per record
-constexpr int      T_RAWQ    = 32;             // raw runs per record (column runs + pass-through ops)
-constexpr int      T_PIECEQ  = 12;             // compare pieces per record
-constexpr uint32_t T_QSTAGE  = TT * 168;       // query bases staged per tile
+// per-variant quotas (Cfg below): raw runs per record (column runs + pass-through ops), compare pieces per record, query
+// bases staged per tile
 constexpr uint32_t T_RWIN    = 192;            // target bases staged per record (6 x 16 bytes of nibbles)
 constexpr uint32_t T_RCH     = T_RWIN / 32;    // 16-byte chunks per staged target window
 constexpr uint32_t T_MMW     = 6;              // mismatch bit words per record (query coordinates): reads up to 192 bases
@@ -46,12 +47,24 @@ constexpr uint32_t T_C1_ITERS = 192;           // bound of the column walk (long
 constexpr uint32_t RAW_PASS  = 0x8000u;        // raw entry refers to input op (entry & 0x7fff)
 constexpr uint32_t ERR_DEFER = 0x80000000u;
 
-// 10 KB per one-warp tile ⇒ 19-20 CTAs per SM. `fin` reuses the memory of `ref` (dead after phase C2; a barrier separates them).
-struct TileSmem {
-	uint16_t raw[T_RAWQ][TT];
-	uint32_t piece[T_PIECEQ][TT];              // qpos | (target offset from the staged window start) << 8 | len << 24
+// Two layouts, chosen at launch (PV3_K1T_STAGE_REF, default 0):
+//  STAGE = true  (v5-v8): the target windows are staged in shared memory; 10.3 KB per one-warp tile ⇒ 20 CTAs per SM. `fin`
+//                reuses the memory of `ref` (dead after phase C2; a barrier separates them).
+//  STAGE = false (v9): phase C2 reads the packed target codes through L1 (phase A prefetches the record's window), and
+//                `fin` reuses the staged query and the piece list (dead after C2): 7.0 KB per tile ⇒ 28 CTAs per SM. The
+//                kernel is latency-bound at 5 warps per scheduler (profiles/r1_v8_ncu_k1t_full_summary.txt), so resident
+//                warps are what buys time.
+template <int V> struct Cfg;
+template <> struct Cfg <0> { static constexpr bool STAGE = true;  static constexpr int RAWQ = 32, PIECEQ = 12; static constexpr uint32_t QSTAGE = TT * 168; };
+template <> struct Cfg <1> { static constexpr bool STAGE = false; static constexpr int RAWQ = 32, PIECEQ = 12; static constexpr uint32_t QSTAGE = TT * 168; };
+template <> struct Cfg <2> { static constexpr bool STAGE = false; static constexpr int RAWQ = 24, PIECEQ = 10; static constexpr uint32_t QSTAGE = TT * 156; };   // 6.1 KB ⇒ 32 CTAs per SM
+
+template <int V, bool STAGE = Cfg <V>::STAGE> struct TileSmemT;
+template <int V> struct TileSmemT <V, true> {
+	uint16_t raw[Cfg <V>::RAWQ][TT];
+	uint32_t piece[Cfg <V>::PIECEQ][TT];       // qpos | (target offset from the staged window start) << 8 | len << 24
 	uint32_t mm[T_MMW + 1][TT];
-	uint2    q4[T_QSTAGE / 16 + 2];            // packed query: 16 bases per element
+	uint2    q4[Cfg <V>::QSTAGE / 16 + 2];     // packed query: 16 bases per element
 	union {
 		uint4    ref[TT][T_RCH];               // [record][staged packed target codes]
 		uint32_t fin[T_OUTQ][TT];              // final ops
@@ -60,9 +73,24 @@ struct TileSmem {
 	uint32_t scan[TT / 32];
 	unsigned long long base;
 };
+template <int V> struct TileSmemT <V, false> {
+	uint16_t raw[Cfg <V>::RAWQ][TT];
+	uint32_t mm[T_MMW + 1][TT];
+	union {
+		struct {
+			uint2    q4[Cfg <V>::QSTAGE / 16 + 2];
+			uint32_t piece[Cfg <V>::PIECEQ][TT];
+		};
+		uint32_t fin[T_OUTQ][TT];
+	};
+	uint32_t scan[TT / 32];
+	unsigned long long base;
+};
 static_assert(sizeof(uint4) * T_RCH * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in ref");
+static_assert(sizeof(uint2) * (Cfg <2>::QSTAGE / 16 + 2) + sizeof(uint32_t) * Cfg <2>::PIECEQ * TT >= sizeof(uint32_t) * T_OUTQ * TT, "fin must fit in q4 + piece");
 
 __device__ __forceinline__ uint32_t ctz64(uint64_t x) { return (uint32_t) __ffsll((long long) x) - 1u; }   // x != 0
+__device__ __forceinline__ uint32_t ctz32(uint32_t x) { return (uint32_t) __popc(~x & (x - 1u)); }             // 32 for x == 0
 
 // 8 nibbles of t → 8 bits (bit i set ⇔ nibble i non-zero), returned in bits 24..31
 __device__ __forceinline__ uint32_t nonzero_nibbles_hi(uint32_t t)
@@ -79,6 +107,16 @@ __device__ __forceinline__ void load16n(const uint32_t *base, uint32_t a, uint32
 	const uint32_t *p = base + (a >> 3);
 	uint32_t const sh = (a & 7u) * 4u;
 	uint32_t const w0 = p[0], w1 = p[1], w2 = p[2];
+	lo = __funnelshift_r(w0, w1, sh);
+	hi = __funnelshift_r(w1, w2, sh);
+}
+
+// the same through the read-only path (word-aligned base in global memory)
+__device__ __forceinline__ void load16n_ldg(const uint32_t *base, uint32_t a, uint32_t &lo, uint32_t &hi)
+{
+	const uint32_t *p = base + (a >> 3);
+	uint32_t const sh = (a & 7u) * 4u;
+	uint32_t const w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
 	lo = __funnelshift_r(w0, w1, sh);
 	hi = __funnelshift_r(w1, w2, sh);
 }
@@ -115,11 +153,15 @@ __device__ __forceinline__ uint32_t bam4_word_to_ranks(uint32_t w)
 	return ((x >> 1) & 0x77777777u & m) | (0x33333333u & ~m);
 }
 
+template <int V>
 __global__ void __launch_bounds__(TT)
 k1_thread_kernel(K1Params P)
 {
+	constexpr bool STAGE = Cfg <V>::STAGE;
+	constexpr int T_RAWQ = Cfg <V>::RAWQ, T_PIECEQ = Cfg <V>::PIECEQ;
+	constexpr uint32_t T_QSTAGE = Cfg <V>::QSTAGE;
 	extern __shared__ __align__(16) uint8_t smem_raw[];
-	TileSmem &sm = *reinterpret_cast <TileSmem *>(smem_raw);
+	TileSmemT <V> &sm = *reinterpret_cast <TileSmemT <V> *>(smem_raw);
 	unsigned const tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 
@@ -157,7 +199,7 @@ k1_thread_kernel(K1Params P)
 		RefDesc R = {};
 		uint64_t c0 = 0, e0 = 0, spos = 0, qoff = 0, nq = 0, cbase = 0;
 		uint32_t nc = 0, first_op = 0;
-		sm.ref_ptr[tid] = nullptr;
+		if constexpr (STAGE) sm.ref_ptr[tid] = nullptr;
 		if (active) {
 			uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec), rf = __ldg(P.dst_ref + rec);
 			if (sr >= P.n_rows || dr >= P.n_rows || rf >= P.n_refs) flags = PV3_FLAG_BAD_ID;
@@ -176,14 +218,21 @@ k1_thread_kernel(K1Params P)
 				c0 = (spos < S.n_zeros) ? select0_thread(S, spos + 1) : S.n_bits;     // rewrite_cigar.hh:51
 				e0 = rank0_thread(D, c0);                                              // :52
 				if (S.n_bits != D.n_bits || e0 > R.n || nq > 32u * T_MMW || nc >= RAW_PASS) defer = true;   // unusual: the general kernel guards it
-				if (!defer) sm.ref_ptr[tid] = R.codes4 + ((e0 & ~31ull) >> 1);
+				if (!defer) {
+					const uint8_t *rp = R.codes4 + ((e0 & ~31ull) >> 1);
+					if constexpr (STAGE) sm.ref_ptr[tid] = rp;
+					else {                                                               // the window C2 will read: 96 bytes from a 16-byte boundary
+						asm volatile("prefetch.global.L1 [%0];" :: "l"(rp));
+						asm volatile("prefetch.global.L1 [%0];" :: "l"(rp + 95));
+					}
+				}
 			}
 		}
 		// a query rank above 7 anywhere in the tile: the nibble compare cannot represent it, the general kernel takes the tile
 		if (__syncthreads_or((int) bad_rank)) defer = true;
 
 		// ---- phase B2: per record a window of packed target codes (8 lanes per record, 16 bytes per lane) --------------
-		for (uint32_t r = warp * 32 + (lane >> 3); r < warp * 32 + 32; r += 4) {
+		if constexpr (STAGE) for (uint32_t r = warp * 32 + (lane >> 3); r < warp * 32 + 32; r += 4) {
 			const uint8_t *rp = sm.ref_ptr[r];
 			uint32_t const l8 = lane & 7u;
 			if (rp && l8 < T_RCH) sm.ref[r][l8] = __ldg(reinterpret_cast <const uint4 *>(rp) + l8);
@@ -221,54 +270,60 @@ k1_thread_kernel(K1Params P)
 			};
 			for (uint32_t it = 0; ; ++it) {
 				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
+				bool walk = true;
 				if (rem == 0) {                                                    // next input op
 					if (k == nc) break;
 					uint32_t const packed = k ? __ldg(P.cig + cbase + k) : first_op;
 					uint32_t const cnt = packed >> 4, op = packed & 0xfu;
-					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; continue; }       // rewrite_cigar.hh:149-151
-					if ((0x72u >> op) & 1u) {                                          // I S H P pass through (:68-77)
+					walk = false;
+					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; }                 // rewrite_cigar.hh:149-151
+					else if ((0x72u >> op) & 1u) {                                     // I S H P pass through (:68-77)
 						flush();
 						if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) (RAW_PASS | k);
 						++n_raw;
 						if (op == OP_I || op == OP_S) qpos = min(qpos + cnt, 0x10000u);
 						++k;
-						continue;
+					} else {
+						mlike = (op != OP_D && op != OP_N);
+						if (cnt > src_left) { err = PV3_FLAG_POS_OOB; k = nc; }
+						else { src_left -= cnt; rem = cnt; ++k; walk = cnt != 0; }
 					}
-					mlike = (op != OP_D && op != OP_N);
-					if (cnt > src_left) { err = PV3_FLAG_POS_OOB; k = nc; continue; }
-					src_left -= cnt;
-					rem = cnt; ++k;
-					if (!rem) continue;
 				}
-				uint32_t const wi = crel >> 6, b = crel & 63u;
-				if (wi != wcur) {                                                   // next word pair is already in flight
-					Sinv = ~Snext; Dinv = ~Dnext; wcur = wi;
-					Snext = __ldg(Sp + wi + 1); Dnext = __ldg(Dp + wi + 1);
-				}
-				uint64_t const s = Sinv >> b, d = Dinv >> b;
-				uint32_t const sb = (uint32_t) s & 1u, db = (uint32_t) d & 1u;
-				uint64_t const nr = (s ^ (0ull - (uint64_t) sb)) | (d ^ (0ull - (uint64_t) db));
-				uint32_t len = nr ? ctz64(nr) : 64u;
-				len = min(len, 64u - b);
-				if (sb) { len = min(len, rem); rem -= len; }
-				crel += len;
-				bool const isq = sb && mlike;                                       // the run consumes query bases
-				bool const cmp = isq && db;                                         // compare run (:102-113)
-				if (cmp) {
+				if (walk) {
+					uint32_t const wi = crel >> 6, b = crel & 63u;
+					if (wi != wcur) {                                               // next word pair is already in flight
+						Sinv = ~Snext; Dinv = ~Dnext; wcur = wi;
+						Snext = __ldg(Sp + wi + 1); Dnext = __ldg(Dp + wi + 1);
+					}
+					uint64_t const s = Sinv >> b, d = Dinv >> b;
+					uint32_t const sb = (uint32_t) s & 1u, db = (uint32_t) d & 1u;
+					// columns until either row changes: trailing zeros of (s ^ -sb) | (d ^ -db), in 32-bit halves and without a
+					// branch (ctz32(0) = 32, so an all-zero word gives 64)
+					uint32_t const ms = 0u - sb, md = 0u - db;
+					uint32_t const nlo = ((uint32_t) s ^ ms) | ((uint32_t) d ^ md), nhi = ((uint32_t) (s >> 32) ^ ms) | ((uint32_t) (d >> 32) ^ md);
+					uint32_t const zlo = ctz32(nlo);
+					uint32_t len = zlo + (zlo >> 5) * ctz32(nhi);                       // the high half counts only when the low half is empty
+					len = min(len, 64u - b);
+					if (sb) { len = min(len, rem); rem -= len; }
+					crel += len;
+					bool const isq = sb && mlike;                                   // the run consumes query bases
+					bool const cmp = isq && db;                                     // compare run (:102-113)
 					uint32_t e1 = 0;
-					if (qpos + len > nq32) e1 = PV3_FLAG_QUERY_OOB;
-					else if (ra + len > r_lim) e1 = (r_room > 0x10000ull) ? ERR_DEFER : PV3_FLAG_REF_OOB;
-					if (e1) { err = e1; k = nc; rem = 0; continue; }
-				}
-				uint32_t const op = db ? (isq ? OP_EQ : OP_D) : OP_I;             // :92-100, :127-137
-				if (db || isq) {
+					if (cmp) {
+						if (qpos + len > nq32) e1 = PV3_FLAG_QUERY_OOB;
+						else if (ra + len > r_lim) e1 = (r_room > 0x10000ull) ? ERR_DEFER : PV3_FLAG_REF_OOB;
+					}
+					if (e1) { err = e1; k = nc; rem = 0; }                         // ends the op list; nothing is emitted for this run
+					uint32_t const op = db ? (isq ? OP_EQ : OP_D) : OP_I;         // :92-100, :127-137
+					bool const emit = (db || isq) && !e1;
 					// a run that continues the pending one (across a word boundary or over columns that are gaps in both rows)
 					// extends it: fewer raw runs and compare pieces for the next two loops
-					if (op == pend_op && pend_len + len <= 250u) pend_len += len;
-					else { flush(); pend_op = op; pend_len = len; pend_q = qpos; pend_ra = ra; }
+					bool const ext = op == pend_op && pend_len + len <= 250u;
+					if (emit && !ext) { flush(); pend_op = op; pend_len = 0; pend_q = qpos; pend_ra = ra; }
+					if (emit) pend_len += len;
+					if (isq) qpos = min(qpos + len, 0x10000u);
+					if (db) ra = min(ra + len, 0x20000u);
 				}
-				if (isq) qpos = min(qpos + len, 0x10000u);
-				if (db) ra = min(ra + len, 0x20000u);
 			}
 			flush();
 			if (err == ERR_DEFER || n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
@@ -280,7 +335,9 @@ k1_thread_kernel(K1Params P)
 		bool const work2 = work && !flags && !defer;
 		if (work2) {
 			const uint32_t *qs = reinterpret_cast <const uint32_t *>(sm.q4);
-			const uint32_t *rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
+			const uint32_t *rs;                 // the record's target window: staged, or the packed codes themselves (16-byte aligned, 512 readable pad bytes)
+			if constexpr (STAGE) rs = reinterpret_cast <const uint32_t *>(sm.ref[tid]);
+			else rs = reinterpret_cast <const uint32_t *>(R.codes4 + (e0a >> 1));
 			uint32_t const qrel = (q_lead + (uint32_t) (qoff - tq0)) << (packed ? 1 : 0);
 			#pragma unroll
 			for (uint32_t w = 0; w <= T_MMW; ++w) sm.mm[w][tid] = 0;
@@ -294,7 +351,8 @@ k1_thread_kernel(K1Params P)
 				uint32_t const n = min(remaining, 16u);
 				uint32_t qlo, qhi, rlo, rhi;
 				load16n(qs, qrel + qpos, qlo, qhi);
-				if (ra + 24u <= T_RWIN) load16n(rs, ra, rlo, rhi);
+				if (!STAGE) load16n_ldg(rs, ra, rlo, rhi);
+				else if (ra + 24u <= T_RWIN) load16n(rs, ra, rlo, rhi);
 				else { uint2 const g = load16n_global(R.codes4, e0a + ra); rlo = g.x; rhi = g.y; }   // beyond the staged window
 				uint32_t bits = (nonzero_nibbles_hi(qlo ^ rlo) >> 24) | ((nonzero_nibbles_hi(qhi ^ rhi) >> 16) & 0xff00u);
 				bits &= (1u << n) - 1u;
@@ -336,7 +394,8 @@ k1_thread_kernel(K1Params P)
 					uint32_t const lo = __funnelshift_r(m0, m1, b), hi = __funnelshift_r(m1, m2, b);
 					uint32_t const first = lo & 1u;
 					uint32_t const xlo = lo ^ (0u - first), xhi = hi ^ (0u - first);
-					uint32_t l = xlo ? (uint32_t) (__ffs((int) xlo) - 1) : (xhi ? 32u + (uint32_t) (__ffs((int) xhi) - 1) : 64u);
+					uint32_t const zlo = ctz32(xlo);
+					uint32_t l = zlo + (zlo >> 5) * ctz32(xhi);                         // 64 when neither half changes
 					l = min(l, left);
 					op = first ? OP_X : OP_EQ; len = l;
 					left -= l; qpos += l;
@@ -445,18 +504,33 @@ k1_thread_kernel(K1Params P)
 	}
 }
 
-void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
+template <int V>
+static void launch_variant(const K1Params &P, int n_sms, cudaStream_t stream)
 {
 	static int per_sm = 0;
+	size_t const bytes = sizeof(TileSmemT <V>);
 	if (!per_sm) {
-		cudaFuncSetAttribute(k1_thread_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(TileSmem));
-		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_thread_kernel, TT, sizeof(TileSmem)) != cudaSuccess || per_sm < 1) per_sm = 1;
+		cudaFuncSetAttribute(k1_thread_kernel <V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bytes);
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_thread_kernel <V>, TT, bytes) != cudaSuccess || per_sm < 1) per_sm = 1;
+		if (getenv("PV3_TRACE")) fprintf(stderr, "[pv3 trace] k1_thread_kernel variant %d: %zu bytes of shared memory per tile, %d CTAs per SM\n", V, bytes, per_sm);
 	}
 	uint64_t const n_tiles = (P.n + TT - 1) / TT;
 	if (!n_tiles) return;
 	uint64_t blocks = (uint64_t) n_sms * per_sm;  // persistent: every resident CTA strides over the tiles (shared memory bounds the count)
 	if (blocks > n_tiles) blocks = n_tiles;
-	k1_thread_kernel<<<(unsigned) blocks, TT, sizeof(TileSmem), stream>>>(P);
+	k1_thread_kernel <V><<<(unsigned) blocks, TT, bytes, stream>>>(P);
+}
+
+// PV3_K1T_VARIANT: 0 = target windows staged in shared memory (v5-v8, 20 CTAs per SM), 1 = target codes read through L1 (28),
+// 2 = the same with smaller per-record quotas (32, the default). Measured on B200, 1 M configs[1] records in random order:
+// 0.344 / 0.296 / 0.289 ms, and the same 12 records deferred to the warp kernel in all three.
+void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
+{
+	static int variant = -1;
+	if (variant < 0) { const char *e = getenv("PV3_K1T_VARIANT"); variant = (e && *e >= '0' && *e <= '2') ? (*e - '0') : 2; }
+	if (variant == 0) launch_variant <0>(P, n_sms, stream);
+	else if (variant == 1) launch_variant <1>(P, n_sms, stream);
+	else launch_variant <2>(P, n_sms, stream);
 }
 
 } // namespace pv3
