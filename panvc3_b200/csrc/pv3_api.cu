@@ -73,6 +73,7 @@ struct pv3_ctx {
 	DevBuf       index_mem;              // words, directories, contigs — one allocation
 	DevBuf       row_desc, ref_desc;
 	uint64_t     index_bytes = 0;
+	uint64_t     target_code_bytes = 0;   // packed target codes of all references (chooses the thread kernel's layout)
 
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
@@ -297,6 +298,8 @@ int pv3_index_commit(pv3_ctx *ctx)
 	PV3_CUDA(ctx, ctx->index_mem.ensure(total));
 	PV3_CUDA(ctx, cudaMemcpy(ctx->index_mem.p, host.data(), total, cudaMemcpyHostToDevice));
 	ctx->index_bytes = total;
+	ctx->target_code_bytes = 0;
+	for (auto const &rf : ctx->refs) ctx->target_code_bytes += (rf.bases.size() + 1) / 2;
 
 	std::vector <RowDesc> rd(ctx->rows.size() ? ctx->rows.size() : 1);
 	for (size_t r = 0; r < ctx->rows.size(); ++r) {
@@ -447,7 +450,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 	int st = PV3_OK;
 	if (ctx->kernel_path == 0) {
 		// short records: one thread each; whatever exceeds its fixed quotas comes back in the deferred list
-		launch_k1_thread(P, ctx->n_sms, stream);
+		launch_k1_thread(P, ctx->n_sms, ctx->target_code_bytes, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], stream));
 		ctx->timing.launches += 1;

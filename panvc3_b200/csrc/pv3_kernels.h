@@ -99,7 +99,7 @@ struct K4Params {
 };
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
-void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream);   // thread per record (short records)
+void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record (short records)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
 void launch_k3_thread(const K3Params &P, cudaStream_t stream);               // thread per run (small runs)
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);

@@ -58,6 +58,8 @@ template <int V> struct Cfg;
 template <> struct Cfg <0> { static constexpr bool STAGE = true;  static constexpr int RAWQ = 32, PIECEQ = 12; static constexpr uint32_t QSTAGE = TT * 168; };
 template <> struct Cfg <1> { static constexpr bool STAGE = false; static constexpr int RAWQ = 32, PIECEQ = 12; static constexpr uint32_t QSTAGE = TT * 168; };
 template <> struct Cfg <2> { static constexpr bool STAGE = false; static constexpr int RAWQ = 24, PIECEQ = 10; static constexpr uint32_t QSTAGE = TT * 156; };   // 6.1 KB ⇒ 32 CTAs per SM
+template <> struct Cfg <3> { static constexpr bool STAGE = true;  static constexpr int RAWQ = 24, PIECEQ = 10; static constexpr uint32_t QSTAGE = TT * 156; };   // 9.3 KB ⇒ 22 CTAs per SM
+template <> struct Cfg <4> { static constexpr bool STAGE = false; static constexpr int RAWQ = 24, PIECEQ = 10; static constexpr uint32_t QSTAGE = TT * 156; };   // as 2, no L1 prefetch
 
 template <int V, bool STAGE = Cfg <V>::STAGE> struct TileSmemT;
 template <int V> struct TileSmemT <V, true> {
@@ -221,7 +223,7 @@ k1_thread_kernel(K1Params P)
 				if (!defer) {
 					const uint8_t *rp = R.codes4 + ((e0 & ~31ull) >> 1);
 					if constexpr (STAGE) sm.ref_ptr[tid] = rp;
-					else {                                                               // the window C2 will read: 96 bytes from a 16-byte boundary
+					else if (V != 4) {                                                   // the window C2 will read: 96 bytes from a 16-byte boundary
 						asm volatile("prefetch.global.L1 [%0];" :: "l"(rp));
 						asm volatile("prefetch.global.L1 [%0];" :: "l"(rp + 95));
 					}
@@ -256,17 +258,12 @@ k1_thread_kernel(K1Params P)
 			uint64_t Sinv = 0, Dinv = 0;
 			uint64_t Snext = __ldg(Sp), Dnext = __ldg(Dp);                      // the walk starts in word 0 of the window; one word ahead
 			bool mlike = false;
-			uint32_t pend_op = OP_NONE, pend_len = 0, pend_q = 0, pend_ra = 0;   // the open run (not yet in the lists)
-			auto flush = [&]() {
-				if (pend_op != OP_NONE) {
-					if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) ((pend_len << 4) | pend_op);
-					++n_raw;
-					if (pend_op == OP_EQ) {
-						if (n_piece < (uint32_t) T_PIECEQ) sm.piece[n_piece][tid] = pend_q | (pend_ra << 8) | (pend_len << 24);
-						++n_piece;
-					}
-					pend_op = OP_NONE;
-				}
+			// The open run lives in registers AND in the first free slot of the lists (rewritten whenever it grows), so that
+			// closing it is a counter increment: no flush branch that a few lanes take in every iteration.
+			uint32_t pend_op = OP_NONE, pend_len = 0, pend_q = 0, pend_ra = 0;
+			auto close_run = [&]() {
+				n_raw += (pend_op != OP_NONE) ? 1u : 0u;
+				n_piece += (pend_op == OP_EQ) ? 1u : 0u;
 			};
 			for (uint32_t it = 0; ; ++it) {
 				if (it >= T_C1_ITERS) { err = ERR_DEFER; break; }
@@ -278,8 +275,8 @@ k1_thread_kernel(K1Params P)
 					walk = false;
 					if (op > OP_X) { err = PV3_FLAG_BAD_OP; k = nc; }                 // rewrite_cigar.hh:149-151
 					else if ((0x72u >> op) & 1u) {                                     // I S H P pass through (:68-77)
-						flush();
-						if (n_raw < (uint32_t) T_RAWQ) sm.raw[n_raw][tid] = (uint16_t) (RAW_PASS | k);
+						close_run(); pend_op = OP_NONE;
+						sm.raw[min(n_raw, (uint32_t) T_RAWQ - 1u)][tid] = (uint16_t) (RAW_PASS | k);   // a clamped slot is only hit when the list overflows (⇒ deferred)
 						++n_raw;
 						if (op == OP_I || op == OP_S) qpos = min(qpos + cnt, 0x10000u);
 						++k;
@@ -301,8 +298,7 @@ k1_thread_kernel(K1Params P)
 					// branch (ctz32(0) = 32, so an all-zero word gives 64)
 					uint32_t const ms = 0u - sb, md = 0u - db;
 					uint32_t const nlo = ((uint32_t) s ^ ms) | ((uint32_t) d ^ md), nhi = ((uint32_t) (s >> 32) ^ ms) | ((uint32_t) (d >> 32) ^ md);
-					uint32_t const zlo = ctz32(nlo);
-					uint32_t len = zlo + (zlo >> 5) * ctz32(nhi);                       // the high half counts only when the low half is empty
+					uint32_t len = ctz32(nlo ? nlo : nhi) + (nlo ? 0u : 32u);         // one population count: the half that holds the change
 					len = min(len, 64u - b);
 					if (sb) { len = min(len, rem); rem -= len; }
 					crel += len;
@@ -319,13 +315,18 @@ k1_thread_kernel(K1Params P)
 					// a run that continues the pending one (across a word boundary or over columns that are gaps in both rows)
 					// extends it: fewer raw runs and compare pieces for the next two loops
 					bool const ext = op == pend_op && pend_len + len <= 250u;
-					if (emit && !ext) { flush(); pend_op = op; pend_len = 0; pend_q = qpos; pend_ra = ra; }
-					if (emit) pend_len += len;
+					bool const fresh = emit && !ext;
+					if (fresh) close_run();
+					pend_op = fresh ? op : pend_op; pend_q = fresh ? qpos : pend_q; pend_ra = fresh ? ra : pend_ra;
+					pend_len = (fresh ? 0u : pend_len) + (emit ? len : 0u);
+					// (a clamped slot is only written while a run is open, and closing that run overflows the list ⇒ deferred)
+					if (pend_op != OP_NONE) sm.raw[min(n_raw, (uint32_t) T_RAWQ - 1u)][tid] = (uint16_t) ((pend_len << 4) | pend_op);
+					if (pend_op == OP_EQ) sm.piece[min(n_piece, (uint32_t) T_PIECEQ - 1u)][tid] = pend_q | (pend_ra << 8) | (pend_len << 24);
 					if (isq) qpos = min(qpos + len, 0x10000u);
 					if (db) ra = min(ra + len, 0x20000u);
 				}
 			}
-			flush();
+			close_run();
 			if (err == ERR_DEFER || n_raw > (uint32_t) T_RAWQ || n_piece > (uint32_t) T_PIECEQ) defer = true;
 			else flags |= err;
 		}
@@ -341,26 +342,54 @@ k1_thread_kernel(K1Params P)
 			uint32_t const qrel = (q_lead + (uint32_t) (qoff - tq0)) << (packed ? 1 : 0);
 			#pragma unroll
 			for (uint32_t w = 0; w <= T_MMW; ++w) sm.mm[w][tid] = 0;
-			uint32_t j = 0, remaining = 0, qpos = 0, ra = 0;
-			for (;;) {
-				if (!remaining) {
-					if (j == n_piece) break;
-					uint32_t const v = sm.piece[j][tid]; ++j;
-					qpos = v & 0xffu; ra = (v >> 8) & 0xffffu; remaining = v >> 24;
+			if constexpr (STAGE) {
+				uint32_t j = 0, remaining = 0, qpos = 0, ra = 0;
+				for (;;) {
+					if (!remaining) {
+						if (j == n_piece) break;
+						uint32_t const v = sm.piece[j][tid]; ++j;
+						qpos = v & 0xffu; ra = (v >> 8) & 0xffffu; remaining = v >> 24;
+					}
+					uint32_t const n = min(remaining, 16u);
+					uint32_t qlo, qhi, rlo, rhi;
+					load16n(qs, qrel + qpos, qlo, qhi);
+					if (ra + 24u <= T_RWIN) load16n(rs, ra, rlo, rhi);
+					else { uint2 const g = load16n_global(R.codes4, e0a + ra); rlo = g.x; rhi = g.y; }   // beyond the staged window
+					uint32_t bits = (nonzero_nibbles_hi(qlo ^ rlo) >> 24) | ((nonzero_nibbles_hi(qhi ^ rhi) >> 16) & 0xff00u);
+					bits &= (1u << n) - 1u;
+					uint32_t const w = qpos >> 5, b = qpos & 31u;
+					uint64_t const placed = (uint64_t) bits << b;
+					sm.mm[w][tid] |= (uint32_t) placed;
+					sm.mm[w + 1][tid] |= (uint32_t) (placed >> 32);
+					qpos += n; ra += n; remaining -= n;
 				}
-				uint32_t const n = min(remaining, 16u);
-				uint32_t qlo, qhi, rlo, rhi;
-				load16n(qs, qrel + qpos, qlo, qhi);
-				if (!STAGE) load16n_ldg(rs, ra, rlo, rhi);
-				else if (ra + 24u <= T_RWIN) load16n(rs, ra, rlo, rhi);
-				else { uint2 const g = load16n_global(R.codes4, e0a + ra); rlo = g.x; rhi = g.y; }   // beyond the staged window
-				uint32_t bits = (nonzero_nibbles_hi(qlo ^ rlo) >> 24) | ((nonzero_nibbles_hi(qhi ^ rhi) >> 16) & 0xff00u);
-				bits &= (1u << n) - 1u;
-				uint32_t const w = qpos >> 5, b = qpos & 31u;
-				uint64_t const placed = (uint64_t) bits << b;
-				sm.mm[w][tid] |= (uint32_t) placed;
-				sm.mm[w + 1][tid] |= (uint32_t) (placed >> 32);
-				qpos += n; ra += n; remaining -= n;
+			} else {
+				// The target words come from global memory (L1 when the target is small, L2 or HBM at chromosome scale), so
+				// the loop is rotated: the three words of step i+1 are requested before step i is compared.
+				uint32_t j = 0, rem_n = 0, qpos_n = 0, ra_n = 0, w0 = 0, w1 = 0, w2 = 0;
+				bool have = false;
+				auto request = [&]() {                                              // next step: position and loads
+					if (!rem_n) {
+						have = j != n_piece;
+						if (have) { uint32_t const v = sm.piece[j][tid]; ++j; qpos_n = v & 0xffu; ra_n = (v >> 8) & 0xffffu; rem_n = v >> 24; }
+					}
+					if (have) { const uint32_t *p = rs + (ra_n >> 3); w0 = __ldg(p); w1 = __ldg(p + 1); w2 = __ldg(p + 2); }
+				};
+				request();
+				while (have) {
+					uint32_t const n = min(rem_n, 16u), qpos = qpos_n, sh = (ra_n & 7u) * 4u;
+					uint32_t const rlo = __funnelshift_r(w0, w1, sh), rhi = __funnelshift_r(w1, w2, sh);
+					qpos_n += n; ra_n += n; rem_n -= n;
+					request();
+					uint32_t qlo, qhi;
+					load16n(qs, qrel + qpos, qlo, qhi);
+					uint32_t bits = (nonzero_nibbles_hi(qlo ^ rlo) >> 24) | ((nonzero_nibbles_hi(qhi ^ rhi) >> 16) & 0xff00u);
+					bits &= (1u << n) - 1u;
+					uint32_t const w = qpos >> 5, b = qpos & 31u;
+					uint64_t const placed = (uint64_t) bits << b;
+					sm.mm[w][tid] |= (uint32_t) placed;
+					sm.mm[w + 1][tid] |= (uint32_t) (placed >> 32);
+				}
 			}
 		}
 
@@ -394,28 +423,21 @@ k1_thread_kernel(K1Params P)
 					uint32_t const lo = __funnelshift_r(m0, m1, b), hi = __funnelshift_r(m1, m2, b);
 					uint32_t const first = lo & 1u;
 					uint32_t const xlo = lo ^ (0u - first), xhi = hi ^ (0u - first);
-					uint32_t const zlo = ctz32(xlo);
-					uint32_t l = zlo + (zlo >> 5) * ctz32(xhi);                         // 64 when neither half changes
+					uint32_t l = ctz32(xlo ? xlo : xhi) + (xlo ? 0u : 32u);             // 64 when neither half changes
 					l = min(l, left);
 					op = first ? OP_X : OP_EQ; len = l;
 					left -= l; qpos += l;
 				}
-				if (len) {
-					if (carry_op == op) carry_cnt += len;
-					else {
-						if ((carry_op | op) == 3u) adjacent_id = true;                 // I next to D (N is never produced)
-						if (carry_op != OP_NONE) {
-							if (n_ops < (uint32_t) T_OUTQ) sm.fin[n_ops][tid] = (carry_cnt << 4) | carry_op;
-							++n_ops;
-						}
-						carry_op = op; carry_cnt = len;
-					}
-				}
+				// cigar_buffer::push_back without a branch: the open op is kept in its slot (rewritten as it grows); a different
+				// op closes it by advancing the count
+				bool const fresh = len != 0 && carry_op != op;
+				adjacent_id |= fresh && (carry_op | op) == 3u;                         // I next to D (N is never produced)
+				n_ops += (fresh && carry_op != OP_NONE) ? 1u : 0u;
+				carry_cnt = (fresh ? 0u : carry_cnt) + len;
+				carry_op = fresh ? op : carry_op;
+				sm.fin[min(n_ops, (uint32_t) T_OUTQ - 1u)][tid] = (carry_cnt << 4) | carry_op;   // clamped only when the list overflows (⇒ deferred)
 			}
-			if (carry_op != OP_NONE) {                                              // cigar_buffer::finish (cigar.cc:89-95)
-				if (n_ops < (uint32_t) T_OUTQ) sm.fin[n_ops][tid] = (carry_cnt << 4) | carry_op;
-				++n_ops;
-			}
+			n_ops += (carry_op != OP_NONE) ? 1u : 0u;                                // cigar_buffer::finish (cigar.cc:89-95)
 			if (n_ops > (uint32_t) T_OUTQ) defer = true;
 			if (!defer && P.stage == 0) {
 				if (n_ops == 0) flags |= PV3_FLAG_EMPTY_CIGAR;                                   // cigar.cc:16-18 UB
@@ -521,16 +543,29 @@ static void launch_variant(const K1Params &P, int n_sms, cudaStream_t stream)
 	k1_thread_kernel <V><<<(unsigned) blocks, TT, bytes, stream>>>(P);
 }
 
-// PV3_K1T_VARIANT: 0 = target windows staged in shared memory (v5-v8, 20 CTAs per SM), 1 = target codes read through L1 (28),
-// 2 = the same with smaller per-record quotas (32, the default). Measured on B200, 1 M configs[1] records in random order:
-// 0.344 / 0.296 / 0.289 ms, and the same 12 records deferred to the warp kernel in all three.
-void launch_k1_thread(const K1Params &P, int n_sms, cudaStream_t stream)
+// Layout choice. Reading the target codes through L1 (no staging, 32 CTAs per SM) wins while the packed target stays close
+// to the SMs (L1 / the near part of L2); with a large target every tile's windows come from L2 / HBM and the staged layout
+// wins, because its coalesced 16-byte loads are issued before the column walk and used after it. Measured on B200, 1 M
+// 150-bp records in random order, staged (variant 0) against through-L1 (variant 4), ms per launch (profiles/r1_v12_*):
+//   configs[1] (25 KB of codes) 0.335 / 0.277    10^5 columns (0.2 MB) 0.274 / 0.246    10^6 (2 MB) 0.292 / 0.302
+//   10^7 (20 MB) 0.298 / 0.313                   10^8 (200 MB) 0.409 / 0.477 (0.504 without the L1 prefetch)
+// PV3_K1T_VARIANT overrides: 0 = staged windows (v5-v8 layout, 20 CTAs per SM), 1 = through L1 with the old quotas (28),
+// 2 = through L1 with smaller quotas (32) and an L1 prefetch of the window, 3 = staged with the smaller quotas (21),
+// 4 = as 2 without the prefetch.
+constexpr uint64_t L1_RESIDENT_TARGET_BYTES = 512 * 1024;   // between the 0.2 MB and 2 MB measurements
+
+void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream)
 {
-	static int variant = -1;
-	if (variant < 0) { const char *e = getenv("PV3_K1T_VARIANT"); variant = (e && *e >= '0' && *e <= '2') ? (*e - '0') : 2; }
-	if (variant == 0) launch_variant <0>(P, n_sms, stream);
-	else if (variant == 1) launch_variant <1>(P, n_sms, stream);
-	else launch_variant <2>(P, n_sms, stream);
+	const char *e = getenv("PV3_K1T_VARIANT");                          // read per launch: the parity tests switch layouts in-process
+	int const forced = (e && *e >= '0' && *e <= '4') ? (*e - '0') : -1;
+	int const variant = forced >= 0 ? forced : (target_code_bytes <= L1_RESIDENT_TARGET_BYTES ? 4 : 0);
+	switch (variant) {
+		case 0: launch_variant <0>(P, n_sms, stream); break;
+		case 1: launch_variant <1>(P, n_sms, stream); break;
+		case 2: launch_variant <2>(P, n_sms, stream); break;
+		case 3: launch_variant <3>(P, n_sms, stream); break;
+		default: launch_variant <4>(P, n_sms, stream); break;
+	}
 }
 
 } // namespace pv3

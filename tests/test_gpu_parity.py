@@ -297,6 +297,35 @@ def test_realistic_reads_both_paths_and_mixed_lengths(gpu, port, workflow_msa):
             assert_same(idx.project_batch(b, go, ge), exp, b, f"mixed go={go} path={path}")
 
 
+@pytest.mark.parametrize("layout", ["0", "1", "2", "3", "4"])
+def test_thread_kernel_layouts(gpu, port, workflow_msa, monkeypatch, layout):
+    """Every shared-memory layout of the thread-per-record kernel (PV3_K1T_VARIANT: staged target windows or target codes
+    through L1, both quota sets, with and without the L1 prefetch) on the bench distribution, on crafted random batches
+    with tiny indexes and on an index whose target is far beyond L1 — the default picks one of them by target size."""
+    from panvc3_b200.workload import sample_reads, synth_msa
+    monkeypatch.setenv("PV3_K1T_VARIANT", layout)
+    b = sample_reads(workflow_msa, 30000, 150, seed=41, ins=0.003, dele=0.003, clip_frac=0.1)
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    for go, ge in [(0, -1), (-2, -1)]:
+        exp = oi.project_batch(b, go, ge, n_threads=os.cpu_count() or 1)
+        assert_same(idx.project_batch(b, go, ge), exp, b, f"layout={layout} go={go}")
+    packed = b.to_bam4()
+    assert_same(idx.project_batch(packed, 0, -1), oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1), b, f"layout={layout} bam4")
+    for seed in (3, 4):
+        msa, rb = casegen.random_batch(4100 + seed, 1500, n_cols=[300, 6000][seed % 2], max_len=40)
+        ri = device_index(msa)
+        ro = port.make_index(*casegen.index_inputs(msa))
+        for stage in (1, 0):
+            ri.ctx.set_stage(stage)
+            assert_same(ri.project_batch(rb, 0, -1), ro.project_batch(rb, 0, -1, stage=stage), rb, f"layout={layout} random seed={seed} stage={stage}")
+    big = synth_msa(2_000_000, 3, seed=77, p_gap=0.004, mean_gap=8, snp=0.002)
+    bi = device_index(big)
+    bo = port.make_index(*casegen.index_inputs(big))
+    bb = sample_reads(big, 20000, 150, seed=12, ins=0.002, dele=0.002)
+    assert_same(bi.project_batch(bb, 0, -1), bo.project_batch(bb, 0, -1, n_threads=os.cpu_count() or 1), bb, f"layout={layout} 2M columns")
+
+
 def test_indel_heavy_batch_thread_dp_kernel(gpu, port):
     """configs[3]-style stress (scaled): most records realign, tens of thousands of small runs — the thread-per-run DP kernel,
     the compact list of larger runs for the warp kernel and the warp-aggregated splice, in all three DP modes."""
