@@ -153,8 +153,9 @@ int pv3_set_stage(pv3_ctx *, int stage);
  * (default 16384), otherwise one warp per run like the large windows; 0 sends every small run to the thread-per-run kernel.
  * Results are identical. */
 int pv3_set_dp_thread_min(pv3_ctx *, uint64_t n);
-/* Parity probe: 0 (default) = thread-per-record rewrite kernel, records beyond its quotas go to the warp-per-record
- * kernel; 1 = warp-per-record kernel for every record. Results are identical. */
+/* Parity probe: 0 (default) = thread-per-record rewrite kernel (run walk), records beyond its quotas go to the
+ * warp-per-record kernel; 1 = warp-per-record kernel for every record; 2 = thread-per-record word-parallel kernel, records
+ * beyond its quotas go to the warp-per-record kernel. Results are identical. */
 int pv3_set_kernel_path(pv3_ctx *, int path);
 
 int pv3_get_timing(const pv3_ctx *, pv3_timing *out);

@@ -82,10 +82,11 @@ struct pv3_ctx {
 	uint64_t     chunk_edge = 125000;        // records of the first and the last chunk: a short pipeline fill and drain (PV3_CHUNK_EDGE; 0 = equal chunks)
 	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all
 	bool         many_deferred = false;      // last batch: more than 1/16 of the records went to the warp-per-record kernel
-	int          kernel_path = 0;            // 0: thread-per-record kernel + warp-per-record for deferred records; 1: warp-per-record only
+	int          kernel_path = 0;            // 0: thread-per-record run-walk kernel + warp-per-record for deferred records; 1: warp-per-record only;
+	                                         // 2: thread-per-record word-parallel kernel + warp-per-record for deferred records
 
 	// device work buffers
-	DevBuf       counters, jobs, dp_arena, pool, deferred, big_list, d_packed, d_job_qual_off;
+	DevBuf       counters, jobs, dp_arena, pool, deferred, complex_list, complex_ce, big_list, d_packed, d_job_qual_off;
 	DevBuf       ex_text, ex_words, ex_seq, ex_status;   // pv3_msa_row_extract
 	DevBuf       an[16];                                 // pv3_format_oa / pv3_format_cigars
 	Job         *h_jobs = nullptr; uint64_t *h_job_qual_off = nullptr; uint64_t h_jobs_cap = 0;   // pinned (lazy QUAL)
@@ -169,7 +170,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->big_list, &ctx->d_packed, &ctx->d_job_qual_off,
+	for (DevBuf *b : { &ctx->index_mem, &ctx->row_desc, &ctx->ref_desc, &ctx->counters, &ctx->jobs, &ctx->dp_arena, &ctx->pool, &ctx->deferred, &ctx->complex_list, &ctx->complex_ce, &ctx->big_list, &ctx->d_packed, &ctx->d_job_qual_off,
 			&ctx->ex_text, &ctx->ex_words, &ctx->ex_seq, &ctx->ex_status,
 			&ctx->in_src_row, &ctx->in_dst_row, &ctx->in_dst_ref, &ctx->in_src_pos, &ctx->in_seq_off, &ctx->in_seq, &ctx->in_qual_off,
 			&ctx->in_qual, &ctx->in_cig_off, &ctx->in_cig, &ctx->out_dst_pos, &ctx->out_flags, &ctx->out_cig_off, &ctx->out_cig_len,
@@ -349,7 +350,7 @@ int pv3_get_quality_lut(const pv3_ctx *ctx, int32_t *lut84)
 
 int pv3_set_kernel_path(pv3_ctx *ctx, int path)
 {
-	if (!ctx || path < 0 || path > 1) return PV3_ERR_INVALID;
+	if (!ctx || path < 0 || path > 2) return PV3_ERR_INVALID;
 	ctx->kernel_path = path;
 	return PV3_OK;
 }
@@ -442,15 +443,26 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 	if (!in->n) return PV3_OK;
 	PV3_CUDA(ctx, ctx->jobs.ensure((out->rr_cap ? out->rr_cap : 1) * sizeof(Job)));
 	PV3_CUDA(ctx, ctx->deferred.ensure(in->n * 8));
+	PV3_CUDA(ctx, ctx->complex_list.ensure(in->n * 8));
+	PV3_CUDA(ctx, ctx->complex_ce.ensure(in->n * 16));
 	K1Params P = make_k1(ctx, in, out);
 	P.deferred = ctx->deferred.as <uint64_t>();
+	P.complex_list = ctx->complex_list.as <uint64_t>();
+	P.complex_ce = ctx->complex_ce.as <uint64_t>();
 	P.arena_off = opt.arena_off; P.rr_base = opt.rr_base;
 	PV3_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), stream));
 	PV3_CUDA(ctx, cudaEventRecord(ctx->ev[0], stream));
 	int st = PV3_OK;
-	if (ctx->kernel_path == 0) {
+	if (ctx->kernel_path != 1) {
 		// short records: one thread each; whatever exceeds its fixed quotas comes back in the deferred list
-		launch_k1_thread(P, ctx->n_sms, ctx->target_code_bytes, stream);
+		{
+			// path 0: the run-walk kernel (v13); path 2: the word-parallel kernel (v14). PV3_K1_KERNEL=word|thread overrides path 0
+			// (A/B runs of bench.py); both are parity-tested.
+			const char *e = getenv("PV3_K1_KERNEL");
+			bool const word = ctx->kernel_path == 2 || (ctx->kernel_path == 0 && e && e[0] == 'w');
+			if (word) launch_k1_word(P, ctx->n_sms, stream);
+			else launch_k1_thread(P, ctx->n_sms, ctx->target_code_bytes, stream);
+		}
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ctx->ev[4], stream));
 		ctx->timing.launches += 1;
@@ -594,7 +606,7 @@ int run_pipeline(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out, PipeO
 	out->n_realigned = c.n_realigned;
 	out->dp_cells = c.dp_cells;
 	cudaEventElapsedTime(&ctx->timing.ms_rewrite, ctx->ev[0], ctx->ev[1]);
-	if (ctx->kernel_path == 0) cudaEventElapsedTime(&ctx->timing.ms_rewrite_main, ctx->ev[0], ctx->ev[4]);
+	if (ctx->kernel_path != 1) cudaEventElapsedTime(&ctx->timing.ms_rewrite_main, ctx->ev[0], ctx->ev[4]);
 	else ctx->timing.ms_rewrite_main = ctx->timing.ms_rewrite;
 	ctx->timing.n_deferred = c.n_deferred;
 	if (ran_dp) {

@@ -69,6 +69,7 @@ struct Counters {
 	unsigned int       pad;
 	unsigned long long n_big_jobs;     // runs too large for the thread-per-run DP kernel (the warp-per-run kernel takes them)
 	unsigned long long big_cursor;     // entries of the big-run list written by the thread-per-run kernel
+	unsigned long long n_complex;      // records with I S H P D N ops the first launch of the word kernel left to the second
 };
 
 // BAM op codes

@@ -38,6 +38,8 @@ struct K1Params {
 	uint64_t        n_list;
 	const unsigned long long *n_list_dev;   // warp kernel: when set, the list length is read on the device (no host round trip)
 	uint64_t       *deferred;    // thread kernel: records it could not handle (capacity n)
+	uint64_t       *complex_list;// word kernel: records with events, handled by its second launch (capacity n)
+	uint64_t       *complex_ce;  // word kernel: start column and projected position of those records (2 per entry)
 	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
 	uint64_t        rr_base;     // added to every stored rr_off
 };
@@ -99,7 +101,8 @@ struct K4Params {
 };
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
-void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record (short records)
+void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record, run walk (v4-v13)
+void launch_k1_word(const K1Params &P, int n_sms, cudaStream_t stream);     // thread per record, word-parallel (v14; default)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
 void launch_k3_thread(const K3Params &P, cudaStream_t stream);               // thread per run (small runs)
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);

@@ -1,0 +1,156 @@
+// TEST INFRASTRUCTURE — runs the per-record core of kernel K1W (panvc3_b200/csrc/pv3_k1w_core.h, the very code the CUDA
+// kernel executes per thread) on the CPU, so that it can be checked against the oracle without a GPU
+// (tests/test_k1w_core.py). Everything around the core that the kernel does cooperatively (query staging, start
+// position by select0/rank0) is restated here in the plainest way.
+//
+//   g++ -O2 -std=c++17 -shared -fPIC -o tests/cpp/_build/libk1w_emul.so tests/cpp/k1w_emul.cc
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../panvc3_b200/csrc/pv3_k1w_core.h"
+#include "../../panvc3_b200/csrc/pv3_index_build.h"
+
+using namespace pv3;
+
+namespace {
+
+struct Row {
+	std::vector <uint64_t> words;     // padded with all-ones words, bits >= n_bits set
+	std::vector <uint64_t> zeros_before;  // per word
+	uint64_t n_bits = 0, n_zeros = 0;
+};
+
+struct Ref { std::vector <uint8_t> codes4; uint64_t n = 0; };
+
+struct Index { std::vector <Row> rows; std::vector <Ref> refs; };
+
+uint64_t rank0(Row const &r, uint64_t pos)
+{
+	if (pos >= r.n_bits) return r.n_zeros;
+	uint64_t const w = pos >> 6, b = pos & 63;
+	uint64_t z = r.zeros_before[w];
+	if (b) z += (uint64_t) __builtin_popcountll(~r.words[w] & ((1ull << b) - 1ull));
+	return z;
+}
+
+uint64_t select0(Row const &r, uint64_t k)   // position of the k-th zero (1-based); n_bits when there are fewer
+{
+	if (k == 0 || k > r.n_zeros) return r.n_bits;
+	size_t lo = 0, hi = r.zeros_before.size() - 1;     // last word with zeros_before < k
+	while (lo < hi) { size_t const mid = (lo + hi + 1) / 2; if (r.zeros_before[mid] < k) lo = mid; else hi = mid - 1; }
+	uint64_t inv = ~r.words[lo];
+	uint64_t need = k - r.zeros_before[lo];
+	for (unsigned b = 0; b < 64; ++b) if ((inv >> b) & 1ull) { if (--need == 0) return lo * 64 + b; }
+	return r.n_bits;
+}
+
+} // namespace
+
+static int g_events_everywhere = 1;   // 1: one launch, event code for every record (what the kernel does); 0: EV = false first, EV = true for the rest
+
+extern "C" {
+
+void k1w_set_mode(int events_everywhere) { g_events_everywhere = events_everywhere; }
+
+void *k1w_index_create() { return new Index; }
+void k1w_index_destroy(void *p) { delete (Index *) p; }
+
+int k1w_index_add_row(void *p, const uint64_t *words, uint64_t n_bits)
+{
+	Index &ix = *(Index *) p;
+	Row r;
+	r.n_bits = n_bits;
+	size_t const nw = (n_bits + 63) / 64;
+	r.words.assign(words, words + nw);
+	if (n_bits % 64) r.words[nw - 1] |= ~0ull << (n_bits % 64);
+	r.words.resize(nw + 72, ~0ull);
+	r.zeros_before.resize(r.words.size());
+	uint64_t z = 0;
+	for (size_t w = 0; w < r.words.size(); ++w) { r.zeros_before[w] = z; z += (uint64_t) __builtin_popcountll(~r.words[w]); }
+	r.n_zeros = z;
+	ix.rows.push_back(std::move(r));
+	return (int) ix.rows.size() - 1;
+}
+
+int k1w_index_add_ref(void *p, const char *bases, uint64_t n)
+{
+	Index &ix = *(Index *) p;
+	Ref r; r.n = n;
+	r.codes4.resize(codes4_bytes(n) + 64);
+	pack_codes4(bases, n, r.codes4.data());
+	ix.refs.push_back(std::move(r));
+	return (int) ix.refs.size() - 1;
+}
+
+// Whole records. status: 0 done by the first launch (no events), 2 done by the second (events), 1 deferred (the general
+// kernel would take the record). ops: [n][OUTQ].
+// Returns the number of deferred records.
+uint64_t k1w_emul_batch(void *p, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint32_t *dst_ref, const uint64_t *src_pos,
+	const uint64_t *seq_off, const uint8_t *seq, const uint64_t *cig_off, const uint32_t *cig,
+	uint8_t *status, uint64_t *dst_pos, uint32_t *n_ops, uint32_t *ops, uint8_t *adjacent)
+{
+	Index &ix = *(Index *) p;
+	uint64_t deferred = 0;
+	std::vector <uint32_t> q4;
+	for (uint64_t rec = 0; rec < n; ++rec) {
+		status[rec] = 1; dst_pos[rec] = 0; n_ops[rec] = 0; adjacent[rec] = 0;
+		Row const &S = ix.rows[src_row[rec]], &D = ix.rows[dst_row[rec]];
+		Ref const &R = ix.refs[dst_ref[rec]];
+		uint64_t const spos = src_pos[rec], nq = seq_off[rec + 1] - seq_off[rec], nc = cig_off[rec + 1] - cig_off[rec];
+		uint64_t const c0 = (spos < S.n_zeros) ? select0(S, spos + 1) : S.n_bits;
+		uint64_t const e0 = rank0(D, c0);
+		dst_pos[rec] = e0;
+		bool defer = (S.n_bits != D.n_bits || e0 > R.n || nc >= 0x8000 || spos >= S.n_zeros);
+		// query staging: nibbles at an arbitrary lead (as in a tile, where the record starts somewhere inside the staged bytes)
+		uint32_t const qrel = (uint32_t) (rec * 7u) % 29u;
+		q4.assign((qrel + nq + 7) / 8 + 4, 0xeeeeeeeeu);      // foreign nibbles around the record never equal a target code of interest
+		for (uint64_t i = 0; i < nq; ++i) {
+			uint8_t const rank = seq[seq_off[rec] + i];
+			if (rank > 7) defer = true;
+			uint32_t const a = qrel + (uint32_t) i;
+			q4[a >> 3] = (q4[a >> 3] & ~(0xfu << (4 * (a & 7)))) | ((uint32_t) (rank & 0xf) << (4 * (a & 7)));
+		}
+		int path = 0;
+		if (!defer) {
+			uint32_t cmp[k1w::NW], ins[k1w::NW], del[k1w::NW], xm[k1w::NW], brk[k1w::NBRK], fin[k1w::OUTQ];
+			k1w::Lane <1> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
+			k1w::SpanIn I;
+			I.Sp = S.words.data() + (c0 >> 6); I.Dp = D.words.data() + (c0 >> 6); I.c_lo6 = (uint32_t) c0 & 63u;
+			I.src_left = S.n_zeros - spos; I.e_start = e0; I.ref_n = R.n; I.nq = (uint32_t) nq; I.q_start = 0;
+			k1w::OpRange opr; opr.cig = cig + cig_off[rec]; opr.k0 = 0; opr.k1 = (uint32_t) nc; opr.first_cnt = ~0u; opr.last_cnt = ~0u; opr.first_val = nc ? opr.cig[0] : 0u;
+			k1w::SpanState st;
+			uint64_t const e0a = e0 & ~31ull;
+			const uint32_t *rs = reinterpret_cast <const uint32_t *>(R.codes4.data() + (e0a >> 1));
+			uint32_t no = 0; bool adj = false;
+			// first launch: records without events; second launch (EV = true): the others
+			int rc = g_events_everywhere ? 2 : k1w::build_span <1, false>(I, opr, L, st);
+			if (rc == 0) {
+				k1w::compare_span <1, false>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
+				k1w::mark_runs <1, false>(L, st.n_brk, st.w_end);
+				no = k1w::emit_ops <1, false>(L, st.n_brk, opr, st.w_end, adj);
+			} else if (rc == 2) {
+				rc = k1w::build_span <1, true>(I, opr, L, st);
+				path = st.simple ? 0 : 2;
+				if (rc == 0) {
+					k1w::compare_span <1, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
+					k1w::mark_runs <1, true>(L, st.n_brk, st.w_end);
+					no = k1w::emit_ops <1, true>(L, st.n_brk, opr, st.w_end, adj);
+				}
+			}
+			if (rc != 0 || no > (uint32_t) k1w::OUTQ) defer = true;
+			else {
+				n_ops[rec] = no; adjacent[rec] = adj;
+				memcpy(ops + rec * k1w::OUTQ, fin, no * 4);
+			}
+		}
+		status[rec] = defer ? 1 : (uint8_t) path;
+		deferred += defer;
+	}
+	return deferred;
+}
+
+int k1w_outq() { return k1w::OUTQ; }
+
+} // extern "C"

@@ -96,7 +96,7 @@ def test_reference_tables_through_projector_api(gpu, fixtures_json):
 def test_golden_random_vectors_of_compiled_reference(gpu):
     for msa, b, go, ge, full, rew in load_golden_random():
         idx = device_index(msa)
-        for path in (0, 1):
+        for path in (0, 1, 2):
             idx.ctx.set_kernel_path(path)
             idx.ctx.set_stage(0)
             assert_same(idx.project_batch(b, go, ge), full, b, f"gpu vs golden(reference) full go={go} ge={ge} path={path}")
@@ -114,7 +114,7 @@ def test_random_batches_match_oracle(gpu, port, seed):
     for go, ge in [(0, -1), (0, -3), (-2, -1), (-5, -2), (3, -1)]:
         for stage in (1, 0):
             exp = oi.project_batch(b, go, ge, stage=stage)
-            for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):      # dp_min 0: small runs go to the thread-per-run DP kernel
+            for path, dp_min in ((0, 16384), (1, 16384), (0, 0), (2, 16384)):      # dp_min 0: small runs go to the thread-per-run DP kernel
                 idx.ctx.set_stage(stage)
                 idx.ctx.set_kernel_path(path)
                 idx.ctx.set_dp_thread_min(dp_min)
@@ -174,7 +174,7 @@ def test_dp_modes_large_windows(gpu, port):
     b = RecordBatch.from_records(recs)
     for go, ge in [(0, -1), (-3, -1), (2, -2)]:
         exp = oi.project_batch(b, go, ge)
-        for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):
+        for path, dp_min in ((0, 16384), (1, 16384), (0, 0), (2, 16384)):
             idx.ctx.set_kernel_path(path)
             idx.ctx.set_dp_thread_min(dp_min)
             got = idx.project_batch(b, go, ge)
@@ -191,7 +191,7 @@ def test_long_reads_overflow_the_stage(gpu, port):
     oi = port.make_index(*casegen.index_inputs(msa))
     exp = oi.project_batch(b, 0, -1)
     assert int(exp.cig_len.max()) > 300
-    for path in (0, 1):
+    for path in (0, 1, 2):
         idx.ctx.set_kernel_path(path)
         assert_same(idx.project_batch(b, 0, -1), exp, b, f"long reads path={path}")
 
@@ -292,7 +292,7 @@ def test_realistic_reads_both_paths_and_mixed_lengths(gpu, port, workflow_msa):
     oi = port.make_index(*casegen.index_inputs(workflow_msa))
     for go, ge in [(0, -1), (-2, -1)]:
         exp = oi.project_batch(b, go, ge, n_threads=os.cpu_count() or 1)
-        for path in (0, 1):
+        for path in (0, 1, 2):
             idx.ctx.set_kernel_path(path)
             assert_same(idx.project_batch(b, go, ge), exp, b, f"mixed go={go} path={path}")
 
@@ -350,7 +350,7 @@ def test_large_index_parity(gpu, port):
     oi = port.make_index(*casegen.index_inputs(msa))
     b = sample_reads(msa, 40_000, 150, seed=9)
     exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
-    for path in (0, 1):
+    for path in (0, 1, 2):
         idx.ctx.set_kernel_path(path)
         assert_same(idx.project_batch(b, 0, -1), exp, b, f"large index path={path}")
     # mates: position-only projection at random positions of every founder row
@@ -537,7 +537,7 @@ def test_bam4_packed_seq_random_batches(gpu, port, seed):
     for go, ge in [(0, -1), (-2, -1), (3, -1)]:
         for stage in (1, 0):
             exp = oi.project_batch(b, go, ge, stage=stage)
-            for path, dp_min in ((0, 16384), (1, 16384), (0, 0)):
+            for path, dp_min in ((0, 16384), (1, 16384), (0, 0), (2, 16384)):
                 idx.ctx.set_stage(stage); idx.ctx.set_kernel_path(path); idx.ctx.set_dp_thread_min(dp_min)
                 assert_same(idx.project_batch(p, go, ge), exp, b, f"bam4 seed={seed} stage={stage} go={go} ge={ge} path={path} dp_min={dp_min}")
 
