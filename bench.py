@@ -2,17 +2,25 @@
 """bench.py — project_alignments hot path on B200 (contract: see the task statement / DESIGN.md §Measurement).
 
   python bench.py --gpus N --steps K --warmup W            our CUDA path (one process per GPU under torchrun for N>1)
-  python bench.py --impl reference --steps K --warmup W    the reference's own CPU implementation on the host cores
+  python bench.py --impl reference --gpus N --steps K --warmup W    the reference's own CPU implementation on the host cores
 
-A step = one pass of the hot path (projection → CIGAR rewrite → indel-run realignment → splice) over one batch of
-synthetic records. Workload at every N: BASELINE.json configs[1] — the test-workflow MSA index (5 rows × 12 636 columns,
-tests/golden/test_workflow_msa.npz) and 1 M synthetic 150-bp reads PER GPU sampled from the founder rows (weak scaling;
-contiguous shards, no data-path collective).
+A step = one pass of the hot path (projection → CIGAR rewrite → indel-run realignment → splice; mate positions where the
+workload is paired) over one batch of synthetic records.
+
+Workload:
+  N = 1   BASELINE.json configs[1] — the test-workflow MSA index (5 rows × 12 636 columns, tests/golden/test_workflow_msa.npz)
+          and 1 M synthetic 150-bp reads sampled from the founder rows (the config BASELINE labels "1 GPU"); a `chr_scale` leg
+          beside it runs configs[2]'s index on the same GPU
+  N >= 2  BASELINE.json configs[2] — chromosome-scale MSA (REF + 25 founders, 2.5·10⁸ columns, rows built as bit words),
+          1 M synthetic 150-bp PAIRED reads per GPU per step (mates projected inside the step); weak scaling, contiguous
+          shards, index replicated, no data-path collective
 
   value     alignments/s, whole job, inputs resident in HBM, K steps timed with CUDA events on the launch stream
-  e2e       the same through pv3_project with pinned HOST buffers: H2D + kernels + D2H inside the timed region
-  roofline  dominant kernel (k1_rewrite_kernel): algorithmic bytes / its mean CUDA-event duration vs the measured HBM peak
-  cpu_baseline  oracle/_ref (the reference compiled in place) or the C port, timed on the host cores (rank 0, N=1 only)
+  e2e       the same through pv3_project with pinned HOST buffers (compact input encoding, BAM-packed SEQ, ordered narrow
+            output written back in place): H2D + kernels + write-back inside the timed region; for N > 1 every rank's
+            results land in its slice of ONE shared pinned buffer in input order (the writer's memory)
+  roofline  dominant kernel (the thread-per-record rewrite kernel): algorithmic bytes / its mean CUDA-event duration
+  cpu_baseline  oracle/_ref (the reference compiled in place), timed on the host cores (rank 0, N=1 only)
 """
 from __future__ import annotations
 
@@ -36,44 +44,58 @@ UNIT = "alignments/s"
 SEED = 20261104 + 2          # seed = 20261104 + config id
 READ_LEN = 150
 RECORDS_PER_GPU = 1_000_000
+PARITY_SAMPLE = 20_000       # records per shard compared with the oracle after the timed region
 
 
-def load_workload(n: int, rank: int = 0, workload: str = "config2"):
-    from panvc3_b200.workload import load_msa_npz, sample_reads, synth_msa
+class Workload:
+    """index_inputs: (gap rows, contigs) as the oracle and the product take them; batch: RecordBatch of this rank; mates:
+    (mate_row, dst_row, mate_pos) or None; regen(rank, n): the first n records (+ mates) of any rank's batch."""
+
+    def __init__(self, name, index_inputs, batch, mates, regen, msa):
+        self.name, self.index_inputs, self.batch, self.mates, self.regen, self.msa = name, index_inputs, batch, mates, regen, msa
+
+
+def load_workload(n: int, rank: int = 0, workload: str = "config2", index_only: bool = False) -> Workload:
+    import casegen
+    from panvc3_b200.workload import READ_BLOCK, load_msa_npz, sample_reads, sample_reads_words, synth_msa, synth_msa_words
+    if workload == "chr26":
+        cols = int(os.environ.get("PV3_CHR_COLS", "250000000"))
+        founders = int(os.environ.get("PV3_CHR_FOUNDERS", "25"))
+        msa = synth_msa_words(cols, founders, seed=SEED + 21, p_gap=0.002, mean_gap=8, snp=0.001)
+        name = (f"configs[2]: chromosome-scale MSA ({cols} columns, REF + {founders} founders = {founders + 1} gap rows built as bit words), "
+                f"synthetic 150-bp PAIRED reads sampled from the founders (mate positions projected inside the step), QUAL present, M-style CIGARs")
+        make = lambda r, m: sample_reads_words(msa, m, READ_LEN, seed=SEED + 1000 * r + 2)
+        batch, mates = (None, None) if index_only else make(rank, n)
+
+        def regen(r, m):
+            # blocks of READ_BLOCK reads have their own seeds: the head of rank r's batch without generating all of it
+            bt, mt = make(r, max(m, min(n, READ_BLOCK)))
+            return bt.slice(0, m), tuple(a[:m] for a in mt)
+        return Workload(name, msa.index_inputs(), batch, mates, regen, msa)
     if workload == "indel":
         # configs[3]-style stress (scaled): dense abutting insertion/deletion columns force realignment (DP-bound)
         msa = synth_msa(400_000, 4, seed=SEED + 11, p_gap=0.01, mean_gap=6, snp=0.01, anticorrelated=0.01)
-        batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank + 1, ins=0.001, dele=0.001)
+        make = lambda r, m: sample_reads(msa, m, READ_LEN, seed=SEED + 1000 * r + 1, ins=0.001, dele=0.001)
         name = "configs[3]-style indel-heavy stress: synthetic 400k-column MSA with abutting I/D columns, 150-bp reads"
     elif workload == "long":
-        # configs[4]-style long reads (scaled): every record exceeds the thread kernel's quotas → the warp-per-record kernel
-        cols = int(os.environ.get("PV3_CHR_COLS", "20000000"))
+        cols = int(os.environ.get("PV3_LONG_COLS", "20000000"))
         msa = synth_msa(cols, 3, seed=SEED + 31, p_gap=0.002, mean_gap=8, snp=0.001)
-        batch = sample_reads(msa, n, 10_000, seed=SEED + 1000 * rank + 3, ins=0.0002, dele=0.0002)
+        make = lambda r, m: sample_reads(msa, m, 10_000, seed=SEED + 1000 * r + 3, ins=0.0002, dele=0.0002)
         name = f"configs[4]-style long reads: synthetic {cols}-column MSA, 1+3 rows, 10-kb reads with indels"
-    elif workload == "chr":
-        # configs[2]-style scale (bounded by host memory for the generator): index and target are not cache-resident
-        cols = int(os.environ.get("PV3_CHR_COLS", "100000000"))
-        msa = synth_msa(cols, 3, seed=SEED + 21, p_gap=0.002, mean_gap=8, snp=0.001)
-        batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank + 2)
-        name = f"configs[2]-style scale: synthetic {cols}-column MSA, 1+3 rows, 150-bp reads sampled from the founders"
     else:
         msa = load_msa_npz(os.path.join(ROOT, "tests", "golden", "test_workflow_msa.npz"))
-        batch = sample_reads(msa, n, READ_LEN, seed=SEED + 1000 * rank)
+        make = lambda r, m: sample_reads(msa, m, READ_LEN, seed=SEED + 1000 * r)
         name = "configs[1]: test-workflow index (5 rows x 12636 cols) + 1M synthetic 150bp reads per GPU, QUAL present, M-style CIGARs"
-    if os.environ.get("PV3_BENCH_ORDER", "") == "sorted":
+    batch = None if index_only else make(rank, n)
+    if batch is not None and os.environ.get("PV3_BENCH_ORDER", "") == "sorted":
         batch = batch.coordinate_sorted()
         name += " [coordinate-sorted]"
-    return msa, batch, name
+    regen = lambda r, m: (make(r, n).slice(0, m), None)
+    return Workload(name, casegen.index_inputs(msa), batch, None, regen, msa)
 
 
-def algorithmic_bytes(msa, batch, out_cig_words: int, n_runs: int, dp_window_bytes: int) -> dict:
-    """Bytes the path must move per SURVEY.md §8(d) (B_rec summed over the batch).
-
-    strict: what the rewrite kernel's algorithm has to touch — query bases, the compared target bytes, the src+dst gap
-    bits over the spanned columns, two directory entries, CIGAR ops in and out, positions/ids/offsets, range outputs.
-    QUAL is only needed for realigned windows, so only those bytes are counted. `survey` adds the full QUAL string as
-    §8(d)'s formula does (≈590 B per 150-bp record)."""
+def spanned_columns(wl: Workload, batch) -> np.ndarray:
+    """Columns of the source row every record spans: select0(pos + ref_consumed) - select0(pos + 1) + 1."""
     n = batch.n
     ops = batch.cig & 0xF
     cnt = (batch.cig >> 4).astype(np.int64)
@@ -81,24 +103,46 @@ def algorithmic_bytes(msa, batch, out_cig_words: int, n_runs: int, dp_window_byt
     ref_cons = np.zeros(n, np.int64)
     m = np.isin(ops, [0, 2, 3, 7, 8])
     np.add.at(ref_cons, rec_of_op[m], cnt[m])
-    mlike = np.zeros(n, np.int64)
-    mm = np.isin(ops, [0, 7, 8])
-    np.add.at(mlike, rec_of_op[mm], cnt[mm])
-    # columns spanned in the source row: select0(pos + ref_cons) - select0(pos + 1) + 1
     span = np.zeros(n, np.int64)
-    for r in range(msa.n_rows):
+    rows, _ = wl.index_inputs
+    for r in np.unique(batch.src_row):
         sel = np.flatnonzero(batch.src_row == r)
-        if not sel.size:
-            continue
-        zero_pos = np.flatnonzero(msa.rows[r] != ord("-"))
+        words, n_bits = rows[int(r)]
+        inv = ~np.asarray(words, dtype=np.uint64)
+        if n_bits % 64:
+            inv[-1] &= (np.uint64(1) << np.uint64(n_bits % 64)) - np.uint64(1)
+        pc = np.unpackbits(inv.view(np.uint8)).reshape(-1, 64).sum(axis=1) if inv.size < (1 << 22) else None
+        if pc is None:
+            from panvc3_b200.workload import _popcount64
+            pc = _popcount64(inv)
+        zb = np.zeros(inv.size + 1, np.int64); np.cumsum(pc, out=zb[1:])
+
+        def col_of(k):                                    # column of the k-th base (0-based), clamped to the row
+            k = np.minimum(k, zb[-1] - 1)
+            w = np.searchsorted(zb, k, side="right") - 1
+            bits = np.unpackbits(inv[w].view(np.uint8).reshape(-1, 8), axis=1, bitorder="little")
+            inside = (np.cumsum(bits, axis=1) > (k - zb[w])[:, None]).argmax(axis=1)
+            return w * 64 + inside
         p0 = batch.src_pos[sel].astype(np.int64)
-        p1 = np.minimum(p0 + np.maximum(ref_cons[sel], 1) - 1, zero_pos.size - 1)
-        span[sel] = zero_pos[p1] - zero_pos[np.minimum(p0, zero_pos.size - 1)] + 1
+        span[sel] = col_of(p0 + np.maximum(ref_cons[sel], 1) - 1) - col_of(p0) + 1
+    return span, ref_cons, np.isin(ops, [0, 7, 8]), rec_of_op, cnt
+
+
+def algorithmic_bytes(wl: Workload, batch, out_cig_words: int, n_runs: int, mates: bool) -> dict:
+    """Bytes the path must move per SURVEY.md §8(d) (B_rec summed over the batch).
+
+    strict: what the rewrite kernel's algorithm has to touch — query bases, the compared target bytes, the src+dst gap
+    bits over the spanned columns, two directory entries, CIGAR ops in and out, positions/ids/offsets, range outputs; for a
+    paired workload also the mate's ids / position in, projected position out and two more directory entries. QUAL is only
+    needed for realigned windows and not counted. `survey` adds the full QUAL string as §8(d)'s formula does."""
+    n = batch.n
+    span, ref_cons, mm, rec_of_op, cnt = spanned_columns(wl, batch)
+    mlike = np.zeros(n, np.int64)
+    np.add.at(mlike, rec_of_op[mm], cnt[mm])
     gap_bytes = 2 * ((span + 7) // 8)
-    seq_bytes = int(batch.seq.size)
-    strict = (seq_bytes + int(mlike.sum()) + int(gap_bytes.sum()) + 32 * n + 4 * (int(batch.cig.size) + out_cig_words)
-              + 16 * n + 12 * n + 32 * n_runs + dp_window_bytes)
-    survey = strict + (int(batch.qual.size) if batch.qual_off is not None else 0) - dp_window_bytes
+    strict = (int(batch.seq.size) + int(mlike.sum()) + int(gap_bytes.sum()) + 32 * n + 4 * (int(batch.cig.size) + out_cig_words)
+              + 16 * n + 12 * n + 32 * n_runs + ((4 + 8 + 8 + 32) * n if mates else 0))
+    survey = strict + (int(batch.qual.size) if batch.qual_off is not None else 0)
     return {"strict": int(strict), "survey": int(survey)}
 
 
@@ -149,8 +193,7 @@ class ClockSampler:
 
 def bind_to_gpu_numa_node(gpu_index: int) -> str | None:
     """Pins this rank to the CPUs next to its GPU (NVML's affinity mask) before any pinned buffer is allocated, so that the
-    host side of every H2D/D2H copy is first-touched on the GPU's own NUMA node (one process per GPU: 8 ranks otherwise share
-    whatever node the launcher started them on)."""
+    host side of every H2D/D2H copy is first-touched on the GPU's own NUMA node."""
     try:
         import pynvml
         pynvml.nvmlInit()
@@ -176,64 +219,16 @@ def measured_peak_gbs() -> tuple[float, str]:
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def measured_traffic_bytes() -> tuple[int | None, str | None]:
-    """dram__bytes_read.sum + dram__bytes_write.sum of one k1_thread_kernel launch on this workload, from the committed
+def measured_traffic_bytes(key: str) -> tuple[int | None, str | None]:
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel on this workload, from the committed
     `ncu --set full` capture (profiles/k1t_traffic.json); None when no capture is on record."""
     p = os.path.join(ROOT, "profiles", "k1t_traffic.json")
     try:
         d = json.load(open(p))
+        d = d.get(key, d if key == "config2" else None)
         return int(d["dram_bytes_read"] + d["dram_bytes_write"]), d.get("source")
     except Exception:
         return None, None
-
-
-def realign_dp_leg(ctx, dev, n: int, steps: int) -> dict:
-    """Realignment throughput on the DP-bound shape (configs[3]-style indel-heavy reads, scaled): GCUPS over the DP kernels."""
-    from panvc3_b200.device import DeviceBatch, project_device
-    from panvc3_b200.projector import MsaIndex
-    msa, batch, name = load_workload(n, 0, "indel")
-    idx = MsaIndex.from_msa(msa, device=dev.index)
-    c = idx.ctx
-    c.set_params(0, -1)
-    db = DeviceBatch(batch, dev)
-    out = project_device(c, db)
-    for _ in range(2):
-        project_device(c, db, out)
-    ms = []
-    for _ in range(steps):
-        project_device(c, db, out)
-        ms.append(c.timing()["ms_realign"])
-    st = dict(out.stats)
-    t = statistics.mean(ms)
-    return {"workload": name, "records": n, "runs": st["rr_used"], "dp_cells": st["dp_cells"], "ms_dp_kernels": t,
-            "gcups": st["dp_cells"] / (t * 1e-3) / 1e9 if t > 0 else None,
-            "note": "runs here are a few bases wide (mean 17 cells): the figure is bounded by per-run overhead, not by cell updates"}
-
-
-def sorted_input_leg(ctx, dev, stream, msa, batch, steps: int, peak: float) -> dict:
-    """The same records in the order the reference's workflow feeds them: test-workflow/Snakefile runs `samtools sort` before
-    project_alignments (its input is alignments.sorted.bam), so consecutive records share source row and neighbourhood and
-    the lanes of a warp walk similar gap structure. Device-resident input, CUDA events, like `value`."""
-    from panvc3_b200.device import DeviceBatch, project_device
-    sb = batch.coordinate_sorted()
-    db = DeviceBatch(sb, dev)
-    out = project_device(ctx, db)
-    for _ in range(3):
-        project_device(ctx, db, out)
-    e0, e1 = torch_events()
-    k1 = []
-    e0.record(stream)                       # the stream the kernels are launched on (pv3_set_stream)
-    for _ in range(steps):
-        project_device(ctx, db, out)
-        k1.append(ctx.timing()["ms_rewrite_main"])
-    e1.record(stream); e1.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    st = dict(out.stats)
-    ab = algorithmic_bytes(msa, sb, int(out.cig_len[:sb.n].sum().item()), st["rr_used"], 0)
-    k = statistics.mean(k1)
-    return {"value": sb.n / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "k1_thread_kernel_ms": k,
-            "roofline_frac": ab["strict"] / (k * 1e-3) / 1e9 / peak,
-            "what": "same records sorted by (source row, position) as `samtools sort` leaves them for project_alignments in test-workflow/Snakefile; the headline `value` keeps the random order"}
 
 
 def torch_events():
@@ -241,10 +236,160 @@ def torch_events():
     return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
 
+def device_leg(ctx, dev, stream, wl: Workload, batch, mates, steps: int, warmup: int, peak: float) -> dict:
+    """HBM-resident inputs, K steps between CUDA events on the launch stream; mates projected by the same call."""
+    from panvc3_b200.device import DeviceBatch, project_device
+    db = DeviceBatch(batch, dev, mates=mates)
+    out = project_device(ctx, db)
+    for _ in range(warmup):
+        project_device(ctx, db, out)
+    e0, e1 = torch_events()
+    k1, k1m, k3, k4, n_def = [], [], [], [], []
+    launches0 = ctx.total_launches()
+    e0.record(stream)
+    for _ in range(steps):
+        project_device(ctx, db, out)
+        t = ctx.timing()
+        k1.append(t["ms_rewrite"]); k1m.append(t["ms_rewrite_main"]); k3.append(t["ms_realign"]); k4.append(t["ms_splice"]); n_def.append(t["n_deferred"])
+    e1.record(stream); e1.synchronize()
+    ms = e0.elapsed_time(e1)
+    st = dict(out.stats)
+    ab = algorithmic_bytes(wl, batch, int(out.cig_len[:batch.n].sum().item()), st["rr_used"], mates is not None)
+    kern = statistics.mean(k1m)
+    kernel_name = "k1_thread_kernel"
+    if int(max(n_def)) * 2 > batch.n:
+        kern = statistics.mean(k1)
+        kernel_name = "k1_thread_kernel + k1_rewrite_kernel (most records deferred to the warp-per-record kernel)"
+    return {"ms_total": ms, "ms_per_step": ms / steps, "launches": ctx.total_launches() - launches0, "stats": st, "out": out, "db": db,
+            "kernels_ms": {"rewrite": statistics.mean(k1), "rewrite_thread_kernel_alone": statistics.mean(k1m), "deferred_records": int(max(n_def)),
+                           "realign": statistics.mean(k3), "splice": statistics.mean(k4)},
+            "roofline": {"kernel": kernel_name, "kernel_ms": kern, "achieved": ab["strict"] / (kern * 1e-3) / 1e9, "frac": ab["strict"] / (kern * 1e-3) / 1e9 / peak,
+                         "algorithmic_bytes_per_launch": ab["strict"], "bytes_per_record": ab["strict"] / batch.n,
+                         "bytes_per_record_survey_formula": ab["survey"] / batch.n, "frac_survey_formula": ab["survey"] / (kern * 1e-3) / 1e9 / peak}}
+
+
+class HostBuffers:
+    """One rank's pinned input (compact or wide encoding) and its output slice; `shared` places the output in a POSIX
+    shared-memory segment (one per job, every rank registers its slice with pv3_host_register) so that all shards end up in
+    input order in memory the writer — rank 0 — can read without any further copy."""
+
+    def __init__(self, ctx, batch, mates, cig_cap, rr_cap, compact: bool, packed: bool, out_view=None):
+        from panvc3_b200.batch import RecordBatch
+        from panvc3_b200.capi import PinnedArena, alloc_output
+        lib = ctx.lib
+        src = batch.to_bam4() if packed else batch
+        self.src = src
+        n = batch.n
+        self.arena = PinnedArena(lib, src.input_bytes() + n * 80 + 64 * 4096 + (0 if out_view is not None else n * 48 + cig_cap * 4 + rr_cap * 32))
+        take = lambda a: None if a is None else self._copy(a)
+        self.pb = RecordBatch.__new__(RecordBatch)
+        for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
+            setattr(self.pb, k, take(getattr(src, k)))
+        self.mates = None if mates is None else (take(np.ascontiguousarray(mates[0], dtype=np.uint32)), take(np.ascontiguousarray(mates[-1], dtype=np.uint64)))
+        self.compact = None
+        if compact:
+            self.compact = {k: take(v) for k, v in src.compact_arrays(mates).items()}
+        mk = (lambda shape, dt: self.arena.take(shape, dt)) if out_view is None else out_view
+        self.narrow = None
+        if compact:
+            self.narrow = dict(dst_pos32=mk((n,), np.uint32), flags8=mk((n,), np.uint8), cig_len16=mk((n,), np.uint16), rr_len8=mk((n,), np.uint8))
+            if mates is not None:
+                self.narrow["mate_dst_pos32"] = mk((n,), np.uint32)
+        from panvc3_b200.batch import ProjectedBatch
+        z = np.zeros(1, np.uint64)
+        if compact:
+            self.out = ProjectedBatch(dst_pos=z, flags=z.view(np.uint32)[:1], cig_off=z, cig_len=z.view(np.uint32)[:1], cig=mk((cig_cap,), np.uint32),
+                                      rr_off=z, rr_len=z.view(np.uint32)[:1], rr=mk((rr_cap, 4), np.uint64))
+        else:
+            self.out = ProjectedBatch(dst_pos=mk((n,), np.uint64), flags=mk((n,), np.uint32), cig_off=mk((n,), np.uint64), cig_len=mk((n,), np.uint32),
+                                      cig=mk((cig_cap,), np.uint32), rr_off=mk((n,), np.uint64), rr_len=mk((n,), np.uint32), rr=mk((rr_cap, 4), np.uint64))
+            if mates is not None:
+                self.out.mate_dst_pos = mk((n,), np.uint64)
+        self.h2d_bytes = (src.compact_input_bytes(mates is not None) if compact else
+                          src.input_bytes() - (src.qual.nbytes + src.qual_off.nbytes if src.qual_off is not None else 0) + (12 * n if mates is not None else 0)
+                          + (src.qual_off.nbytes if src.qual_off is not None else 0))
+        self.fixed_out = n * ((4 + 1 + 2 + 1 + (4 if mates is not None else 0)) if compact else (36 + (8 if mates is not None else 0)))
+
+    def _copy(self, a):
+        q = self.arena.take(a.shape, a.dtype); q[...] = a
+        return q
+
+    def run(self, ctx):
+        return ctx.project(self.pb, self.out, mates=None if self.compact else self.mates, compact=self.compact, narrow=self.narrow)
+
+    def d2h_bytes(self, stats):
+        return int(self.fixed_out + stats["cig_used"] * 4 + stats["rr_used"] * 32)
+
+    def as_projected(self, n):
+        """The results as a wide ProjectedBatch (offsets by scanning the lengths: the arenas are in record order)."""
+        from panvc3_b200.batch import ProjectedBatch
+        if not self.compact:
+            return self.out
+        cl, rl = self.narrow["cig_len16"].astype(np.uint32), self.narrow["rr_len8"].astype(np.uint32)
+        ex = lambda l: np.concatenate([[0], np.cumsum(l[:-1], dtype=np.uint64)]).astype(np.uint64) if l.size else np.zeros(0, np.uint64)
+        return ProjectedBatch(dst_pos=self.narrow["dst_pos32"].astype(np.uint64), flags=self.narrow["flags8"].astype(np.uint32), cig_off=ex(cl), cig_len=cl,
+                              cig=self.out.cig, rr_off=ex(rl), rr_len=rl, rr=self.out.rr,
+                              mate_dst_pos=self.narrow["mate_dst_pos32"].astype(np.uint64) if "mate_dst_pos32" in self.narrow else None)
+
+
+def shared_output_views(n: int, cig_cap: int, rr_cap: int, world: int, rank: int, dist, lib):
+    """One POSIX shared-memory segment for the whole job's ordered output; returns (segment, allocator for this rank's slice,
+    per-rank slice size)."""
+    from multiprocessing import shared_memory
+    per_rank = (n * 16 + cig_cap * 4 + rr_cap * 32 + 16 * 4096 + 4095) // 4096 * 4096
+    name = [None]
+    seg = None
+    if rank == 0:
+        seg = shared_memory.SharedMemory(create=True, size=per_rank * world)
+        name[0] = seg.name
+    dist.broadcast_object_list(name, src=0)
+    if rank != 0:
+        seg = shared_memory.SharedMemory(name=name[0])
+    whole = np.frombuffer(seg.buf, dtype=np.uint8)
+    mine = whole[rank * per_rank:(rank + 1) * per_rank]
+    if lib.pv3_host_register(mine.ctypes.data, mine.nbytes) != 0:
+        raise RuntimeError("pv3_host_register failed on the shared output segment")
+    off = [0]
+
+    def alloc(shape, dt, base=mine, cursor=off):
+        dt = np.dtype(dt)
+        nb = int(np.prod(shape)) * dt.itemsize
+        o = (cursor[0] + 255) // 256 * 256
+        cursor[0] = o + nb
+        return base[o:o + nb].view(dt).reshape(shape)
+    return seg, whole, mine, alloc, per_rank
+
+
+def parity_check(wl: Workload, world: int, n: int, fetch_shard, with_mates: bool) -> dict:
+    """After the timed region: a sample of every shard of the ordered output against the oracle (the C port; pinned to the
+    compiled reference in tests/). fetch_shard(r) → (ProjectedBatch of rank r's records, stats)."""
+    from oracle import oracle_lib
+    from parity import assert_same
+    port = oracle_lib.load("port")
+    oi = port.make_index(*wl.index_inputs)
+    checked = 0
+    m = min(PARITY_SAMPLE, n)
+    for r in range(world):
+        bt, mt = wl.regen(r, m)
+        exp = oi.project_batch(bt, 0, -1, n_threads=os.cpu_count() or 1)
+        got = fetch_shard(r)
+        from panvc3_b200.batch import ProjectedBatch
+        head = ProjectedBatch(dst_pos=got.dst_pos[:m], flags=got.flags[:m], cig_off=got.cig_off[:m], cig_len=got.cig_len[:m], cig=got.cig,
+                              rr_off=got.rr_off[:m], rr_len=got.rr_len[:m], rr=got.rr)
+        assert_same(head, exp, bt, f"shard {r} of the ordered output vs oracle", flags_exact=True)
+        if with_mates and mt is not None and got.mate_dst_pos is not None:
+            k = min(m, 2000)
+            want = np.array([oi.project_position(int(mt[0][i]), 0, int(mt[2][i])) for i in range(k)], dtype=np.uint64)
+            assert np.array_equal(got.mate_dst_pos[:k], want), f"shard {r}: mate positions differ from the oracle"
+        checked += m
+    return {"parity_checked": checked, "per_shard": m, "oracle": "C port of the reference (oracle/pv3_oracle.c)", "what": "dst_pos, flags, CIGAR words, realigned ranges (all records of the sample), mate positions (first 2000 per shard)"}
+
+
 def cpu_reference_lib():
     from oracle import oracle_lib
     if oracle_lib.have("reference"):
         return oracle_lib.load("reference"), "reference"
+    sys.stderr.write("bench.py: oracle/_ref is not built — the CPU baseline falls back to the C PORT of the reference (kind = 'port')\n")
     return oracle_lib.load("port"), "port"
 
 
@@ -258,16 +403,14 @@ def time_cpu(lib_index, batch, n_threads: int, repeats: int = 1) -> float:
     return best
 
 
-def cpu_baseline(msa, batch) -> dict:
+def cpu_baseline(wl: Workload, batch) -> dict:
     """Reference CPU path on the box's host cores over a bounded sample of the same workload (rank 0, N=1)."""
-    import casegen
     lib, kind = cpu_reference_lib()
-    idx = lib.make_index(*casegen.index_inputs(msa))
+    idx = lib.make_index(*wl.index_inputs)
     cores = os.cpu_count() or 1
     one = batch.slice(0, min(batch.n, 40_000))
     t1 = time_cpu(idx, one, 1)
     rate1 = one.n / t1
-    # all cores: size the sample for a few seconds of work
     n_all = int(min(batch.n, max(40_000, rate1 * cores * 3)))
     sample = batch.slice(0, n_all)
     tall = time_cpu(idx, sample, cores, repeats=2)
@@ -276,29 +419,41 @@ def cpu_baseline(msa, batch) -> dict:
             "value_1thread": rate1, "sample_1thread": f"first {one.n} records, 1 thread (what the shipped single-threaded binary does, SURVEY F6)"}
 
 
+def default_workload(world: int) -> str:
+    return "chr26" if world > 1 else "config2"
+
+
 def run_reference_arm(args) -> None:
     """--impl reference: the reference's own CPU code for the path (oracle/_ref when built, else the C port), all host
-    threads, each step a bounded sample of the same workload."""
+    threads, the same workload and records per step as the repo arm at this N."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import casegen
-    n = 400_000
-    msa, batch, name = load_workload(n, 0, args.workload)
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    workload = args.workload or default_workload(world)
+    n = args.records
+    wl = load_workload(n, 0, workload)
     lib, kind = cpu_reference_lib()
-    idx = lib.make_index(*casegen.index_inputs(msa))
+    idx = lib.make_index(*wl.index_inputs)
     cores = os.cpu_count() or 1
-    for _ in range(args.warmup):
+    batch = wl.batch
+
+    def step():
+        # (the CLI also projects the mate's position per record, project_alignments.cc:880-906: two rank/select queries against
+        # ~450 per record in rewrite_cigar; left out of the CPU step, which only flatters the CPU arm)
         idx.project_batch(batch, 0, -1, n_threads=cores)
+    for _ in range(args.warmup):
+        step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        idx.project_batch(batch, 0, -1, n_threads=cores)
+        step()
     dt = time.perf_counter() - t0
     value = n * args.steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": name, "records_per_step": n, "note": "bounded sample of the 1M-record step; CPU only, no GPU"},
+            "config": {"workload": wl.name, "records_per_gpu_per_step": n, "read_len": READ_LEN, "gap_open": 0, "gap_ext": -1,
+                       "note": "CPU only, no GPU: one shard's records per step (the CPU arm does not scale with --gpus); mate positions not projected"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": f"{n} records per step, {cores} threads, one projector per thread"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -310,8 +465,6 @@ def run_gpu_arm(args) -> None:
     import torch
     import torch.distributed as dist
     from panvc3_b200 import build as pv3_build
-    from panvc3_b200.capi import PinnedArena, alloc_output
-    from panvc3_b200.device import DeviceBatch, project_device
     from panvc3_b200.projector import MsaIndex
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -326,14 +479,16 @@ def run_gpu_arm(args) -> None:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     pv3_build.build()
+    workload = args.workload or default_workload(world)
+    peak, peak_src = measured_peak_gbs()
 
     n = args.records
-    msa, batch, name = load_workload(n, rank, args.workload)
-    idx = MsaIndex.from_msa(msa, device=local_rank)
+    wl = load_workload(n, rank, workload)
+    batch, mates = wl.batch, wl.mates
+    idx = MsaIndex.from_rows(*wl.index_inputs, device=local_rank)
     ctx = idx.ctx
     ctx.set_params(0, -1)                      # project_alignments defaults -g 0 -e -1
     stream = torch.cuda.Stream(device=dev)
-    ctx.set_stream(stream.cuda_stream)
 
     def barrier():
         if world > 1:
@@ -341,174 +496,228 @@ def run_gpu_arm(args) -> None:
         torch.cuda.synchronize(dev)
 
     # ---- value: inputs resident in HBM ----------------------------------------------------------------------------
-    dbatch = DeviceBatch(batch, dev)
-    dout = project_device(ctx, dbatch)          # sizes the output arenas (and is warm-up step 0)
-    for _ in range(args.warmup):
-        project_device(ctx, dbatch, dout)
+    ctx.set_stream(stream.cuda_stream)
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
-    launches0 = ctx.total_launches()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    k1_ms, k3_ms, k4_ms, k1m_ms, n_def = [], [], [], [], []
     with torch.cuda.stream(stream):
-        e0.record(stream)
-        for _ in range(args.steps):
-            project_device(ctx, dbatch, dout)
-            t = ctx.timing()
-            k1_ms.append(t["ms_rewrite"]); k3_ms.append(t["ms_realign"]); k4_ms.append(t["ms_splice"])
-            k1m_ms.append(t["ms_rewrite_main"]); n_def.append(t["n_deferred"])
-        e1.record(stream)
+        leg = device_leg(ctx, dev, stream, wl, batch, mates, args.steps, args.warmup, peak)
     barrier()
-    dev_ms = e0.elapsed_time(e1)
-    gpu_launches = ctx.total_launches() - launches0
-    stats = dict(dout.stats)
+    dev_ms = leg["ms_total"]
+    gpu_launches = leg["launches"]
+    stats = leg["stats"]
 
-    # ---- e2e: pinned host buffers through pv3_project, H2D and D2H inside the timed region -------------------------
-    ctx.set_stream(None)                       # the library's own two streams: chunked H2D / kernels / D2H overlap
-    lib = ctx.lib
-    pin_in = PinnedArena(lib, batch.input_bytes() + 16 * 4096)
-    from panvc3_b200.batch import RecordBatch
-    kw = {}
-    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual"):
-        a = getattr(batch, k)
-        if a is None:
-            continue
-        p = pin_in.take(a.shape, a.dtype); p[...] = a; kw[k] = p
-    pbatch = RecordBatch.__new__(RecordBatch)
-    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual"):
-        setattr(pbatch, k, kw.get(k))
-    cig_cap, rr_cap = stats["cig_used"] + 4096, stats["rr_used"] + 1024
-    pin_out = PinnedArena(lib, n * 36 + cig_cap * 4 + rr_cap * 32 + 16 * 4096)
-    pout = alloc_output(n, cig_cap, rr_cap, pin_out)
+    # ---- e2e: pinned host buffers through pv3_project; H2D, kernels and the ordered write-back inside the timed region -----
+    ctx.set_stream(None)                       # the library's own two streams: chunked H2D / kernels / write-back overlap
+    cig_cap, rr_cap = stats["cig_used"] + stats["cig_used"] // 8 + 4096, stats["rr_used"] + stats["rr_used"] // 8 + 1024
+    seg = None
+    out_alloc = None
+    if world > 1:
+        seg, whole, mine, out_alloc, per_rank = shared_output_views(n, cig_cap, rr_cap, world, rank, dist, ctx.lib)
+    hb = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=True, packed=True, out_view=out_alloc)
     for _ in range(max(args.warmup, 1)):
-        pout = ctx.project(pbatch, pout)
+        hb.run(ctx)
     barrier()
     t0 = time.perf_counter()
     h2d_ms, d2h_ms = [], []
     for _ in range(args.steps):
-        pout = ctx.project(pbatch, pout)
+        res = hb.run(ctx)
         t = ctx.timing(); h2d_ms.append(t["ms_h2d"]); d2h_ms.append(t["ms_d2h"])
-    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()                          # every shard of every step is in the writer's memory
     e2e_s = time.perf_counter() - t0
+    e2e_stats = dict(res.stats)
     barrier()
     clocks = sampler.stop()
 
-    # ---- the same with SEQ as a BAM file holds it (4-bit packed, pv3_batch_in.seq_len): half the SEQ bytes over PCIe -----
-    bam4_s, bam4_bytes = None, None
-    if not args.no_bam4_leg:
-        packed = batch.to_bam4()
-        pin_in4 = PinnedArena(lib, packed.input_bytes() + 16 * 4096)
-        p4 = RecordBatch.__new__(RecordBatch)
-        for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
-            a = getattr(packed, k)
-            if a is not None:
-                q = pin_in4.take(a.shape, a.dtype); q[...] = a; a = q
-            setattr(p4, k, a)
-        pin_out4 = PinnedArena(lib, n * 36 + cig_cap * 4 + rr_cap * 32 + 16 * 4096)
-        pout4 = alloc_output(n, cig_cap, rr_cap, pin_out4)
-        for _ in range(max(args.warmup, 1)):
-            pout4 = ctx.project(p4, pout4)
-        assert np.array_equal(pout4.dst_pos, pout.dst_pos) and pout4.stats["cig_used"] == pout.stats["cig_used"]
+    # ---- the same call with the wide encoding of round 1 (u32 ids, u64 offsets, byte SEQ, 36-byte records out) ---------------
+    wide_s, wide = None, None
+    if not args.no_wide_leg:
+        wide = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=False, packed=False)
+        for _ in range(2):
+            wide.run(ctx)
         barrier()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            pout4 = ctx.project(p4, pout4)
+        k = max(2, args.steps // 2)
+        for _ in range(k):
+            wres = wide.run(ctx)
         torch.cuda.synchronize(dev)
-        bam4_s = time.perf_counter() - t0
+        wide_s = (time.perf_counter() - t0) / k
         barrier()
-        bam4_bytes = int(packed.input_bytes() - (packed.qual.nbytes if packed.qual_off is not None else 0) + 0)
-    d2h_bytes = n * 36 + pout.stats["cig_used"] * 4 + pout.stats["rr_used"] * 32
-    rr_all = pout.rr[:pout.stats["rr_used"]]
-    lazy_qual_bytes = int(rr_all[:, 3].sum()) if (batch.qual_off is not None and pout.stats["rr_used"] * 16 <= n) else (batch.qual.nbytes if batch.qual_off is not None else 0)
 
     # ---- max over ranks ---------------------------------------------------------------------------------------------
-    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches), (bam4_s or 0.0) * 1e3], dtype=torch.float64, device=dev)
+    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches), (wide_s or 0.0) * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_ms_max, bam4_ms_max = float(times[0]), float(times[1]), float(times[3])
+    dev_ms_max, e2e_ms_max, wide_ms_max = float(times[0]), float(times[1]), float(times[3])
 
-    # ---- ordered gather over NVLink (N>1): results of one step to rank 0 in input order, timed separately -----------
-    gather_ms = None
-    if world > 1:
+    # ---- A/B: the ordered gather over NVLink (NCCL) that round 1 used, timed on its own -------------------------------------
+    gather = None
+    if world > 1 and not args.no_nccl_gather:
         from panvc3_b200.gather import gather_ordered
+        dout = leg["out"]
         local = dict(dst_pos=dout.dst_pos[:n], flags=dout.flags[:n], cig_off=dout.cig_off[:n], cig_len=dout.cig_len[:n],
                      rr_off=dout.rr_off[:n], rr_len=dout.rr_len[:n], cig=dout.cig[:stats["cig_used"]], rr=dout.rr[:4 * stats["rr_used"]])
-        gather_ordered(local, device=dev)       # warm-up (NCCL channel setup, pinned staging buffers)
         gather_ordered(local, device=dev)
         barrier()
-        g0, g1, g2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        g0, g1 = torch_events()
         g0.record()
-        gather_ordered(local, device=dev, to_host=False)     # collectives + device-side merge only
+        merged = gather_ordered(local, device=dev)
         g1.record()
-        merged = gather_ordered(local, device=dev)            # … and the writer's copy in pinned host memory
-        g2.record()
         barrier()
-        gt = torch.tensor([g1.elapsed_time(g2), g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
+        gt = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device=dev)
         dist.all_reduce(gt, op=dist.ReduceOp.MAX)
-        gather_ms, gather_dev_ms = float(gt[0]), float(gt[1])
+        gather = {"ms": float(gt[0]), "backend": "nccl",
+                  "what": "A/B against the in-place shared buffer: one step's device-resident results of all ranks to rank 0 over NVLink, then through rank 0's PCIe link into pinned memory"}
+
+    # ---- parity of the ordered output against the oracle, every shard ---------------------------------------------------------
+    parity = None
+    if not args.no_parity_check:
+        if world > 1:
+            dist.barrier()
         if rank == 0:
-            assert merged.n == n * world
+            def fetch(r):
+                if world == 1:
+                    return hb.as_projected(n)
+                # rank r's slice of the shared segment, same layout as rank 0's (same allocation order and sizes)
+                base = whole[r * per_rank:(r + 1) * per_rank]
+                cur = [0]
+
+                def alloc(shape, dt):
+                    dt = np.dtype(dt); nb = int(np.prod(shape)) * dt.itemsize
+                    o = (cur[0] + 255) // 256 * 256; cur[0] = o + nb
+                    return base[o:o + nb].view(dt).reshape(shape)
+                view = HostBuffers.__new__(HostBuffers)
+                view.compact = True
+                view.narrow = dict(dst_pos32=alloc((n,), np.uint32), flags8=alloc((n,), np.uint8), cig_len16=alloc((n,), np.uint16), rr_len8=alloc((n,), np.uint8))
+                if mates is not None:
+                    view.narrow["mate_dst_pos32"] = alloc((n,), np.uint32)
+                from panvc3_b200.batch import ProjectedBatch
+                z = np.zeros(1, np.uint64)
+                view.out = ProjectedBatch(dst_pos=z, flags=z.view(np.uint32)[:1], cig_off=z, cig_len=z.view(np.uint32)[:1], cig=alloc((cig_cap,), np.uint32),
+                                          rr_off=z, rr_len=z.view(np.uint32)[:1], rr=alloc((rr_cap, 4), np.uint64))
+                return view.as_projected(n)
+            parity = parity_check(wl, world, n, fetch, mates is not None)
+        if world > 1:
+            dist.barrier()
 
     if rank == 0:
         total_records = n * world * args.steps
         value = total_records / (dev_ms_max * 1e-3)
         e2e_value = total_records / (e2e_ms_max * 1e-3)
-        dp_window_bytes = 0
-        ab = algorithmic_bytes(msa, batch, int(dout.cig_len[:n].sum().item()), stats["rr_used"], dp_window_bytes)
-        peak, peak_src = measured_peak_gbs()
-        k1 = statistics.mean(k1m_ms)          # the dominant kernel alone (k1_thread_kernel), CUDA events on its stream
-        roofline_kernel = "k1_thread_kernel"
-        if int(max(n_def)) * 2 > n:
-            # most records exceed the thread kernel's quotas (long reads): the work is done by the warp-per-record kernel
-            # that follows it, so the roofline is taken over both launches
-            k1 = statistics.mean(k1_ms)
-            roofline_kernel = "k1_thread_kernel + k1_rewrite_kernel (most records deferred to the warp-per-record kernel)"
-        achieved = ab["strict"] / (k1 * 1e-3) / 1e9
-        traffic, traffic_src = measured_traffic_bytes() if args.workload == "config2" else (None, None)
+        rf = leg["roofline"]
+        traffic, traffic_src = measured_traffic_bytes(workload)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": name, "records_per_gpu_per_step": n, "read_len": int(batch.seq.size // max(n, 1)), "gap_open": 0, "gap_ext": -1,
+            "config": {"workload": wl.name, "records_per_gpu_per_step": n, "read_len": READ_LEN, "gap_open": 0, "gap_ext": -1,
+                       "rows": len(wl.index_inputs[0]), "paired": mates is not None,
                        "l2_policy": f"inputs larger than L2: {batch.input_bytes() / 1e6:.0f} MB of input per step per GPU vs 126 MB L2",
                        "parallelism": f"{world} independent contiguous shards, index replicated per GPU, no data-path collective",
                        "realigned_runs_per_step": stats["rr_used"], "dp_cells_per_step": stats["dp_cells"],
                        "flagged_records": stats["n_flagged"]},
-            "roofline": {"bound": "hbm", "kernel": roofline_kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": ab["strict"], "bytes_per_record": ab["strict"] / n,
-                         "bytes_per_record_survey_formula": ab["survey"] / n, "kernel_ms": k1,
-                         "frac_survey_formula": ab["survey"] / (k1 * 1e-3) / 1e9 / peak},
-            "kernels_ms": {"rewrite": statistics.mean(k1_ms), "rewrite_thread_kernel_alone": statistics.mean(k1m_ms), "deferred_records": int(max(n_def)), "realign": statistics.mean(k3_ms), "splice": statistics.mean(k4_ms)},
-            "realign_gcups": (stats["dp_cells"] / (statistics.mean(k3_ms) * 1e-3) / 1e9) if statistics.mean(k3_ms) > 0 else None,
-            "e2e": {"value": e2e_value, "unit": UNIT,
-                    "h2d_bytes_per_step": int(batch.input_bytes() - (batch.qual.nbytes if batch.qual_off is not None else 0) + lazy_qual_bytes),
-                    "d2h_bytes_per_step": int(d2h_bytes),
-                    "h2d_note": "QUAL is uploaded lazily: only the query windows of realigned runs cross PCIe (bulk upload when > 1/16 of the records realign)",
-                    "ms_per_step": e2e_ms_max / args.steps, "h2d_ms": statistics.mean(h2d_ms), "d2h_ms": statistics.mean(d2h_ms),
-                    "timer": "host perf_counter around K pv3_project calls, synchronized both sides, max over ranks",
+            "roofline": {"bound": "hbm", "kernel": rf["kernel"], "achieved": rf["achieved"], "peak": peak, "unit": "GB/s",
+                         "frac": rf["frac"], "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": rf["algorithmic_bytes_per_launch"], "bytes_per_record": rf["bytes_per_record"],
+                         "bytes_per_record_survey_formula": rf["bytes_per_record_survey_formula"], "kernel_ms": rf["kernel_ms"],
+                         "frac_survey_formula": rf["frac_survey_formula"],
+                         "note": "the kernel is issue/latency-bound, not DRAM-bound (ncu: DRAM traffic below the algorithmic bytes); frac is reported against the HBM roofline as the task defines it"},
+            "kernels_ms": leg["kernels_ms"],
+            "realign_gcups": (stats["dp_cells"] / (leg["kernels_ms"]["realign"] * 1e-3) / 1e9) if leg["kernels_ms"]["realign"] > 0 else None,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(hb.h2d_bytes), "d2h_bytes_per_step": hb.d2h_bytes(e2e_stats),
+                    "encoding": "compact input (u16 ids, u32 positions, lengths instead of offsets, BAM 4-bit SEQ) and narrow ordered output written in place by the last kernel of every chunk; QUAL read in place from pinned memory, only where a run is realigned",
+                    "ordered_output": ("every rank writes its shard into its slice of ONE shared pinned buffer (POSIX shared memory + pv3_host_register); the timed region ends when all shards of all steps are there"
+                                       if world > 1 else "records in input order in the caller's pinned arrays"),
+                    "ms_per_step": e2e_ms_max / args.steps, "h2d_ms": statistics.mean(h2d_ms), "writeback_ms": statistics.mean(d2h_ms),
+                    "timer": "host perf_counter around K pv3_project calls (+ a barrier for N > 1), synchronized both sides, max over ranks",
                     "numa_binding": numa_note},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
         }
-        if bam4_s is not None:
-            line["e2e_bam4_seq"] = {"value": total_records / (bam4_ms_max * 1e-3), "unit": UNIT, "ms_per_step": bam4_ms_max / args.steps,
-                                    "h2d_bytes_per_step": bam4_bytes + lazy_qual_bytes, "d2h_bytes_per_step": int(d2h_bytes),
-                                    "what": "same records, same call, SEQ passed 4-bit packed as a BAM file stores it (pv3_batch_in.seq_len); results checked equal to the e2e run's"}
-        if gather_ms is not None:
-            line["ordered_gather"] = {"ms": gather_ms, "ms_device_only": gather_dev_ms, "backend": "nccl",
-                                      "what": "one step's results of all ranks to rank 0 in input order (ms: into the writer's pinned host memory; ms_device_only: collectives + merge on the GPU)"}
-        if world == 1 and not args.no_dp_leg and args.workload == "config2":
-            ctx.set_stream(stream.cuda_stream)
-            line["coordinate_sorted_input"] = sorted_input_leg(ctx, dev, stream, msa, batch, args.steps, peak)
-            ctx.set_stream(None)
-            line["realign_dp"] = realign_dp_leg(ctx, dev, 250_000, 3)
+        if wide_s is not None:
+            line["e2e_wide_encoding"] = {"value": n * world / (wide_ms_max * 1e-3), "unit": UNIT, "ms_per_step": wide_ms_max,
+                                         "h2d_bytes_per_step": int(wide.h2d_bytes), "d2h_bytes_per_step": wide.d2h_bytes(dict(wres.stats)),
+                                         "what": "same records, same call, round 1's encoding (u32 ids, u64 offsets and positions, one byte per base, 36-byte records out)"}
+        if gather is not None:
+            line["ordered_gather_nccl"] = gather
+        if parity is not None:
+            line["parity_checked"] = parity["parity_checked"]
+            line["parity"] = parity
+        if world == 1 and workload == "config2":
+            if not args.no_dp_leg:
+                ctx.set_stream(stream.cuda_stream)
+                with torch.cuda.stream(stream):
+                    sb = batch.coordinate_sorted()
+                    sl = device_leg(ctx, dev, stream, wl, sb, None, args.steps, 3, peak)
+                line["coordinate_sorted_input"] = {"value": sb.n / (sl["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": sl["ms_per_step"],
+                                                   "k1_thread_kernel_ms": sl["roofline"]["kernel_ms"], "roofline_frac": sl["roofline"]["frac"],
+                                                   "what": "same records sorted by (source row, position) as `samtools sort` leaves them for project_alignments in test-workflow/Snakefile; the headline `value` keeps the random order"}
+                del sl
+                ctx.set_stream(None)
+                line["realign_dp"] = realign_dp_leg(dev, 250_000, 3)
+            if not args.no_chr_leg:
+                line["chr_scale"] = chr_scale_leg(dev, stream, args, peak)
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(msa, batch)
+            line["cpu_baseline"] = cpu_baseline(wl, batch)
         emit(line)
     if world > 1:
+        dist.barrier()
+        if seg is not None:
+            try:
+                ctx.lib.pv3_host_unregister(mine.ctypes.data)
+            except Exception:
+                pass
+            del hb, whole, mine
+            try:
+                seg.close()
+                if rank == 0:
+                    seg.unlink()
+            except Exception:
+                pass
         dist.destroy_process_group()
+
+
+def realign_dp_leg(dev, n: int, steps: int) -> dict:
+    """Realignment throughput on the DP-bound shape (configs[3]-style indel-heavy reads, scaled): GCUPS over the DP kernels."""
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.projector import MsaIndex
+    wl = load_workload(n, 0, "indel")
+    idx = MsaIndex.from_rows(*wl.index_inputs, device=dev.index)
+    c = idx.ctx
+    c.set_params(0, -1)
+    db = DeviceBatch(wl.batch, dev)
+    out = project_device(c, db)
+    for _ in range(2):
+        project_device(c, db, out)
+    ms = []
+    for _ in range(steps):
+        project_device(c, db, out)
+        ms.append(c.timing()["ms_realign"])
+    st = dict(out.stats)
+    t = statistics.mean(ms)
+    return {"workload": wl.name, "records": n, "runs": st["rr_used"], "dp_cells": st["dp_cells"], "ms_dp_kernels": t,
+            "gcups": st["dp_cells"] / (t * 1e-3) / 1e9 if t > 0 else None,
+            "note": "runs here are a few bases wide (mean 17 cells): the figure is bounded by per-run overhead, not by cell updates"}
+
+
+def chr_scale_leg(dev, stream, args, peak: float) -> dict:
+    """configs[2]'s index and paired reads on this one GPU (the workload every rank runs at N >= 2)."""
+    import torch
+    from panvc3_b200.projector import MsaIndex
+    n = min(args.records, 1_000_000)
+    wl = load_workload(n, 0, "chr26")
+    idx = MsaIndex.from_rows(*wl.index_inputs, device=dev.index)
+    c = idx.ctx
+    c.set_params(0, -1)
+    c.set_stream(stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        leg = device_leg(c, dev, stream, wl, wl.batch, wl.mates, max(3, args.steps // 2), 3, peak)
+    c.set_stream(None)
+    rf = leg["roofline"]
+    return {"workload": wl.name, "rows": len(wl.index_inputs[0]), "records": n, "value": n / (leg["ms_per_step"] * 1e-3), "unit": UNIT,
+            "ms_per_step": leg["ms_per_step"], "kernels_ms": leg["kernels_ms"],
+            "roofline": {"kernel": rf["kernel"], "kernel_ms": rf["kernel_ms"], "frac": rf["frac"], "bytes_per_record": rf["bytes_per_record"], "frac_survey_formula": rf["frac_survey_formula"]}}
 
 
 _RESULT_FD = None
@@ -538,12 +747,18 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config2", choices=["config2", "indel", "chr", "long"])
+    ap.add_argument("--workload", default=None, choices=["config2", "indel", "chr26", "chr", "long"],
+                    help="default: config2 (configs[1]) on one GPU, chr26 (configs[2]) on several")
     ap.add_argument("--records", type=int, default=RECORDS_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-bam4-leg", action="store_true", help="skip the e2e leg with 4-bit packed SEQ input")
-    ap.add_argument("--no-dp-leg", action="store_true", help="skip the realignment-throughput leg on the indel-heavy shape")
+    ap.add_argument("--no-wide-leg", action="store_true", help="skip the e2e leg with round 1's wide encoding")
+    ap.add_argument("--no-dp-leg", action="store_true", help="skip the sorted-input and realignment-throughput legs")
+    ap.add_argument("--no-chr-leg", action="store_true", help="skip the chromosome-scale leg of the one-GPU run")
+    ap.add_argument("--no-nccl-gather", action="store_true", help="skip the A/B leg of the NCCL ordered gather (N > 1)")
+    ap.add_argument("--no-parity-check", action="store_true")
     args = ap.parse_args()
+    if args.workload == "chr":
+        args.workload = "chr26"
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         run_reference_arm(args)

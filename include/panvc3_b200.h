@@ -8,8 +8,11 @@
  * detection, realignment of the flagged runs and splice/collapse — bit-exact with the reference CPU code.
  *
  * Plain C, plain pointers and sizes; no CUDA or torch types.  All functions return PV3_OK (0) or a negative
- * pv3_status; pv3_last_error() gives the message.  A context is single-submitter (one host thread at a time), owns
- * one CUDA stream and all device memory, and is bound to one device (one context per GPU / per process rank).
+ * pv3_status; pv3_last_error() gives the message.  THREADING: a context is single-submitter — calls on one context must
+ * not overlap (no internal locking; its index tables, parameters, work buffers and streams are unsynchronised state).
+ * Give every submitting thread its own context (the index is small next to 180 GB of HBM), or serialise the calls. A
+ * context owns its CUDA streams and all device memory and is bound to one device (one context per GPU / per process
+ * rank); pv3_multi below drives several contexts — one per GPU — from one thread with results in submission order.
  *
  * Encodings (what the reference's in-memory types already hold, so the adapter can memcpy):
  *   seq   one byte per base, seqan3::dna5 rank  A=0 C=1 G=2 N=3 T=4     (lib/seqan3/.../nucleotide/dna5.hpp:95-110)
@@ -29,7 +32,7 @@
 extern "C" {
 #endif
 
-#define PV3_ABI_VERSION 4
+#define PV3_ABI_VERSION 5
 
 typedef struct pv3_ctx pv3_ctx;
 
@@ -75,6 +78,22 @@ typedef struct {
 	                              then counts BYTES and seq_len[i] is the record's number of bases. Codes other than A C G T are
 	                              read as N, as seqan3 does when it reads a BAM SEQ into dna5 (no unpacking on
 	                              the host, half the bytes over PCIe). */
+	/* -- ABI 5 (all optional; zero-initialise the struct) ------------------------------------------------------------- */
+	const uint32_t *mate_row;  /* [n] row id of the sequence the MATE was aligned to (RNEXT); its position is projected to
+	                              dst_row with sequence_entry::project_position (project_alignments.cc:880-906). NULL: no mates */
+	const uint64_t *mate_pos;  /* [n] */
+	/* Compact encoding (pv3_project only, compact != 0): the arrays below are what crosses PCIe instead of src_row,
+	 * dst_row, dst_ref, src_pos, seq_off, cig_off, qual_off, mate_row, mate_pos (u16 ids, u32 positions, lengths instead of
+	 * offsets: 16 B per record instead of 52). seq / cig / qual hold the records back to back in record order; seq_len
+	 * counts bases (SEQ is BAM 4-bit packed iff seq_bam4); QUAL, where present (bit i of has_qual), is as long as SEQ.
+	 * seq_off, cig_off and qual_off must still be valid ON THE HOST (the call cuts the batch into chunks with them; a
+	 * packer has them as running totals anyway) but are not uploaded. */
+	int             compact;
+	int             seq_bam4;
+	const uint16_t *src_row16, *dst_row16, *dst_ref16, *mate_row16;
+	const uint32_t *src_pos32, *mate_pos32;
+	const uint16_t *cig_len16;
+	const uint8_t  *has_qual;  /* bit i & 7 of byte i / 8; NULL: no record has QUAL */
 } pv3_batch_in;
 
 /* Output batch. CIGARs and realigned ranges live in arenas and are addressed per record by (off, len); arena order
@@ -98,6 +117,18 @@ typedef struct {
 	uint64_t  n_flagged;       /* records with flags != 0 */
 	uint64_t  n_realigned;     /* records with at least one realigned run */
 	uint64_t  dp_cells;        /* sum over runs of ref_length * query_length (GCUPS numerator) */
+	/* -- ABI 5 (all optional; zero-initialise the struct) ------------------------------------------------------------- */
+	uint64_t *mate_dst_pos;    /* [n] projected mate positions (pv3_batch_in.mate_row set) */
+	/* pv3_project writes the arenas in RECORD ORDER: cig_off[i + 1] == cig_off[i] + cig_len[i], likewise rr. Offsets are
+	 * therefore redundant: cig_off, rr_off, flags, rr_len may be NULL (not written), and each of the narrow arrays below,
+	 * when non-NULL, is written INSTEAD of its wide twin (39 B per 150-bp record over PCIe instead of 67). A value that
+	 * does not fit its narrow field fails the call with PV3_ERR_CAPACITY (retry with the wide field).
+	 * pv3_project_device keeps arena order (one atomic allocation per tile) and ignores these. */
+	uint32_t *dst_pos32;
+	uint8_t  *flags8;
+	uint16_t *cig_len16;
+	uint8_t  *rr_len8;
+	uint32_t *mate_dst_pos32;
 } pv3_batch_out;
 
 /* Device-side durations of the last pv3_project or pv3_project_device call, from CUDA events on the context's stream. */
@@ -126,8 +157,12 @@ int         pv3_set_stream(pv3_ctx *, void *cuda_stream);
 /* -- index (replaces msa_index::sequence_entry over sdsl::rrr_vector<15>, include/panvc3/msa_index.hh:47-74) --------- */
 int pv3_index_add_row(pv3_ctx *, const uint64_t *gap_words, uint64_t n_bits);  /* returns row id >= 0 */
 int pv3_index_add_ref(pv3_ctx *, const char *bases, uint64_t n);               /* returns contig id >= 0 */
-int pv3_index_commit(pv3_ctx *);                /* builds rank/select directories and uploads. Rows/contigs may still be added
-                                                   afterwards (ids are stable); the next commit uploads the whole index again */
+int pv3_index_commit(pv3_ctx *);                /* builds rank/select directories and uploads what was added since the last
+                                                   commit (every row and contig has its own device allocation; the host copies
+                                                   are dropped). Rows/contigs may still be added afterwards, ids are stable */
+int pv3_index_remove_ref(pv3_ctx *, int ref_id);/* frees a contig's device memory; the id is reused by a later pv3_index_add_ref
+                                                   (sequence_buffer_store recycles contig buffers the same way,
+                                                   project_alignments.cc:330-380). Records must no longer refer to it */
 
 /* -- parameters (project_alignments -g / -e; defaults 0 / -1, project-alignments/cmdline.ggo) ------------------------ */
 int pv3_set_params(pv3_ctx *, int32_t gap_open, int32_t gap_ext);
@@ -135,7 +170,10 @@ int pv3_set_quality_lut(pv3_ctx *, const int32_t *lut84);   /* optional override
 int pv3_get_quality_lut(const pv3_ctx *, int32_t *lut84);
 
 /* -- the hot path -------------------------------------------------------------------------------------------------- */
-/* Host buffers in and out (pinned or pageable); H2D copies, kernels and D2H copies all happen inside the call. */
+/* Host buffers in and out; H2D copies, kernels and the write-back all happen inside the call, which synchronises ONCE,
+ * at its end. Use pinned memory (pv3_host_alloc / pv3_host_register): results are then written straight into the
+ * caller's arrays by the last kernel of every chunk and QUAL is read in place, only where a run is realigned. Pageable
+ * memory works (staged copies, one synchronisation per chunk, QUAL uploaded in full) but is slower. */
 int pv3_project(pv3_ctx *, const pv3_batch_in *in, pv3_batch_out *out);
 /* Every pointer inside *in and *out is a DEVICE pointer on the context's device (the structs themselves are host). */
 int pv3_project_device(pv3_ctx *, const pv3_batch_in *in, pv3_batch_out *out);
@@ -143,6 +181,9 @@ int pv3_project_device(pv3_ctx *, const pv3_batch_in *in, pv3_batch_out *out);
  * project_alignments.cc:880-906). Host buffers. */
 int pv3_project_positions(pv3_ctx *, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint64_t *pos,
                           uint64_t *out_pos);
+/* The same with device pointers, asynchronous on the context's stream. */
+int pv3_project_positions_device(pv3_ctx *, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint64_t *pos,
+                                 uint64_t *out_pos);
 /* Raw index queries for parity tests: op 0 = rank0(row,x) zeros in [0,x); 1 = select0(row,x) (x >= 1); 2 = access. */
 int pv3_index_query(pv3_ctx *, int op, uint64_t n, const uint32_t *row, const uint64_t *x, uint64_t *out);
 
@@ -164,6 +205,23 @@ uint64_t pv3_total_launches(const pv3_ctx *);
 /* -- pinned host memory for batches --------------------------------------------------------------------------------- */
 void *pv3_host_alloc(size_t bytes);
 void  pv3_host_free(void *);
+/* Pins (page-locks and maps) memory the caller allocated itself — e.g. a POSIX shared-memory segment into which several
+ * ranks write their shards of one ordered output. */
+int   pv3_host_register(void *p, size_t bytes);
+int   pv3_host_unregister(void *p);
+
+/* -- several GPUs behind one submitter --------------------------------------------------------------------------------
+ * One context per device, the index replicated; pv3_multi_project cuts the batch into contiguous shards (record order is
+ * kept by construction: shard g holds records [n g / G, n (g + 1) / G)), runs every shard's asynchronous pipeline on its
+ * device from the calling thread and synchronises once. Output is ordered across the whole batch as for pv3_project.
+ * The reference's contract: one submitter, records out in input order (project_alignments.cc:958-970). */
+typedef struct pv3_multi pv3_multi;
+int  pv3_multi_create(pv3_multi **out, int n_devices, const int *devices /* NULL: 0..n-1 */);
+void pv3_multi_destroy(pv3_multi *);
+int  pv3_multi_devices(const pv3_multi *);
+pv3_ctx *pv3_multi_ctx(pv3_multi *, int i);     /* context of device i: add rows / contigs / params to EVERY context */
+int  pv3_multi_project(pv3_multi *, const pv3_batch_in *in, pv3_batch_out *out);
+const char *pv3_multi_last_error(const pv3_multi *);
 
 /* -- record annotation text ------------------------------------------------------------------------------
  * The OA entry project_task::process appends to every projected record (project-alignments/project_alignments.cc:803-845):

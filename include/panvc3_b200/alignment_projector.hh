@@ -12,8 +12,15 @@
  * The class is a template over a small traits type that says how to read the caller's element types, so the same code
  * serves (a) the reference's own types — seqan3::dna5 / phred42 / cigar, panvc3::msa_index::sequence_entry,
  * panvc3::range — through `seqan3_traits` (defined when the seqan3 headers are on the include path), and (b) plain
- * structs in this repository's tests (`plain_traits`).  A call is a batch of one; the batched entry
- * (`project_batch`) is what a pipeline should use.
+ * structs in this repository's tests (`plain_traits`).  A call is a batch of one (three stream operations and a
+ * synchronisation per record: compatibility, not speed); `basic_batch_projector` below is what a pipeline should use:
+ * push_back() packs records into a pinned structure-of-arrays arena, flush() runs them as one pv3_project call, results
+ * are read back in submission order.
+ *
+ * THREADING. A device_index (one pv3_ctx) and everything hanging off it — projectors, batch projectors — belong to ONE
+ * submitting thread at a time; nothing here locks. The reference's should_process_tasks_in_parallel mode runs
+ * project_task::process on a concurrent queue: give every worker thread its own device_index (the index is small next
+ * to HBM) or funnel the records of all workers into one batch_projector owned by one thread.
  *
  * Ownership as in the reference: the caller owns all inputs; the projector owns its output vectors, valid until the
  * next reset()/project_alignment().  The gap rows and target contigs are registered with a `device_index` on first
@@ -121,10 +128,27 @@ namespace panvc3_b200 {
 			return std::uint32_t(id);
 		}
 
-		// Forget a contig buffer that is about to be reused for another contig (sequence_buffer_store recycles buffers).
-		void forget_reference(std::vector <char> const &ref_seq) { m_refs.erase(&ref_seq); }
+		// Forget a contig buffer that is about to be reused for another contig (sequence_buffer_store recycles buffers):
+		// the device copy is freed and its id recycled.
+		void forget_reference(std::vector <char> const &ref_seq)
+		{
+			auto const it(m_refs.find(&ref_seq));
+			if (m_refs.end() == it) return;
+			check(pv3_index_remove_ref(m_ctx, int(it->second)), "pv3_index_remove_ref");
+			m_refs.erase(it);
+		}
 
+		// Uploads what was registered since the last commit (rows and contigs have their own device allocations).
 		void commit() { check(pv3_index_commit(m_ctx), "pv3_index_commit"); }
+
+		void set_params(std::int32_t const gap_opening_cost, std::int32_t const gap_extension_cost)
+		{
+			check(pv3_set_params(m_ctx, gap_opening_cost, gap_extension_cost), "pv3_set_params");
+		}
+
+		int project(pv3_batch_in const &in, pv3_batch_out &out) { return pv3_project(m_ctx, &in, &out); }
+		char const *last_error() const { return pv3_last_error(m_ctx); }
+		static constexpr bool needs_offsets = false;       // pv3_project orders the arenas over the whole batch
 
 		// msa_index::sequence_entry::project_position (msa_index.hh:253-258)
 		std::uint64_t project_position(std::uint32_t const src_row, std::uint32_t const dst_row, std::uint64_t const pos)
@@ -137,6 +161,125 @@ namespace panvc3_b200 {
 	};
 }
 
+
+
+namespace panvc3_b200 {
+
+	// Several GPUs behind one submitter (pv3_multi): every row / contig is registered on every device; a batch is cut into
+	// contiguous shards, one per device, and comes back in submission order. Same interface as device_index.
+	class multi_device_index
+	{
+		pv3_multi											*m_multi{};
+		std::unordered_map <void const *, std::uint32_t>	m_rows;
+		std::unordered_map <void const *, std::uint32_t>	m_refs;
+
+		void check(int const st, char const *what, pv3_ctx *ctx) const
+		{
+			if (st < 0)
+				throw std::runtime_error(std::string(what) + ": " + pv3_last_error(ctx));
+		}
+
+	public:
+		explicit multi_device_index(int const n_devices, int const *devices = nullptr)
+		{
+			if (PV3_OK != pv3_multi_create(&m_multi, n_devices, devices))
+				throw std::runtime_error(std::string("pv3_multi_create: ") + pv3_last_error(nullptr));
+		}
+
+		~multi_device_index() { pv3_multi_destroy(m_multi); }
+		multi_device_index(multi_device_index const &) = delete;
+		multi_device_index &operator=(multi_device_index const &) = delete;
+
+		int devices() const { return pv3_multi_devices(m_multi); }
+		pv3_ctx *context() const { return pv3_multi_ctx(m_multi, 0); }
+
+		std::uint32_t register_row_words(void const *key, std::uint64_t const *words, std::uint64_t const n_bits)
+		{
+			auto const it(m_rows.find(key));
+			if (m_rows.end() != it)
+				return it->second;
+			int id(-1);
+			for (int d(0); d < devices(); ++d)
+			{
+				id = pv3_index_add_row(pv3_multi_ctx(m_multi, d), words, n_bits);
+				check(id, "pv3_index_add_row", pv3_multi_ctx(m_multi, d));
+			}
+			m_rows.emplace(key, std::uint32_t(id));
+			return std::uint32_t(id);
+		}
+
+		std::uint32_t register_reference(std::vector <char> const &ref_seq)
+		{
+			auto const it(m_refs.find(&ref_seq));
+			if (m_refs.end() != it)
+				return it->second;
+			int id(-1);
+			for (int d(0); d < devices(); ++d)
+			{
+				id = pv3_index_add_ref(pv3_multi_ctx(m_multi, d), ref_seq.data(), ref_seq.size());
+				check(id, "pv3_index_add_ref", pv3_multi_ctx(m_multi, d));
+			}
+			m_refs.emplace(&ref_seq, std::uint32_t(id));
+			return std::uint32_t(id);
+		}
+
+		void forget_reference(std::vector <char> const &ref_seq)
+		{
+			auto const it(m_refs.find(&ref_seq));
+			if (m_refs.end() == it) return;
+			for (int d(0); d < devices(); ++d)
+				check(pv3_index_remove_ref(pv3_multi_ctx(m_multi, d), int(it->second)), "pv3_index_remove_ref", pv3_multi_ctx(m_multi, d));
+			m_refs.erase(it);
+		}
+
+		void commit() { for (int d(0); d < devices(); ++d) check(pv3_index_commit(pv3_multi_ctx(m_multi, d)), "pv3_index_commit", pv3_multi_ctx(m_multi, d)); }
+
+		void set_params(std::int32_t const gap_opening_cost, std::int32_t const gap_extension_cost)
+		{
+			for (int d(0); d < devices(); ++d) check(pv3_set_params(pv3_multi_ctx(m_multi, d), gap_opening_cost, gap_extension_cost), "pv3_set_params", pv3_multi_ctx(m_multi, d));
+		}
+
+		int project(pv3_batch_in const &in, pv3_batch_out &out) { return pv3_multi_project(m_multi, &in, &out); }
+		char const *last_error() const { return pv3_multi_last_error(m_multi); }
+		static constexpr bool needs_offsets = true;        // arenas are ordered inside every device's shard: offsets are absolute
+	};
+
+
+	// Pinned, growing array (pv3_host_alloc): the arena the batch projector packs into.
+	template <typename t_value>
+	class pinned_vector
+	{
+		t_value		*m_data{};
+		std::size_t	m_size{}, m_cap{};
+
+	public:
+		pinned_vector() = default;
+		pinned_vector(pinned_vector const &) = delete;
+		pinned_vector &operator=(pinned_vector const &) = delete;
+		~pinned_vector() { pv3_host_free(m_data); }
+
+		void reserve(std::size_t const n)
+		{
+			if (n <= m_cap) return;
+			std::size_t const cap(n + n / 2 + 64);
+			auto *p(static_cast <t_value *>(pv3_host_alloc(cap * sizeof(t_value))));
+			if (!p) throw std::bad_alloc();
+			for (std::size_t i(0); i < m_size; ++i) p[i] = m_data[i];
+			pv3_host_free(m_data);
+			m_data = p; m_cap = cap;
+		}
+
+		void resize(std::size_t const n) { reserve(n); m_size = n; }
+		void push_back(t_value const v) { if (m_size == m_cap) reserve(m_size + 1); m_data[m_size++] = v; }
+		t_value *append(std::size_t const n) { reserve(m_size + n); t_value *p(m_data + m_size); m_size += n; return p; }
+		void clear() { m_size = 0; }
+		std::size_t size() const { return m_size; }
+		t_value *data() { return m_data; }
+		t_value const *data() const { return m_data; }
+		t_value &operator[](std::size_t const i) { return m_data[i]; }
+		t_value const &operator[](std::size_t const i) const { return m_data[i]; }
+	};
+}
 
 
 namespace panvc3_b200 {
@@ -160,6 +303,14 @@ namespace panvc3_b200 {
 
 		static std::uint64_t n_bits(sequence_entry_type const &e) { return e.gap_positions.size(); }
 		static bool gap_bit(sequence_entry_type const &e, std::uint64_t const i) { return e.gap_positions[i]; }
+		// 64 gap bits from column 64 w (LSB first), fewer at the end of the row
+		static std::uint64_t gap_word(sequence_entry_type const &e, std::uint64_t const w)
+		{
+			std::uint64_t v(0);
+			std::uint64_t const n(e.gap_positions.size());
+			for (std::uint64_t i(64 * w); i < n && i < 64 * w + 64; ++i) if (e.gap_positions[i]) v |= std::uint64_t(1) << (i - 64 * w);
+			return v;
+		}
 		static std::uint8_t seq_rank(sequence_alphabet const x) { return x; }
 		static std::uint8_t qual_rank(quality_alphabet const x) { return x; }
 		static std::uint32_t cigar_count(cigar_type const &c) { return c.count; }
@@ -170,6 +321,16 @@ namespace panvc3_b200 {
 
 
 	template <typename t_traits> class basic_alignment_projector; // Fwd.
+
+	// Registers a sequence entry's gap row word by word (64 columns per traits call).
+	template <typename t_traits, typename t_index>
+	std::uint32_t register_entry_words(t_index &index, typename t_traits::sequence_entry_type const &entry)
+	{
+		std::uint64_t const n_bits(t_traits::n_bits(entry));
+		std::vector <std::uint64_t> words((n_bits + 63) / 64);
+		for (std::uint64_t w(0); w < words.size(); ++w) words[w] = t_traits::gap_word(entry, w);
+		return index.register_row_words(&entry, words.data(), n_bits);
+	}
 
 	template <typename t_traits>
 	struct basic_alignment_projector_delegate
@@ -224,10 +385,7 @@ namespace panvc3_b200 {
 			m_realigned_query_ranges.clear();
 		}
 
-		std::uint32_t register_entry(sequence_entry_type const &entry)
-		{
-			return m_index->register_row(&entry, t_traits::n_bits(entry), [&entry](std::uint64_t const i){ return t_traits::gap_bit(entry, i); });
-		}
+		std::uint32_t register_entry(sequence_entry_type const &entry) { return register_entry_words <t_traits>(*m_index, entry); }
 
 		// Same parameter list as panvc3::alignment_projector::project_alignment (alignment_projector.hh:58-68).
 		std::size_t project_alignment(
@@ -316,6 +474,172 @@ namespace panvc3_b200 {
 	};
 
 	typedef basic_alignment_projector <plain_traits> plain_alignment_projector;
+
+
+	// The batched entry of the host pipeline: what fills the reference's 4-record tasks
+	// (project-alignments/project_alignments.cc:597-631) packs records here instead, into ONE pinned structure of arrays in
+	// the compact encoding of pv3_batch_in (16-bit ids, 32-bit positions, lengths; SEQ one dna5 rank per byte as seqan3 holds
+	// it); flush() = one pv3_project (or pv3_multi_project) call; results are read in submission order. Register every
+	// sequence entry and contig (register_entry / register_reference) before the first push_back that uses it.
+	template <typename t_traits, typename t_index = device_index>
+	class basic_batch_projector
+	{
+	public:
+		typedef typename t_traits::sequence_entry_type	sequence_entry_type;
+		typedef typename t_traits::sequence_alphabet	sequence_alphabet;
+		typedef typename t_traits::quality_alphabet		quality_alphabet;
+		typedef typename t_traits::cigar_type			cigar_type;
+		typedef typename t_traits::range_type			range_type;
+
+	protected:
+		t_index							*m_index{};
+		// input, pinned
+		pinned_vector <std::uint16_t>	m_src_row, m_dst_row, m_dst_ref, m_cig_len, m_mate_row;
+		pinned_vector <std::uint32_t>	m_src_pos, m_seq_len, m_cig, m_mate_pos;
+		pinned_vector <std::uint8_t>	m_seq, m_qual, m_has_qual;
+		std::vector <std::uint64_t>		m_seq_off{0}, m_cig_off{0}, m_qual_off{0};     // host only: chunk cuts
+		bool							m_any_qual{}, m_mates{};
+		// output, pinned
+		pinned_vector <std::uint64_t>	m_dst_pos, m_out_cig_off, m_out_rr_off, m_rr, m_mate_dst_pos;
+		pinned_vector <std::uint32_t>	m_flags, m_out_cig_len, m_out_rr_len, m_out_cig;
+		std::size_t						m_flushed{};
+
+		static std::uint32_t bam_op(char const c)
+		{
+			char const ops[] = "MIDNSHP=X";
+			for (std::uint32_t i(0); i < 9; ++i) if (ops[i] == c) return i;
+			return 15;
+		}
+
+	public:
+		explicit basic_batch_projector(t_index &index): m_index(&index) {}
+
+		std::uint32_t register_entry(sequence_entry_type const &entry) { return register_entry_words <t_traits>(*m_index, entry); }
+		std::uint32_t register_reference(std::vector <char> const &ref_seq) { return m_index->register_reference(ref_seq); }
+
+		std::size_t size() const { return m_src_row.size(); }
+
+		void clear()
+		{
+			for (auto *v : { &m_src_row, &m_dst_row, &m_dst_ref, &m_cig_len, &m_mate_row }) v->clear();
+			for (auto *v : { &m_src_pos, &m_seq_len, &m_cig, &m_mate_pos }) v->clear();
+			for (auto *v : { &m_seq, &m_qual, &m_has_qual }) v->clear();
+			m_seq_off.assign(1, 0); m_cig_off.assign(1, 0); m_qual_off.assign(1, 0);
+			m_any_qual = false; m_mates = false; m_flushed = 0;
+		}
+
+		// Arguments as alignment_projector::project_alignment takes them (alignment_projector.hh:58-68), the entries and the
+		// contig by the ids register_entry / register_reference returned; returns the record's index in the batch.
+		std::size_t push_back(
+			std::size_t const src_pos, std::uint32_t const src_row, std::uint32_t const dst_row, std::uint32_t const dst_ref,
+			std::vector <sequence_alphabet> const &query_seq, std::vector <cigar_type> const &cigar_seq,
+			std::vector <quality_alphabet> const &base_qualities)
+		{
+			if (src_row > 0xffff || dst_row > 0xffff || dst_ref > 0xffff || src_pos > 0xffffffffull || cigar_seq.size() > 0xffff)
+				throw std::range_error("batch_projector: value does not fit the compact encoding");
+			if (!base_qualities.empty() && base_qualities.size() != query_seq.size())
+				throw std::invalid_argument("batch_projector: QUAL must be empty or as long as SEQ");
+			std::size_t const i(size());
+			m_src_row.push_back(std::uint16_t(src_row)); m_dst_row.push_back(std::uint16_t(dst_row)); m_dst_ref.push_back(std::uint16_t(dst_ref));
+			m_src_pos.push_back(std::uint32_t(src_pos)); m_seq_len.push_back(std::uint32_t(query_seq.size())); m_cig_len.push_back(std::uint16_t(cigar_seq.size()));
+			std::uint8_t *sp(m_seq.append(query_seq.size()));
+			for (std::size_t k(0); k < query_seq.size(); ++k) sp[k] = t_traits::seq_rank(query_seq[k]);
+			std::uint32_t *cp(m_cig.append(cigar_seq.size()));
+			for (std::size_t k(0); k < cigar_seq.size(); ++k) cp[k] = (t_traits::cigar_count(cigar_seq[k]) << 4) | bam_op(t_traits::cigar_op_char(cigar_seq[k]));
+			if (0 == i % 8) m_has_qual.push_back(0);
+			if (!base_qualities.empty())
+			{
+				m_has_qual[i / 8] = std::uint8_t(m_has_qual[i / 8] | (1u << (i % 8)));
+				std::uint8_t *qp(m_qual.append(base_qualities.size()));
+				for (std::size_t k(0); k < base_qualities.size(); ++k) qp[k] = t_traits::qual_rank(base_qualities[k]);
+				m_any_qual = true;
+			}
+			m_seq_off.push_back(m_seq.size()); m_cig_off.push_back(m_cig.size()); m_qual_off.push_back(m_qual.size());
+			m_mate_row.push_back(0); m_mate_pos.push_back(0);
+			return i;
+		}
+
+		// The mate of the record pushed last: its position is projected from mate_row to the record's dst_row
+		// (sequence_entry::project_position, project_alignments.cc:880-906).
+		void set_mate(std::uint32_t const mate_row, std::size_t const mate_pos)
+		{
+			m_mate_row[size() - 1] = std::uint16_t(mate_row); m_mate_pos[size() - 1] = std::uint32_t(mate_pos); m_mates = true;
+		}
+
+		// Runs every record pushed since the last clear().
+		void flush(std::int32_t const gap_opening_cost, std::int32_t const gap_extension_cost)
+		{
+			std::size_t const n(size());
+			m_flushed = 0;
+			if (!n) return;
+			m_index->commit();
+			m_index->set_params(gap_opening_cost, gap_extension_cost);
+			pv3_batch_in in{};
+			in.n = n; in.compact = 1; in.seq_bam4 = 0;
+			in.src_row16 = m_src_row.data(); in.dst_row16 = m_dst_row.data(); in.dst_ref16 = m_dst_ref.data(); in.src_pos32 = m_src_pos.data();
+			in.seq_len = m_seq_len.data(); in.cig_len16 = m_cig_len.data(); in.has_qual = m_any_qual ? m_has_qual.data() : nullptr;
+			in.seq_off = m_seq_off.data(); in.cig_off = m_cig_off.data(); in.qual_off = m_any_qual ? m_qual_off.data() : nullptr;
+			in.seq = m_seq.data(); in.cig = m_cig.data(); in.qual = m_any_qual ? m_qual.data() : nullptr;
+			if (m_mates) { in.mate_row16 = m_mate_row.data(); in.mate_pos32 = m_mate_pos.data(); }
+			m_dst_pos.resize(n); m_flags.resize(n); m_out_cig_off.resize(n); m_out_cig_len.resize(n); m_out_rr_off.resize(n); m_out_rr_len.resize(n);
+			if (m_mates) m_mate_dst_pos.resize(n);
+			if (m_out_cig.size() < 2 * m_cig.size() + 8 * n) m_out_cig.resize(2 * m_cig.size() + 8 * n);
+			if (m_rr.size() < 4 * (n / 8 + 64)) m_rr.resize(4 * (n / 8 + 64));
+			for (;;)
+			{
+				pv3_batch_out out{};
+				out.dst_pos = m_dst_pos.data(); out.flags = m_flags.data(); out.cig_off = m_out_cig_off.data(); out.cig_len = m_out_cig_len.data();
+				out.cig = m_out_cig.data(); out.cig_cap = m_out_cig.size();
+				out.rr_off = m_out_rr_off.data(); out.rr_len = m_out_rr_len.data(); out.rr = m_rr.data(); out.rr_cap = m_rr.size() / 4;
+				out.mate_dst_pos = m_mates ? m_mate_dst_pos.data() : nullptr;
+				int const st(m_index->project(in, out));
+				if (PV3_ERR_CAPACITY == st)
+				{
+					m_out_cig.resize(2 * out.cig_used + 64);
+					m_rr.resize(4 * (2 * out.rr_used + 8));
+					continue;
+				}
+				if (st < 0) throw std::runtime_error(m_index->last_error());
+				break;
+			}
+			m_flushed = n;
+		}
+
+		// -- results of the last flush(), by submission index -------------------------------------------------------------
+		std::uint32_t flags(std::size_t const i) const { return m_flags[i]; }
+		void throw_if_rejected(std::size_t const i) const { if (m_flags[i]) throw projection_error(m_flags[i], describe_flags(m_flags[i])); }
+		std::size_t position(std::size_t const i) const { return m_dst_pos[i]; }
+		std::size_t mate_position(std::size_t const i) const { return m_mate_dst_pos[i]; }
+		std::size_t realigned_range_count(std::size_t const i) const { return m_out_rr_len[i]; }
+
+		// packed ops (len << 4 | BAM op) of record i: what a BAM writer stores as they are
+		std::pair <std::uint32_t const *, std::size_t> packed_alignment(std::size_t const i) const
+		{
+			return { m_out_cig.data() + m_out_cig_off[i], m_out_cig_len[i] };
+		}
+
+		void alignment(std::size_t const i, std::vector <cigar_type> &dst) const
+		{
+			char const ops[] = "MIDNSHP=X";
+			auto const pa(packed_alignment(i));
+			dst.clear();
+			for (std::size_t k(0); k < pa.second; ++k) dst.push_back(t_traits::make_cigar(pa.first[k] >> 4, ops[pa.first[k] & 0xf]));
+		}
+
+		void realigned_ranges(std::size_t const i, std::vector <range_type> &ref_ranges, std::vector <range_type> &query_ranges) const
+		{
+			ref_ranges.clear(); query_ranges.clear();
+			for (std::uint32_t k(0); k < m_out_rr_len[i]; ++k)                  // alignment_projector.cc:69-73
+			{
+				std::uint64_t const *rr(m_rr.data() + 4 * (m_out_rr_off[i] + k));
+				ref_ranges.push_back(t_traits::make_range(rr[0], rr[1]));
+				query_ranges.push_back(t_traits::make_range(rr[2], rr[3]));
+			}
+		}
+	};
+
+	typedef basic_batch_projector <plain_traits> plain_batch_projector;
+	typedef basic_batch_projector <plain_traits, multi_device_index> plain_multi_batch_projector;
 }
 
 
@@ -340,6 +664,13 @@ namespace panvc3_b200 {
 
 		static std::uint64_t n_bits(sequence_entry_type const &e) { return e.gap_positions.size(); }
 		static bool gap_bit(sequence_entry_type const &e, std::uint64_t const i) { return e.gap_positions[i]; }	// rrr access
+		// One rrr decode per 64 columns instead of one per column (rrr_vector<15>::get_int, rrr_vector_15.hpp:320-360):
+		// registering a 2.7e8-column row costs 4.2e6 decodes, not 2.7e8 block scans.
+		static std::uint64_t gap_word(sequence_entry_type const &e, std::uint64_t const w)
+		{
+			std::uint64_t const n(e.gap_positions.size()), first(64 * w);
+			return e.gap_positions.get_int(first, std::uint8_t(n - first < 64 ? n - first : 64));
+		}
 		static std::uint8_t seq_rank(sequence_alphabet const x) { return x.to_rank(); }
 		static std::uint8_t qual_rank(quality_alphabet const x) { return x.to_rank(); }
 		static std::uint32_t cigar_count(cigar_type const &c) { using seqan3::get; return get <0>(c); }
@@ -356,6 +687,8 @@ namespace panvc3_b200 {
 	// Drop-in names: `using panvc3::alignment_projector = panvc3_b200::alignment_projector` in the reference's build.
 	typedef basic_alignment_projector <seqan3_traits>			alignment_projector;
 	typedef basic_alignment_projector_delegate <seqan3_traits>	alignment_projector_delegate;
+	typedef basic_batch_projector <seqan3_traits>				batch_projector;
+	typedef basic_batch_projector <seqan3_traits, multi_device_index>	multi_batch_projector;
 }
 #endif
 

@@ -179,6 +179,25 @@ class RecordBatch:
             kw["seq_len"] = self.seq_len[begin:end]
         return RecordBatch(**kw)
 
+    @classmethod
+    def concat(cls, parts: Sequence["RecordBatch"]) -> "RecordBatch":
+        """Concatenation in order (offsets rebased)."""
+        def cat_off(name):
+            offs, base = [np.zeros(1, np.uint64)], np.uint64(0)
+            for p in parts:
+                o = getattr(p, name)
+                offs.append(o[1:] + base)
+                base = base + o[-1]
+            return np.concatenate(offs)
+        kw = {k: np.concatenate([getattr(p, k) for p in parts]) for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq", "cig")}
+        kw["seq_off"], kw["cig_off"] = cat_off("seq_off"), cat_off("cig_off")
+        if parts[0].qual_off is not None:
+            kw["qual_off"] = cat_off("qual_off")
+            kw["qual"] = np.concatenate([p.qual for p in parts])
+        if parts[0].seq_len is not None:
+            kw["seq_len"] = np.concatenate([p.seq_len for p in parts])
+        return cls(**kw)
+
     def take(self, order) -> "RecordBatch":
         """The records in the given order (a permutation or any index list), variable-length fields regathered."""
         order = np.asarray(order, dtype=np.int64)
@@ -224,6 +243,28 @@ class RecordBatch:
                            seq=packed, cig_off=self.cig_off, cig=self.cig, qual_off=self.qual_off, qual=self.qual,
                            seq_len=lens.astype(np.uint32))
 
+    def compact_arrays(self, mates=None) -> dict:
+        """The narrow arrays of the compact encoding (pv3_batch_in.compact): what crosses PCIe instead of the u32 ids, u64
+        positions and the three u64 offset arrays."""
+        assert int(self.src_row.max(initial=0)) < 65536 and int(self.dst_ref.max(initial=0)) < 65536 and int(self.src_pos.max(initial=0)) < 2**32
+        n = self.n
+        bases = self.seq_len if self.seq_len is not None else np.diff(self.seq_off).astype(np.uint32)
+        d = dict(src_row16=self.src_row.astype(np.uint16), dst_row16=self.dst_row.astype(np.uint16), dst_ref16=self.dst_ref.astype(np.uint16),
+                 src_pos32=self.src_pos.astype(np.uint32), seq_len=np.ascontiguousarray(bases, dtype=np.uint32),
+                 cig_len16=np.diff(self.cig_off).astype(np.uint16), has_qual=None, mate_row16=None, mate_pos32=None)
+        if self.qual_off is not None:
+            ql = np.diff(self.qual_off)
+            assert np.all((ql == 0) | (ql == bases)), "compact encoding: QUAL is absent or as long as SEQ"
+            d["has_qual"] = np.packbits((ql != 0).astype(np.uint8), bitorder="little")
+        if mates is not None:
+            d["mate_row16"] = np.asarray(mates[0]).astype(np.uint16)
+            d["mate_pos32"] = np.asarray(mates[2] if len(mates) == 3 else mates[1]).astype(np.uint32)
+        return d
+
+    def compact_input_bytes(self, mates: bool = False) -> int:
+        n = self.n
+        return n * (6 + 4 + 4 + 2 + (6 if mates else 0)) + (n + 7) // 8 + self.seq.nbytes + self.cig.nbytes
+
     def input_bytes(self) -> int:
         tot = sum(a.nbytes for a in (self.src_row, self.dst_row, self.dst_ref, self.src_pos, self.seq_off, self.seq, self.cig_off, self.cig))
         if self.seq_len is not None:
@@ -245,6 +286,7 @@ class ProjectedBatch:
     rr_off: np.ndarray
     rr_len: np.ndarray
     rr: np.ndarray = field(default_factory=lambda: np.zeros((0, 4), np.uint64))  # ref_loc, ref_len, qry_loc, qry_len
+    mate_dst_pos: np.ndarray | None = None       # projected mate positions (pv3_batch_in.mate_row given)
 
     @property
     def n(self) -> int:

@@ -24,13 +24,19 @@ EXPORTED_SYMBOLS = [
     "pv3_index_file_open", "pv3_index_file_entries", "pv3_index_file_entry", "pv3_index_file_close", "pv3_index_file_write",
     "pv3_index_file_error", "pv3_msa_row_extract", "pv3_msa_row_extract_device", "pv3_format_oa", "pv3_format_cigars",
     "pv3_rescore_alignments", "pv3_calculate_mapq",
+    "pv3_index_remove_ref", "pv3_project_positions_device", "pv3_host_register", "pv3_host_unregister",
+    "pv3_multi_create", "pv3_multi_destroy", "pv3_multi_devices", "pv3_multi_ctx", "pv3_multi_project", "pv3_multi_last_error",
 ]
 
 
 class BatchIn(C.Structure):
     _fields_ = [("n", C.c_uint64), ("src_row", C.c_void_p), ("dst_row", C.c_void_p), ("dst_ref", C.c_void_p),
                 ("src_pos", C.c_void_p), ("seq_off", C.c_void_p), ("seq", C.c_void_p), ("qual_off", C.c_void_p),
-                ("qual", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p), ("seq_len", C.c_void_p)]
+                ("qual", C.c_void_p), ("cig_off", C.c_void_p), ("cig", C.c_void_p), ("seq_len", C.c_void_p),
+                # ABI 5
+                ("mate_row", C.c_void_p), ("mate_pos", C.c_void_p), ("compact", C.c_int), ("seq_bam4", C.c_int),
+                ("src_row16", C.c_void_p), ("dst_row16", C.c_void_p), ("dst_ref16", C.c_void_p), ("mate_row16", C.c_void_p),
+                ("src_pos32", C.c_void_p), ("mate_pos32", C.c_void_p), ("cig_len16", C.c_void_p), ("has_qual", C.c_void_p)]
 
 
 class BatchOut(C.Structure):
@@ -38,7 +44,10 @@ class BatchOut(C.Structure):
                 ("cig", C.c_void_p), ("cig_cap", C.c_uint64), ("rr_off", C.c_void_p), ("rr_len", C.c_void_p),
                 ("rr", C.c_void_p), ("rr_cap", C.c_uint64),
                 ("cig_used", C.c_uint64), ("rr_used", C.c_uint64), ("n_flagged", C.c_uint64),
-                ("n_realigned", C.c_uint64), ("dp_cells", C.c_uint64)]
+                ("n_realigned", C.c_uint64), ("dp_cells", C.c_uint64),
+                # ABI 5
+                ("mate_dst_pos", C.c_void_p), ("dst_pos32", C.c_void_p), ("flags8", C.c_void_p), ("cig_len16", C.c_void_p),
+                ("rr_len8", C.c_void_p), ("mate_dst_pos32", C.c_void_p)]
 
 
 class OaIn(C.Structure):
@@ -92,6 +101,19 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_project.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
     lib.pv3_project_device.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
     lib.pv3_project_positions.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.pv3_project_positions_device.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.pv3_index_remove_ref.argtypes = [C.c_void_p, C.c_int]
+    lib.pv3_host_register.argtypes = [C.c_void_p, C.c_size_t]
+    lib.pv3_host_unregister.argtypes = [C.c_void_p]
+    lib.pv3_multi_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_void_p]
+    lib.pv3_multi_destroy.argtypes = [C.c_void_p]
+    lib.pv3_multi_destroy.restype = None
+    lib.pv3_multi_devices.argtypes = [C.c_void_p]
+    lib.pv3_multi_ctx.argtypes = [C.c_void_p, C.c_int]
+    lib.pv3_multi_ctx.restype = C.c_void_p
+    lib.pv3_multi_project.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
+    lib.pv3_multi_last_error.argtypes = [C.c_void_p]
+    lib.pv3_multi_last_error.restype = C.c_char_p
     lib.pv3_index_query.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.pv3_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
     lib.pv3_total_launches.argtypes = [C.c_void_p]
@@ -223,22 +245,59 @@ class Context:
         return lut.reshape(42, 2)
 
     # ---- hot path ------------------------------------------------------------------------------------------------
-    def project(self, batch: RecordBatch, out: ProjectedBatch | None = None) -> ProjectedBatch:
-        """Host buffers in and out (pv3_project). `out` may be a preallocated (e.g. pinned) ProjectedBatch."""
+    def project(self, batch: RecordBatch, out: ProjectedBatch | None = None, mates=None, compact=None, narrow=None,
+                multi: "MultiContext | None" = None) -> ProjectedBatch:
+        """Host buffers in and out (pv3_project). `out` may be a preallocated (e.g. pinned) ProjectedBatch.
+        mates: (mate_row, mate_pos) or (mate_row, _, mate_pos) arrays → out.mate_dst_pos.
+        compact: dict from RecordBatch.compact_arrays() (possibly in pinned memory) → the compact input encoding.
+        narrow: dict with any of dst_pos32, flags8, cig_len16, rr_len8, mate_dst_pos32 arrays → written instead of the wide
+        fields (which are then not requested: cig_off / rr_off / flags / rr_len are dropped too)."""
         n = batch.n
         bi = BatchIn(n, _ptr(batch.src_row), _ptr(batch.dst_row), _ptr(batch.dst_ref), _ptr(batch.src_pos), _ptr(batch.seq_off),
                      _ptr(batch.seq), _ptr(batch.qual_off), _ptr(batch.qual) if batch.qual_off is not None else None,
                      _ptr(batch.cig_off), _ptr(batch.cig), _ptr(batch.seq_len))
+        keep = []
+        if mates is not None:
+            mr = np.ascontiguousarray(mates[0], dtype=np.uint32)
+            mp = np.ascontiguousarray(mates[-1], dtype=np.uint64)
+            keep += [mr, mp]
+            bi.mate_row, bi.mate_pos = _ptr(mr), _ptr(mp)
+        if compact is not None:
+            bi.compact = 1
+            bi.seq_bam4 = 1 if batch.seq_len is not None else 0
+            for k in ("src_row16", "dst_row16", "dst_ref16", "src_pos32", "cig_len16", "has_qual", "mate_row16", "mate_pos32"):
+                setattr(bi, k, _ptr(compact.get(k)))
+            bi.seq_len = _ptr(compact["seq_len"])
         if out is None:
             out = alloc_output(n, int(batch.cig.size) * 3 + n * 8 + 1024, n // 8 + 1024)
+        want_mates = mates is not None or (compact is not None and compact.get("mate_row16") is not None)
+        if want_mates and out.mate_dst_pos is None and not (narrow and "mate_dst_pos32" in narrow):
+            out.mate_dst_pos = np.zeros(n, np.uint64)
+        call = self.lib.pv3_project if multi is None else self.lib.pv3_multi_project
+        handle = self.h if multi is None else multi.h
         for _ in range(8):
             bo = BatchOut(_ptr(out.dst_pos), _ptr(out.flags), _ptr(out.cig_off), _ptr(out.cig_len), _ptr(out.cig), out.cig.size,
                           _ptr(out.rr_off), _ptr(out.rr_len), _ptr(out.rr), out.rr.shape[0], 0, 0, 0, 0, 0)
-            st = self.lib.pv3_project(self.h, C.byref(bi), C.byref(bo))
-            if st == PV3_ERR_CAPACITY:
+            bo.mate_dst_pos = _ptr(out.mate_dst_pos)
+            if narrow:
+                for k in ("dst_pos32", "flags8", "cig_len16", "rr_len8", "mate_dst_pos32"):
+                    if k in narrow:
+                        setattr(bo, k, _ptr(narrow[k]))
+                if "dst_pos32" in narrow: bo.dst_pos = None
+                if "flags8" in narrow: bo.flags = None
+                if "cig_len16" in narrow: bo.cig_len = None
+                if "rr_len8" in narrow: bo.rr_len = None
+                if "mate_dst_pos32" in narrow: bo.mate_dst_pos = None
+                bo.cig_off = None; bo.rr_off = None
+            st = call(handle, C.byref(bi), C.byref(bo))
+            if st == PV3_ERR_CAPACITY and not narrow:
                 out = alloc_output(n, max(int(bo.cig_used) * 2, out.cig.size * 2), max(int(bo.rr_used) * 2, out.rr.shape[0] * 2))
+                if want_mates:
+                    out.mate_dst_pos = np.zeros(n, np.uint64)
                 continue
-            self._check(st)
+            if st < 0:
+                msg = self.lib.pv3_last_error(self.h) if multi is None else self.lib.pv3_multi_last_error(multi.h)
+                raise Pv3Error(st, (msg or b"").decode())
             out.stats = dict(cig_used=int(bo.cig_used), rr_used=int(bo.rr_used), n_flagged=int(bo.n_flagged),
                              n_realigned=int(bo.n_realigned), dp_cells=int(bo.dp_cells))
             return out
@@ -258,6 +317,15 @@ class Context:
         out = np.zeros(p.size, dtype=np.uint64)
         self._check(self.lib.pv3_project_positions(self.h, p.size, _ptr(s), _ptr(d), _ptr(p), _ptr(out)))
         return out
+
+    def remove_ref(self, ref_id: int):
+        self._check(self.lib.pv3_index_remove_ref(self.h, ref_id))
+
+    def host_register(self, arr: np.ndarray):
+        self._check(self.lib.pv3_host_register(arr.ctypes.data, arr.nbytes))
+
+    def host_unregister(self, arr: np.ndarray):
+        self.lib.pv3_host_unregister(arr.ctypes.data)
 
     def index_query(self, op: int, row, x) -> np.ndarray:
         r = np.ascontiguousarray(row, dtype=np.uint32)
@@ -346,6 +414,53 @@ class Context:
 
     def total_launches(self) -> int:
         return int(self.lib.pv3_total_launches(self.h))
+
+
+class MultiContext:
+    """pv3_multi: one context per device behind one submitter (records out in input order across the devices)."""
+
+    def __init__(self, n_devices: int, devices=None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        dev = None if devices is None else (C.c_int * n_devices)(*devices)
+        st = self.lib.pv3_multi_create(C.byref(h), n_devices, dev)
+        if st != PV3_OK:
+            raise Pv3Error(st, (self.lib.pv3_last_error(None) or b"").decode())
+        self.h = h
+        self.ctxs = []
+        for i in range(n_devices):
+            c = Context.__new__(Context)
+            c.lib, c.h, c.device, c.n_rows, c.n_refs = self.lib, C.c_void_p(self.lib.pv3_multi_ctx(h, i)), i, 0, 0
+            c.close = lambda: None                      # owned by the multi handle
+            self.ctxs.append(c)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pv3_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def add_row(self, words, n_bits):
+        return [c.add_row(words, n_bits) for c in self.ctxs][0]
+
+    def add_ref(self, bases):
+        return [c.add_ref(bases) for c in self.ctxs][0]
+
+    def commit(self):
+        for c in self.ctxs:
+            c.commit()
+
+    def set_params(self, go=0, ge=-1):
+        for c in self.ctxs:
+            c.set_params(go, ge)
+
+    def project(self, batch, out=None, **kw):
+        return self.ctxs[0].project(batch, out, multi=self, **kw)
 
 
 def alloc_output(n: int, cig_cap: int, rr_cap: int, arena: PinnedArena | None = None) -> ProjectedBatch:

@@ -80,16 +80,32 @@ __host__ __device__ inline bool dp_job_is_small(uint32_t R, uint32_t Q)
 	return R <= K3T_MAX_DIM && Q <= K3T_MAX_DIM && (R + 1) * (Q + 1) <= K3T_MAX_TRACE;
 }
 
+#ifdef __CUDACC__
+// Run count of a batch: given by the host, or (~0) read from the counters the rewrite kernels filled on the same stream.
+__device__ __forceinline__ uint64_t dp_n_jobs(const Counters *c, uint64_t host_value)
+{
+	return host_value == ~0ull ? (uint64_t) *((volatile const unsigned long long *) &c->job_cursor) : host_value;
+}
+// Small runs go to the thread-per-run kernel once a batch holds at least dp_thread_min of them; both DP kernels evaluate this.
+__device__ __forceinline__ bool dp_use_thread_kernel(const Counters *c, uint64_t n_jobs, uint64_t dp_thread_min)
+{
+	uint64_t const n_big = *((volatile const unsigned long long *) &c->n_big_jobs);
+	return n_jobs > n_big && n_jobs - n_big >= dp_thread_min;
+}
+#endif
+
 struct K3Params {
 	K1Params        k1;             // inputs, index, flags, counters, jobs
-	uint64_t        n_jobs;
+	uint64_t        n_jobs;         // ~0: read counters->job_cursor on the device
+	uint64_t        dp_thread_min;  // pv3_set_dp_thread_min
+	uint32_t        grid_hint;      // thread-per-run kernel: CTAs of the resident grid when n_jobs is read on the device
+	uint64_t        pool_slots;     // HBM trace slots allocated (one per resident warp of the warp-per-run kernel)
 	uint32_t       *dp_arena; uint64_t dp_arena_cap;    // realigned ops, R+Q words reserved per job
 	uint8_t        *pool; uint64_t pool_slot_bytes;     // global scratch, one slot per resident warp (for jobs too large for smem)
 	int32_t         lut[84];        // quality LUT: [2*q] match, [2*q+1] mismatch
 	const uint8_t  *packed_qual;    // lazy-QUAL path: phred ranks of the runs' query windows only, run j at job_qual_off[j]
 	const uint64_t *job_qual_off;   // null ⇒ read k1.qual
-	uint64_t       *big_list;       // ids of the runs left to the warp kernel, written by the thread kernel (null ⇒ all runs)
-	uint64_t        n_big;          // length of big_list (known to the host from counters.n_big_jobs)
+	uint64_t       *big_list;       // ids of the runs left to the warp kernel, written by the thread kernel (capacity: jobs)
 };
 
 struct K4Params {
@@ -99,6 +115,55 @@ struct K4Params {
 	const uint32_t *dp_arena;
 	const uint64_t *realigned_recs; // unused (records are found through jobs)
 };
+
+// ---- host pipeline ends (pv3_pack.cu) ----------------------------------------------------------------------------------
+// Compact input (device copies of what crossed PCIe) → the arrays of K1Params.
+struct UnpackParams {
+	uint64_t        n;
+	const uint16_t *src_row16, *dst_row16, *dst_ref16;
+	const uint32_t *src_pos32;
+	const uint32_t *seq_len;      // bases per record
+	const uint16_t *cig_len16;
+	const uint8_t  *has_qual;     // bit i: record i has QUAL (as long as its SEQ); null: none has
+	const uint16_t *mate_row16;   // null: no mates
+	const uint32_t *mate_pos32;
+	int             seq_packed;   // SEQ bytes per record: (bases + 1) / 2 instead of bases
+	uint32_t       *src_row, *dst_row, *dst_ref, *mate_row;
+	uint64_t       *src_pos, *mate_pos, *seq_off, *cig_off, *qual_off;   // qual_off null when has_qual is null
+	uint64_t       *tile_sums;    // scratch: 3 * pack_tiles(n) + 3 words
+};
+
+// What a chunk reports to the host (mapped pinned memory in the host path): read once, after the call's only synchronisation.
+struct ChunkReport {
+	unsigned long long cig_used, rr_used, n_flagged, n_realigned, dp_cells, dp_path, dp_max_pool, arena_need, jobs, n_deferred;
+	unsigned long long cig_base, rr_base;   // the chunk's place in the call's ordered arenas
+	unsigned int       overflow;  // bits 0-3 as Counters::overflow (8: HBM trace slots), 16 / 32: caller's cig / rr capacity, 64: compact field
+	unsigned int       done;
+};
+
+// Arena-addressed results of one chunk → ordered output at the chunk's place in the caller's batch.
+struct PackParams {
+	uint64_t        n, rec0;      // records of the chunk; index of its first record in the caller's batch
+	const uint64_t *dst_pos; const uint32_t *flags;
+	const uint64_t *cig_off; const uint32_t *cig_len; const uint32_t *arena; uint64_t arena_off;
+	const uint64_t *rr_off;  const uint32_t *rr_len;  const uint64_t *rr;    uint64_t rr_base;
+	const uint64_t *mate_dst_pos; // null: no mates
+	const Counters *counters;
+	uint64_t       *running;      // [2] device: output ops / runs of the chunks before this one (chains the chunks of a call)
+	uint64_t       *place;        // [3] device scratch of this chunk: its bases and the overflow word
+	uint64_t       *tile_sums;    // scratch: 3 * pack_tiles(n) + 3 words
+	ChunkReport    *report;
+	// destination (device or mapped host pointers; null = not wanted)
+	uint64_t *out_dst_pos; uint32_t *out_dst_pos32; uint32_t *out_flags; uint8_t *out_flags8;
+	uint64_t *out_cig_off; uint32_t *out_cig_len; uint16_t *out_cig_len16; uint32_t *out_cig; uint64_t out_cig_cap;
+	uint64_t *out_rr_off; uint32_t *out_rr_len; uint8_t *out_rr_len8; uint64_t *out_rr; uint64_t out_rr_cap;
+	uint64_t *out_mate_dst_pos; uint32_t *out_mate_dst_pos32;
+	uint64_t  cig_off_bias, rr_off_bias;   // added to the stored offsets (pv3_multi: where the shard's arenas start in the caller's arrays)
+	int       staged;         // 1: out_cig / out_rr are staging buffers of this chunk (index 0 = the chunk's place)
+};
+uint64_t pack_tiles(uint64_t n);
+void launch_unpack_in(const UnpackParams &P, cudaStream_t stream);
+void launch_pack_out(const PackParams &P, cudaStream_t stream);
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
 void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record, run walk (v4-v13)

@@ -55,13 +55,18 @@ k3_realign_kernel(K3Params P)
 	unsigned const warp_in_block = threadIdx.x >> 5;
 	uint64_t const warp_global = (uint64_t) blockIdx.x * K3_WARPS + warp_in_block;
 	int32_t const gext = B.gap_ext, gopen = B.gap_open + B.gap_ext;   // affine_gap_policy.hpp:183-190
+	// run counts from the device (no host round trip after the rewrite); small runs were realigned by the thread-per-run
+	// kernel iff it decided to run (same counters, same rule): then only its list of large runs is left
+	uint64_t const n_jobs = dp_n_jobs(B.counters, P.n_jobs);
+	bool const only_big = P.big_list && dp_use_thread_kernel(B.counters, n_jobs, P.dp_thread_min);
+	uint64_t const n_mine = only_big ? (uint64_t) B.counters->big_cursor : n_jobs;
 
 	for (;;) {
 		unsigned long long jid = 0;
 		if (lane == 0) jid = atomicAdd(&B.counters->job_ticket, 1ull);
 		jid = shfl_u64(jid, 0);
-		if (jid >= (P.big_list ? P.n_big : P.n_jobs)) break;
-		if (P.big_list) jid = P.big_list[jid];                     // small runs are realigned by the thread-per-run kernel
+		if (jid >= n_mine) break;
+		if (only_big) jid = P.big_list[jid];
 
 		Job const job = B.jobs[jid];
 		uint64_t const rec = job.rec;
@@ -85,6 +90,10 @@ k3_realign_kernel(K3Params P)
 		bool const edit = !has_qual && B.gap_open == 0;
 
 		unsigned long long const need = dp_pool_bytes(R, Q, !edit);
+		if (need > SMEM_POOL && (!P.pool || need > P.pool_slot_bytes || warp_global >= P.pool_slots)) {
+			if (lane == 0) atomicOr(&B.counters->overflow, 8u);      // HBM trace slots missing or too small: the host grows them and re-runs
+			continue;
+		}
 		uint8_t *pool = (need <= SMEM_POOL) ? smem_pool[warp_in_block] : (P.pool + warp_global * P.pool_slot_bytes);
 		uint32_t const trace_bytes = (uint32_t) ((((unsigned long long) (Q + 1) * cols) + 3ull) & ~3ull);
 		uint8_t *T = pool;
@@ -221,7 +230,7 @@ k3_realign_kernel(K3Params P)
 
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream)
 {
-	uint64_t const n = P.big_list ? P.n_big : P.n_jobs;
+	uint64_t const n = P.n_jobs;          // ~0: read on the device
 	if (!n) return;
 	uint64_t warps = grid_warps ? grid_warps : k3_default_grid_warps(n_sms);
 	if (warps > n) warps = n;

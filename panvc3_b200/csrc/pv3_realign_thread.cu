@@ -43,25 +43,31 @@ k3_thread_kernel(K3Params P)
 {
 	K1Params const &B = P.k1;
 	unsigned const lane = lane_id();
-	uint64_t const jid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	int32_t const gext = B.gap_ext, gopen = B.gap_open + B.gap_ext;   // affine_gap_policy.hpp:183-190
+	// The run count is read on the device (the rewrite kernels have finished on this stream): no host round trip between the
+	// rewrite and the DP. Few small runs: the warp-per-run kernel takes them all (it reads the same counters and decides alike).
+	uint64_t const n_jobs = dp_n_jobs(B.counters, P.n_jobs);
+	if (!dp_use_thread_kernel(B.counters, n_jobs, P.dp_thread_min)) return;
+	uint64_t const stride = (uint64_t) gridDim.x * blockDim.x;
+	for (uint64_t jbase = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; jbase < n_jobs; jbase += stride) {
+	uint64_t const jid = jbase + lane;
 
 	uint32_t R = 0, Q = 0, qry_loc = 0;
 	uint64_t rec = 0, ref_loc = 0;
 	bool mine = false;
-	if (jid < P.n_jobs) {
+	if (jid < n_jobs) {
 		Job const &job = B.jobs[jid];
 		R = job.ref_len; Q = job.qry_len; rec = job.rec; ref_loc = job.ref_loc; qry_loc = job.qry_loc;
 		mine = dp_job_is_small(R, Q);
 	}
 	// runs left to the warp kernel: compact list, one atomic per warp
 	{
-		uint32_t const m_big = __ballot_sync(FULL, jid < P.n_jobs && !mine);
+		uint32_t const m_big = __ballot_sync(FULL, jid < n_jobs && !mine);
 		if (m_big && P.big_list) {
 			unsigned long long b = 0;
 			if (lane == 0) b = atomicAdd(&B.counters->big_cursor, (unsigned long long) __popc(m_big));
 			b = shfl_u64(b, 0);
-			if (jid < P.n_jobs && !mine) P.big_list[b + __popc(m_big & lanemask_lt())] = jid;
+			if (jid < n_jobs && !mine) P.big_list[b + __popc(m_big & lanemask_lt())] = jid;
 		}
 	}
 	// op space for the warp's runs (R + Q words each, filled from the end): one atomic
@@ -76,7 +82,7 @@ k3_thread_kernel(K3Params P)
 		if (wbase + total > P.dp_arena_cap) { atomicOr(&B.counters->overflow, 4u); wbase = ~0ull; }
 	}
 	wbase = shfl_u64(wbase, 0);
-	if (!mine || wbase == ~0ull) return;
+	if (!mine || wbase == ~0ull) continue;
 	uint32_t *out = P.dp_arena + wbase + (incl - reserve);
 
 	uint32_t const cols = R + 1;
@@ -195,13 +201,16 @@ k3_thread_kernel(K3Params P)
 		uint32_t const old = atomicOr(&B.flags[rec], PV3_FLAG_TRACE_UB);
 		if (!old) atomicAdd(&B.counters->n_flagged, 1ull);
 	}
+	}   // grid-stride loop over the runs
 }
 
 void launch_k3_thread(const K3Params &P, cudaStream_t stream)
 {
+	// P.n_jobs known (> 0): one pass over the runs; ~0: read on the device, a resident grid strides over them
 	if (!P.n_jobs) return;
 	unsigned const threads = 128;
-	unsigned const blocks = (unsigned) ((P.n_jobs + threads - 1) / threads);
+	uint64_t const want = P.n_jobs == ~0ull ? (uint64_t) P.grid_hint : (P.n_jobs + threads - 1) / threads;
+	unsigned const blocks = (unsigned) (want ? want : 1);
 	if (P.k1.seq_len) k3_thread_kernel <true><<<blocks, threads, 0, stream>>>(P);
 	else k3_thread_kernel <false><<<blocks, threads, 0, stream>>>(P);
 }

@@ -379,8 +379,8 @@ k1_rewrite_kernel(K1Params P, int group)
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)
 {
 	if (P.n_list_dev) {
-		// deferred list of the thread kernel, length known only on the device: a small grid-stride launch, one record per warp
-		k1_rewrite_kernel<<<(unsigned) n_sms * 2, K1_WARPS * 32, 0, stream>>>(P, 1);
+		// deferred list of the thread kernel, length known only on the device: a resident grid strides over it, one record per warp
+		k1_rewrite_kernel<<<(unsigned) n_sms * 4, K1_WARPS * 32, 0, stream>>>(P, 1);
 		return;
 	}
 	uint64_t const n_items = P.rec_list ? P.n_list : P.n;

@@ -12,10 +12,13 @@ namespace pv3 {
 // One thread per run; the thread holding the first run of a record rebuilds that record's CIGAR. The arena space of a
 // warp's records is taken with one atomic (per-record atomics on the cursor serialise when most records realign).
 __global__ void __launch_bounds__(128)
-k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp_arena)
+k4_splice_kernel(K1Params P, uint64_t n_jobs_host, const uint32_t *dp_arena)
 {
-	uint64_t const jid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
 	unsigned const lane = lane_id();
+	uint64_t const n_jobs = dp_n_jobs(P.counters, n_jobs_host);
+	uint64_t const stride = (uint64_t) gridDim.x * blockDim.x;
+	for (uint64_t jbase = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; jbase < n_jobs; jbase += stride) {
+	uint64_t const jid = jbase + lane;
 	uint64_t rec = 0;
 	uint32_t n_runs = 0, n_pre = 0, bound = 0;
 	const uint32_t *pre = nullptr;
@@ -48,8 +51,8 @@ k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp_arena)
 		if (wbase + total > P.arena_cap) { atomicOr(&P.counters->overflow, 1u); wbase = ~0ull; }
 	}
 	wbase = shfl_u64(wbase, 0);
-	if (!owner) return;
-	if (wbase == ~0ull) { P.cig_out_len[rec] = 0; return; }
+	if (!owner) continue;
+	if (wbase == ~0ull) { P.cig_out_len[rec] = 0; continue; }
 	unsigned long long const base = wbase + (incl - bound);
 	uint32_t *dst = P.arena + base;
 	// collapse_cigar_operations (cigar.cc:33-38): the open op stays in registers until a different op arrives
@@ -72,13 +75,15 @@ k4_splice_kernel(K1Params P, uint64_t n_jobs, const uint32_t *dp_arena)
 	if (cur_op != OP_NONE) dst[w++] = (cur_cnt << 4) | cur_op;
 	P.cig_out_off[rec] = base + P.arena_off;
 	P.cig_out_len[rec] = w;
+	}   // grid-stride loop over the runs
 }
 
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream)
 {
 	if (!n_jobs) return;
 	unsigned const threads = 128;
-	unsigned const blocks = (unsigned) ((n_jobs + threads - 1) / threads);
+	// n_jobs == ~0: the count is read on the device and a resident grid strides over the runs
+	unsigned const blocks = n_jobs == ~0ull ? 148u * 8u : (unsigned) ((n_jobs + threads - 1) / threads);
 	k4_splice_kernel<<<blocks, threads, 0, stream>>>(P, n_jobs, dp_arena);
 }
 

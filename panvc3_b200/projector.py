@@ -127,6 +127,17 @@ class MsaIndex:
         return idx.commit()
 
     @classmethod
+    def from_rows(cls, gap_rows, refs, names=None, device: int = 0) -> "MsaIndex":
+        """Entries from (gap words, n_bits) pairs and contigs from byte strings — the inputs the oracle's index takes, e.g.
+        workload.MsaWords.index_inputs() at chromosome scale, where no text rows exist."""
+        idx = cls(device)
+        for i, (words, n_bits) in enumerate(gap_rows):
+            idx.add_entry(names[i] if names else str(i), words, n_bits)
+        for r in refs:
+            idx.add_reference(r)
+        return idx.commit()
+
+    @classmethod
     def from_file(cls, path: str, chr_id: str, references: dict[str, bytes] | None = None, device: int = 0) -> "MsaIndex":
         """Loads the chr entry `chr_id` of an index-msa file (project_alignments.cc:1457-1465 loads the file, :632-650 looks
         the chr and sequence entries up by id). `references` maps seq ids to the unaligned contigs (--reference FASTA,

@@ -214,3 +214,220 @@ def sample_reads(msa: Msa, n: int, read_len: int, seed: int, sub: float = 0.005,
     return RecordBatch(src_row=src_row, dst_row=np.full(n, dst_row, np.uint32), dst_ref=np.zeros(n, np.uint32),
                        src_pos=start.astype(np.uint64), seq_off=seq_off, seq=seq, cig_off=cig_off, cig=cig,
                        qual_off=qual_off, qual=qual)
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# Chromosome-scale workloads (BASELINE.json configs[2]): the MSA is never held as text rows. Gap rows are built directly as
+# bit words from sampled gap runs; one byte array holds the base of every MSA column; a founder's base at a column is that
+# byte unless a hash of (column, founder) makes it a SNP, so no per-founder sequence exists in memory.
+# ------------------------------------------------------------------------------------------------------------------------
+_M1, _M2 = np.uint64(0x9E3779B97F4A7C15), np.uint64(0xC2B2AE3D27D4EB4F)
+
+
+def _mix(cols: np.ndarray, founder: np.ndarray | int, salt: int) -> np.ndarray:
+    """64-bit mix of (column, founder, salt); vectorised."""
+    with np.errstate(over="ignore"):
+        h = cols.astype(np.uint64) * _M1 + (np.asarray(founder, dtype=np.uint64) + np.uint64(salt)) * _M2
+        h ^= h >> np.uint64(29)
+        h *= _M2
+        h ^= h >> np.uint64(32)
+    return h
+
+
+def gap_words_from_runs(n_cols: int, starts: np.ndarray, lens: np.ndarray) -> np.ndarray:
+    """uint64 words (LSB first) with bits [s, s + l) set for every run; O(runs), not O(columns)."""
+    n_words = (n_cols + 63) // 64
+    words = np.zeros(n_words, dtype=np.uint64)
+    s = starts.astype(np.int64)
+    e = np.minimum(s + lens.astype(np.int64), n_cols)
+    keep = e > s
+    s, e = s[keep], e[keep]
+    full = np.uint64(0xFFFFFFFFFFFFFFFF)
+    while s.size:
+        w = s >> 6
+        lo = (s & 63).astype(np.uint64)
+        stop = np.minimum(e, (w + 1) << 6)                     # end of this run inside word w
+        n = (stop - s).astype(np.uint64)
+        mask = np.where(n == 64, full, ((np.uint64(1) << n) - np.uint64(1))) << lo
+        np.bitwise_or.at(words, w, mask)
+        s = stop
+        more = s < e
+        s, e = s[more], e[more]
+    return words
+
+
+@dataclass
+class MsaWords:
+    """One chromosome's MSA as gap words (row 0 = REF, the projection target) + the base of every column."""
+
+    n_cols: int
+    gap_words: list[np.ndarray]
+    col_base: np.ndarray                 # ASCII base of every column (what REF and, SNPs aside, every founder has there)
+    names: list[str]
+    snp: float
+    seed: int
+
+    def __post_init__(self) -> None:
+        self.n_rows = len(self.gap_words)
+        # zeros before every word, per row: rank0 at word granularity (select by searchsorted)
+        self.zeros_before = []
+        for w in self.gap_words:
+            pc = _popcount64(~w)
+            tail = self.n_cols & 63
+            if tail:
+                pc[-1] -= 64 - tail                            # bits beyond n_cols are zeros in `w` but are not columns
+            zb = np.zeros(w.size + 1, dtype=np.int64)
+            np.cumsum(pc, out=zb[1:])
+            self.zeros_before.append(zb)
+        self.n_bases = [int(z[-1]) for z in self.zeros_before]
+
+    def ref_bytes(self) -> bytes:
+        bits = np.unpackbits(self.gap_words[0].view(np.uint8), bitorder="little")[: self.n_cols]
+        return self.col_base[bits == 0].tobytes()
+
+    def index_inputs(self, rows: list[int] | None = None):
+        """(gap_rows, refs) for the oracle / the product's index upload; contig 0 = REF's bases."""
+        rows = list(range(self.n_rows)) if rows is None else rows
+        return [(self.gap_words[r], self.n_cols) for r in rows], [self.ref_bytes()]
+
+
+def _popcount64(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint64, copy=True)
+    m1, m2, m4 = np.uint64(0x5555555555555555), np.uint64(0x3333333333333333), np.uint64(0x0F0F0F0F0F0F0F0F)
+    x -= (x >> np.uint64(1)) & m1
+    x = (x & m2) + ((x >> np.uint64(2)) & m2)
+    x = (x + (x >> np.uint64(4))) & m4
+    with np.errstate(over="ignore"):
+        x = (x * np.uint64(0x0101010101010101)) >> np.uint64(56)
+    return x.astype(np.int64)
+
+
+def synth_msa_words(n_cols: int, n_founders: int, seed: int, p_gap: float = 0.002, mean_gap: float = 8.0, snp: float = 0.001) -> MsaWords:
+    """Gap-run MSA model of SURVEY §8(d) at chromosome scale: per row, gap runs start with probability `p_gap` per column and
+    have geometric length (mean `mean_gap`); REF + `n_founders` founder rows."""
+    rng = np.random.default_rng(seed)
+    col_base = _ACGT[rng.integers(0, 4, n_cols, dtype=np.uint8)]
+    rows = []
+    for _ in range(n_founders + 1):
+        n_runs = int(rng.binomial(n_cols, p_gap))
+        starts = rng.integers(0, n_cols, n_runs)
+        lens = rng.geometric(1.0 / mean_gap, n_runs)
+        rows.append(gap_words_from_runs(n_cols, starts, lens))
+    return MsaWords(n_cols=n_cols, gap_words=rows, col_base=col_base, names=["REF"] + [str(i) for i in range(1, n_founders + 1)], snp=snp, seed=seed)
+
+
+READ_BLOCK = 50_000      # reads are generated in blocks with their own seeds: the first k blocks of a batch do not depend on n
+
+
+def _sample_block(msa: MsaWords, n: int, read_len: int, seed, sub: float, ins: float, dele: float, clip_frac: float, with_qual: bool,
+                  paired: bool):
+    rng = np.random.default_rng(seed)
+    founders = rng.integers(1, msa.n_rows, n)
+    win_words = (read_len + 3 + 64 + 63) // 64 + 1       # a read's span plus slack; windows with too few bases are resampled
+    L = read_len
+    p_any = lambda p: 1.0 - (1.0 - p) ** L
+    u = rng.random(n)
+    c_ins, c_del, c_clip = p_any(ins), p_any(dele), clip_frac
+    kind = np.where(u < c_ins, 1, np.where(u < c_ins + c_del, 2, np.where(u < c_ins + c_del + c_clip, 3, 0)))
+    ev_len = rng.integers(1, 4, n)                       # insertion / deletion length
+    ev_len = np.where(kind == 3, rng.integers(1, 21, n), ev_len)
+    ev_at = rng.integers(5, L - 5, n)                    # read offset of the event
+    lead_clip = rng.random(n) < 0.5
+    # founder bases consumed: L - li (insertion), L + ld (deletion), L - a (clip), L
+    need = np.where(kind == 1, L - ev_len, np.where(kind == 2, L + ev_len, np.where(kind == 3, L - ev_len, L)))
+    max_need = L + 3
+    start_word = np.empty(n, dtype=np.int64)
+    cols = np.empty((n, max_need), dtype=np.int64)
+    todo = np.arange(n)
+    while todo.size:                                     # resample reads whose window holds too few founder bases (long gaps, row ends)
+        m = todo.size
+        sw = rng.integers(0, max(msa.gap_words[0].size - win_words, 1), m)
+        f = founders[todo]
+        got = np.zeros(m, dtype=bool)
+        for fr in np.unique(f):
+            sel = np.flatnonzero(f == fr)
+            idx = sw[sel][:, None] + np.arange(win_words)[None, :]
+            bits = np.unpackbits(msa.gap_words[int(fr)][idx].view(np.uint8).reshape(sel.size, -1), axis=1, bitorder="little")
+            base = bits == 0
+            cum = np.cumsum(base, axis=1, dtype=np.int16)
+            ok = cum[:, -1] >= max_need
+            take = base & (cum <= max_need) & ok[:, None]
+            pos = np.nonzero(take)[1].reshape(-1, max_need)
+            good = sel[ok]
+            cols[todo[good]] = sw[good][:, None] * 64 + pos
+            got[good] = True
+        start_word[todo[got]] = sw[got]
+        todo = todo[~got]
+    first_col = cols[:, 0]
+    # source position = founder bases before the first column
+    src_pos = np.empty(n, dtype=np.int64)
+    for fr in np.unique(founders):
+        sel = np.flatnonzero(founders == fr)
+        w = first_col[sel] >> 6
+        below = msa.gap_words[int(fr)][w] | ~((np.uint64(1) << (first_col[sel] & 63).astype(np.uint64)) - np.uint64(1))
+        src_pos[sel] = msa.zeros_before[int(fr)][w] + _popcount64(~below)
+    # founder bases at the columns (SNPs by hash), then the read with its errors
+    fb = msa.col_base[cols]
+    h = _mix(cols, founders[:, None], msa.seed)
+    is_snp = (h % np.uint64(1_000_000)) < np.uint64(int(msa.snp * 1_000_000))
+    fb = np.where(is_snp, _ACGT[((h >> np.uint64(40)) & np.uint64(3)).astype(np.int64)], fb)
+    franks = ranks_from_ascii(fb.reshape(-1)).reshape(n, max_need)
+    j = np.arange(L)[None, :]
+    at, ln = ev_at[:, None], ev_len[:, None]
+    k = kind[:, None]
+    lead = lead_clip[:, None]
+    # founder offset of read base j (−1: the base is not taken from the founder)
+    off_plain = j
+    off_ins = np.where(j < at, j, np.where(j < at + ln, -1, j - ln))
+    off_del = np.where(j < at, j, j + ln)
+    off_clip = np.where(lead, np.where(j < ln, -1, j - ln), np.where(j < L - ln, j, -1))
+    off = np.where(k == 1, off_ins, np.where(k == 2, off_del, np.where(k == 3, off_clip, off_plain)))
+    rand_ranks = rng.integers(0, 4, (n, L)).astype(np.uint8)
+    rand_ranks = np.where(rand_ranks == 3, 4, rand_ranks).astype(np.uint8)      # A C G T as dna5 ranks 0 1 2 4
+    seq = np.where(off >= 0, np.take_along_axis(franks, np.maximum(off, 0), axis=1), rand_ranks)
+    submask = (rng.random((n, L)) < sub) & (off >= 0)
+    seq = np.where(submask, rand_ranks, seq).astype(np.uint8)
+    # CIGAR (M style, as bowtie2 writes it): up to three ops
+    M, I, D, S = 0, 1, 2, 4
+    pk = lambda cnt, op: (cnt.astype(np.uint32) << np.uint32(4)) | np.uint32(op)
+    ops = np.zeros((n, 3), dtype=np.uint32)
+    n_ops = np.where(kind == 0, 1, np.where(kind == 3, 2, 3))
+    ops[:, 0] = np.where(kind == 0, pk(np.full(n, L), M), np.where(kind == 3, np.where(lead_clip, pk(ev_len, S), pk(L - ev_len, M)), pk(ev_at, M)))
+    ops[:, 1] = np.where(kind == 1, pk(ev_len, I), np.where(kind == 2, pk(ev_len, D), np.where(lead_clip, pk(L - ev_len, M), pk(ev_len, S))))
+    ops[:, 2] = np.where(kind == 1, pk(L - ev_at - ev_len, M), pk(L - ev_at, M))
+    cig_off = np.zeros(n + 1, dtype=np.uint64)
+    cig_off[1:] = np.cumsum(n_ops)
+    cig = ops[np.arange(3)[None, :] < n_ops[:, None]]
+    seq_off = (np.arange(n + 1, dtype=np.uint64) * np.uint64(L))
+    qual_off = qual = None
+    if with_qual:
+        qual_off = seq_off.copy()
+        qual = rng.integers(2, 41, n * L, dtype=np.uint8)
+    batch = RecordBatch(src_row=founders.astype(np.uint32), dst_row=np.zeros(n, np.uint32), dst_ref=np.zeros(n, np.uint32),
+                        src_pos=src_pos.astype(np.uint64), seq_off=seq_off, seq=seq.reshape(-1), cig_off=cig_off, cig=cig,
+                        qual_off=qual_off, qual=qual)
+    mates = None
+    if paired:
+        nb = np.asarray(msa.n_bases, dtype=np.int64)[founders]
+        mate_pos = np.clip(src_pos + np.rint(rng.normal(350, 50, n)).astype(np.int64), 0, nb - 1)
+        mates = (founders.astype(np.uint32), np.zeros(n, np.uint32), mate_pos.astype(np.uint64))
+    return batch, mates
+
+
+def sample_reads_words(msa: MsaWords, n: int, read_len: int, seed: int, sub: float = 0.005, ins: float = 0.0005, dele: float = 0.0005,
+                       clip_frac: float = 0.02, with_qual: bool = True, paired: bool = True):
+    """`n` reads of `read_len` bases sampled from the founder rows with their true alignment (start + CIGAR, at most one indel
+    or soft clip per read), plus — `paired` — the mate position of every record (the CLI projects it with
+    sequence_entry::project_position, project_alignments.cc:880-906). Returns (RecordBatch, (mate_src_row, mate_dst_row,
+    mate_pos) or None). Generated in blocks of READ_BLOCK with seeds (seed, block): a prefix of the batch can be regenerated
+    without the rest (the on-hardware parity check of other ranks' shards relies on it)."""
+    parts, mparts = [], []
+    for b0 in range(0, n, READ_BLOCK):
+        m = min(READ_BLOCK, n - b0)
+        bt, mt = _sample_block(msa, m, read_len, [seed, b0 // READ_BLOCK], sub, ins, dele, clip_frac, with_qual, paired)
+        parts.append(bt); mparts.append(mt)
+    batch = RecordBatch.concat(parts) if len(parts) > 1 else parts[0]
+    mates = None
+    if paired:
+        mates = tuple(np.concatenate([m[i] for m in mparts]) for i in range(3))
+    return batch, mates

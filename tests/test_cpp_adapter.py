@@ -69,6 +69,56 @@ def test_adapter_reproduces_reference_tables(tmp_path, fixtures_json):
     assert out[-1] == f"DELEGATE {n_runs} {n_runs}"
 
 
+def build_batch_test(tmpdir) -> str:
+    from panvc3_b200 import build
+    build.build()
+    exe = os.path.join(str(tmpdir), "batch_test")
+    libdir = os.path.join(ROOT, "panvc3_b200")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", f"-I{ROOT}/include", "-o", exe, os.path.join(CPP, "batch_test.cc"),
+                    f"-L{libdir}", "-lpanvc3_b200", f"-Wl,-rpath,{libdir}"], check=True)
+    return exe
+
+
+def test_batch_projector_compiles_and_links(tmp_path):
+    assert os.path.exists(build_batch_test(tmp_path))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("devices", ["0", "0,0,0", "0,1"])
+def test_batch_projector_reproduces_reference_tables(tmp_path, fixtures_json, devices):
+    """The batched C++ entry (push_back into the pinned arena, one flush = one pv3_project / pv3_multi_project call) against
+    the reference's tables — all records of a cost setting in one batch; on one device, on three shards of one device, and
+    on two GPUs where the box has them. Mates: every record's own start position projected again."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    if devices == "0,1" and torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    exe = build_batch_test(tmp_path)
+    for key, qual, go in (("ref_project_integer", 0, 0), ("ref_project_quality", 1, 0), ("ref_project_affine_go-2", 0, -2)):
+        lines, expected = [], []
+        # enough copies that every shard holds records (shards are cut at multiples of 128 records)
+        for rep in range(40):
+            for table in ("rewrite_cigar", "alignment_projector"):
+                for case in fixtures_json[table]:
+                    lines.append("\t".join([case["src"], case["dst"], case["query"], str(case["src_pos"]), case["cigar"], str(qual), str(go), "-1"]))
+                    expected.append(case[key])
+        lines.append("\t".join(["GAT-ACA", "GATTACA", "T", "2", "2M", str(qual), str(go), "-1"]))
+        res = subprocess.run([exe, devices], input="\n".join(lines) + "\n", capture_output=True, text=True, timeout=600)
+        assert res.returncode == 0, res.stdout[-500:] + res.stderr[-500:]
+        out = res.stdout.strip().split("\n")
+        assert len(out) == 2 * len(lines), out[-3:]
+        for got, exp in zip(out, expected):
+            pos, cigar, rr, qr = (got.split("\t") + ["", ""])[:4]
+            assert int(pos) == exp["pos"] and cigar == exp["cigar"], (got, exp, devices, key)
+            ref_ranges = [tuple(int(v) for v in x.split(":")) for x in rr.split(",") if x]
+            qry_ranges = [tuple(int(v) for v in x.split(":")) for x in qr.split(",") if x]
+            assert [list(a) + list(b) for a, b in zip(ref_ranges, qry_ranges)] == exp["ranges"]
+        assert out[len(expected)] == "ERROR 4"
+        for got, exp in zip(out[len(lines):], expected):
+            assert got == f"MATE {exp['pos']}", (got, exp)        # a record's dst position IS project_position of its start
+
+
 def build_annotator_test(tmpdir) -> str:
     from panvc3_b200 import build
     build.build()

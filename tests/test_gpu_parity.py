@@ -629,3 +629,136 @@ def test_pinned_host_batch(gpu, port, workflow_msa):
         got_pinned = idx.project_batch(pb, go, ge)
         assert_same(got_pinned, exp, b, f"pinned go={go}")
         assert_same(idx.project_batch(b, go, ge), exp, b, f"pageable go={go}")
+
+
+# ---------------------------------------------------------------------------------------------- host pipeline (ABI 5)
+def _pinned_copy(arena, arr):
+    q = arena.take(arr.shape, arr.dtype); q[...] = arr
+    return q
+
+
+def _exclusive(lens):
+    off = np.zeros(lens.size, np.uint64)
+    if lens.size > 1:
+        off[1:] = np.cumsum(lens[:-1].astype(np.uint64))
+    return off
+
+
+@pytest.mark.parametrize("packed_seq", [False, True])
+def test_ordered_compact_output_and_mates(gpu, port, workflow_msa, packed_seq):
+    """pv3_project's host contract: arenas in record order (offsets redundant), mates projected in the same call
+    (project_alignments.cc:880-906), the compact input encoding and the narrow output fields — pageable and pinned
+    (zero-copy write-back) memory — all equal to the oracle."""
+    from panvc3_b200.capi import PinnedArena, alloc_output
+    from panvc3_b200.workload import sample_reads
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    b = sample_reads(workflow_msa, 220_000, 150, seed=81, ins=0.004, dele=0.004, clip_frac=0.1)
+    exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+    assert int(exp.rr_len.sum()) > 500
+    rng = np.random.default_rng(3)
+    lens = np.asarray([u.size for u in workflow_msa.ungapped], dtype=np.int64)
+    mrow = rng.integers(1, workflow_msa.n_rows, b.n).astype(np.uint32)
+    mpos = (rng.random(b.n) * (lens[mrow] - 1)).astype(np.uint64)
+    mexp = np.array([oi.project_position(int(r), 0, int(p)) for r, p in zip(mrow[:3000], mpos[:3000])], dtype=np.uint64)
+    src = b.to_bam4() if packed_seq else b
+    n = b.n
+
+    def check(got, what, narrow=None):
+        if narrow:
+            cl = narrow["cig_len16"].astype(np.uint32)
+            got = type(got)(dst_pos=narrow["dst_pos32"].astype(np.uint64), flags=narrow["flags8"].astype(np.uint32), cig_off=_exclusive(cl), cig_len=cl,
+                            cig=got.cig, rr_off=_exclusive(narrow["rr_len8"].astype(np.uint32)), rr_len=narrow["rr_len8"].astype(np.uint32), rr=got.rr,
+                            mate_dst_pos=narrow["mate_dst_pos32"].astype(np.uint64))
+        assert_same(got, exp, b, what)
+        assert np.array_equal(got.cig_off, _exclusive(got.cig_len)), f"{what}: CIGAR arena not in record order"
+        assert np.array_equal(got.rr_off, _exclusive(got.rr_len)), f"{what}: range arena not in record order"
+        assert np.array_equal(got.mate_dst_pos[:3000], mexp), f"{what}: mate positions"
+        assert int(got.cig_len.sum()) == got_stats["cig_used"] and int(got.rr_len.sum()) == got_stats["rr_used"]
+
+    idx.ctx.set_params(0, -1)
+    # pageable, wide fields (staged copies, one synchronisation per chunk)
+    got = idx.ctx.project(src, mates=(mrow, mpos)); got_stats = got.stats
+    check(got, "pageable")
+    # pinned: results written in place by the pack kernel
+    arena = PinnedArena(idx.ctx.lib, src.input_bytes() + n * 64 + int(exp.cig_len.sum()) * 8 + 1 << 22)
+    pb = RecordBatch.__new__(RecordBatch)
+    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
+        a = getattr(src, k)
+        setattr(pb, k, None if a is None else _pinned_copy(arena, a))
+    pout = alloc_output(n, int(exp.cig_len.sum()) + 4096, int(exp.rr_len.sum()) + 64, arena)
+    pout.mate_dst_pos = arena.take((n,), np.uint64)
+    got = idx.ctx.project(pb, pout, mates=(_pinned_copy(arena, mrow), _pinned_copy(arena, mpos))); got_stats = got.stats
+    check(got, "pinned")
+    # compact input + narrow output, pinned
+    comp = {k: (None if v is None else _pinned_copy(arena, v)) for k, v in src.compact_arrays((mrow, mpos)).items()}
+    narrow = dict(dst_pos32=arena.take((n,), np.uint32), flags8=arena.take((n,), np.uint8), cig_len16=arena.take((n,), np.uint16),
+                  rr_len8=arena.take((n,), np.uint8), mate_dst_pos32=arena.take((n,), np.uint32))
+    pout.cig[:] = 0
+    got = idx.ctx.project(pb, pout, compact=comp, narrow=narrow); got_stats = got.stats
+    check(got, "compact + narrow", narrow)
+    # compact input, pageable output arrays
+    got = idx.ctx.project(src, compact=src.compact_arrays((mrow, mpos))); got_stats = got.stats
+    check(got, "compact pageable")
+    # a caller arena that is too small is reported with the size needed
+    from panvc3_b200.capi import Pv3Error, BatchIn, BatchOut
+    small = alloc_output(n, 1000, 4)
+    small.mate_dst_pos = np.zeros(n, np.uint64)
+    big = idx.ctx.project(src, small, mates=(mrow, mpos))       # the binding grows and retries
+    got_stats = big.stats
+    check(big, "grown after PV3_ERR_CAPACITY")
+
+
+def test_index_grows_after_commit_and_contigs_are_recycled(gpu, port):
+    """pv3_index_commit uploads only what was added since the last commit (the adapter registers entries lazily), and
+    pv3_index_remove_ref frees a contig whose id is then reused (forget_reference)."""
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import sample_reads, synth_msa
+    msa = synth_msa(30_000, 4, seed=17, p_gap=0.01, mean_gap=6, snp=0.01, anticorrelated=0.004)
+    idx = MsaIndex()
+    idx.add_entry("REF", msa.gap_words[0], msa.n_cols)
+    idx.add_entry("1", msa.gap_words[1], msa.n_cols)
+    junk = idx.add_reference(b"ACGT" * 100)
+    idx.commit()
+    idx.ctx.remove_ref(junk)
+    rid = idx.add_reference(msa.ungapped[0].tobytes())
+    assert rid == junk                                                           # the slot is reused
+    idx.commit()
+    oi = port.make_index(*casegen.index_inputs(msa))
+    b = sample_reads(msa, 5000, 150, seed=3, founders=[1], ins=0.003, dele=0.003)
+    b.dst_ref[:] = rid
+    exp = oi.project_batch(b, 0, -1)
+    assert_same(idx.project_batch(b, 0, -1), exp, b, "two rows")
+    # more rows after the first use: ids of the old ones are stable, results unchanged
+    for r in (2, 3, 4):
+        idx.add_entry(str(r), msa.gap_words[r], msa.n_cols)
+    idx.commit()
+    assert_same(idx.project_batch(b, 0, -1), exp, b, "after adding rows")
+    b2 = sample_reads(msa, 5000, 150, seed=4, founders=[2, 3, 4])
+    b2.dst_ref[:] = rid
+    assert_same(idx.project_batch(b2, 0, -1), oi.project_batch(b2, 0, -1), b2, "new rows")
+
+
+def test_multi_context_single_device_shards(gpu, port, workflow_msa):
+    """pv3_multi with every 'device' on GPU 0: shards, shard placement in the caller's arenas and absolute offsets are the
+    same code as with several GPUs (bench.py --gpus N and tests/cpp cover real multi-GPU runs)."""
+    from panvc3_b200.capi import MultiContext
+    from panvc3_b200.workload import sample_reads
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    b = sample_reads(workflow_msa, 90_000, 150, seed=91, ins=0.004, dele=0.004)
+    exp = oi.project_batch(b, -2, -1, n_threads=os.cpu_count() or 1)
+    for n_dev in (1, 3):
+        mc = MultiContext(n_dev, devices=[0] * n_dev)
+        for w in workflow_msa.gap_words:
+            mc.add_row(w, workflow_msa.n_cols)
+        for u in workflow_msa.ungapped:
+            mc.add_ref(u.tobytes())
+        mc.commit(); mc.set_params(-2, -1)
+        got = mc.project(b)
+        assert_same(got, exp, b, f"multi x{n_dev}")
+        # record order inside every shard
+        cuts = [(b.n * g // n_dev) // 128 * 128 for g in range(n_dev)] + [b.n]
+        for g in range(n_dev):
+            o, l = got.cig_off[cuts[g]:cuts[g + 1]], got.cig_len[cuts[g]:cuts[g + 1]]
+            assert np.array_equal(o - o[0], _exclusive(l))
+        mc.close()
