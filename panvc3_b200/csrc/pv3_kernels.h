@@ -84,7 +84,11 @@ __host__ __device__ inline bool dp_job_is_small(uint32_t R, uint32_t Q)
 // Run count of a batch: given by the host, or (~0) read from the counters the rewrite kernels filled on the same stream.
 __device__ __forceinline__ uint64_t dp_n_jobs(const Counters *c, uint64_t host_value)
 {
-	return host_value == ~0ull ? (uint64_t) *((volatile const unsigned long long *) &c->job_cursor) : host_value;
+	if (host_value != ~0ull) return host_value;
+	// an arena or the run list overflowed in the rewrite: runs beyond the list's capacity were not written — nothing to do
+	// here, the host sizes the buffers from the counters and repeats the batch
+	if (*((volatile const unsigned int *) &c->overflow) & 3u) return 0;
+	return (uint64_t) *((volatile const unsigned long long *) &c->job_cursor);
 }
 // Small runs go to the thread-per-run kernel once a batch holds at least dp_thread_min of them; both DP kernels evaluate this.
 __device__ __forceinline__ bool dp_use_thread_kernel(const Counters *c, uint64_t n_jobs, uint64_t dp_thread_min)

@@ -681,7 +681,7 @@ def test_ordered_compact_output_and_mates(gpu, port, workflow_msa, packed_seq):
     got = idx.ctx.project(src, mates=(mrow, mpos)); got_stats = got.stats
     check(got, "pageable")
     # pinned: results written in place by the pack kernel
-    arena = PinnedArena(idx.ctx.lib, src.input_bytes() + n * 64 + int(exp.cig_len.sum()) * 8 + 1 << 22)
+    arena = PinnedArena(idx.ctx.lib, src.input_bytes() + n * 64 + int(exp.cig_len.sum()) * 8 + (1 << 24))
     pb = RecordBatch.__new__(RecordBatch)
     for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
         a = getattr(src, k)
