@@ -141,6 +141,7 @@ struct UnpackParams {
 struct ChunkReport {
 	unsigned long long cig_used, rr_used, n_flagged, n_realigned, dp_cells, dp_path, dp_max_pool, arena_need, jobs, n_deferred;
 	unsigned long long cig_base, rr_base;   // the chunk's place in the call's ordered arenas
+	unsigned long long cig_pad;             // staged output: words in front of the chunk's ops in the staging buffer
 	unsigned int       overflow;  // bits 0-3 as Counters::overflow (8: HBM trace slots), 16 / 32: caller's cig / rr capacity, 64: compact field
 	unsigned int       done;
 };
@@ -164,7 +165,20 @@ struct PackParams {
 	uint64_t *out_mate_dst_pos; uint32_t *out_mate_dst_pos32;
 	uint64_t  cig_off_bias, rr_off_bias;   // added to the stored offsets (pv3_multi: where the shard's arenas start in the caller's arrays)
 	int       staged;         // 1: out_cig / out_rr are staging buffers of this chunk (index 0 = the chunk's place)
+	uint64_t  cig_dst_word0;  // staged: (address of the destination's word 0 of this context's arena) / 4 — the staging copy keeps the
+	                          // destination's alignment modulo 16 bytes so that it can be streamed out with 16-byte stores
 };
+
+// Staged ordered output of a chunk → the caller's pinned arrays, with coalesced 16-byte stores (full PCIe write
+// transactions; per-record stores straight into mapped memory reached 4 GB/s, this reaches the link's rate).
+struct StreamOutParams {
+	struct Seg { void *dst; const void *src; uint64_t bytes; } seg[12];
+	int             n_seg;
+	uint32_t       *cig_dst;  const uint32_t *cig_src;      // dst: word 0 of this context's arena in the caller's array
+	uint64_t       *rr_dst;   const uint64_t *rr_src;
+	const uint64_t *place;    // [0] cig base, [1] rr base, [2] overflow, [3] cig words, [4] runs, [5] cig pad
+};
+void launch_stream_out(const StreamOutParams &P, cudaStream_t stream);
 uint64_t pack_tiles(uint64_t n);
 void launch_unpack_in(const UnpackParams &P, cudaStream_t stream);
 void launch_pack_out(const PackParams &P, cudaStream_t stream);

@@ -141,12 +141,13 @@ __global__ void pack_place_kernel(PackParams P, const uint64_t *totals /* [3] */
 	unsigned ovf = c.overflow;
 	if (cig_base + cig_n > P.out_cig_cap) ovf |= 16u;
 	if (rr_base + rr_n > P.out_rr_cap) ovf |= 32u;
-	P.place[0] = cig_base; P.place[1] = rr_base; P.place[2] = ovf;
+	uint64_t const pad = P.staged ? ((P.cig_dst_word0 + cig_base) & 3ull) : 0ull;
+	P.place[0] = cig_base; P.place[1] = rr_base; P.place[2] = ovf; P.place[3] = cig_n; P.place[4] = rr_n; P.place[5] = pad;
 	P.running[0] = cig_base + cig_n; P.running[1] = rr_base + rr_n;
 	ChunkReport r;
 	r.cig_used = cig_n; r.rr_used = rr_n; r.n_flagged = c.n_flagged; r.n_realigned = c.n_realigned; r.dp_cells = c.dp_cells;
 	r.dp_path = c.dp_path; r.dp_max_pool = c.dp_max_pool; r.arena_need = c.arena_cursor + c.dp_path; r.jobs = c.job_cursor;
-	r.n_deferred = c.n_deferred; r.cig_base = cig_base; r.rr_base = rr_base; r.overflow = ovf; r.done = 1;
+	r.n_deferred = c.n_deferred; r.cig_base = cig_base; r.rr_base = rr_base; r.cig_pad = pad; r.overflow = ovf; r.done = 1;
 	*P.report = r;
 }
 
@@ -166,7 +167,7 @@ __global__ void __launch_bounds__(PK_THREADS) pack_write_kernel(PackParams P)
 	uint64_t ta, tb;
 	uint64_t ea = block_excl_scan(a, sm[0], ta) + P.tile_sums[3 * blockIdx.x] + P.place[0];
 	uint64_t eb = block_excl_scan(b, sm[1], tb) + P.tile_sums[3 * blockIdx.x + 1] + P.place[1];
-	uint64_t const wa = P.staged ? P.place[0] : 0, wb = P.staged ? P.place[1] : 0;   // staging buffers start at the chunk's place
+	uint64_t const wa = P.staged ? P.place[0] - P.place[5] : 0, wb = P.staged ? P.place[1] : 0;   // staging buffers start at the chunk's place (+ pad)
 	#pragma unroll
 	for (int k = 0; k < PK_PER; ++k) {
 		uint64_t const i = i0 + k;
@@ -196,7 +197,36 @@ __global__ void __launch_bounds__(PK_THREADS) pack_write_kernel(PackParams P)
 	}
 }
 
+// bytes from src to dst where (dst - src) is a multiple of 16: byte head, 16-byte body, byte tail; any other pair: bytes
+__device__ void stream_copy(uint8_t *dst, const uint8_t *src, uint64_t bytes, uint64_t tid, uint64_t n_threads)
+{
+	if (!bytes) return;
+	if (((uintptr_t) dst - (uintptr_t) src) & 15u) { for (uint64_t i = tid; i < bytes; i += n_threads) dst[i] = src[i]; return; }
+	uint64_t head = (16u - ((uintptr_t) dst & 15u)) & 15u;
+	if (head > bytes) head = bytes;
+	uint64_t const body = (bytes - head) / 16, tail0 = head + body * 16;
+	if (tid < head) dst[tid] = src[tid];
+	const uint4 *s4 = reinterpret_cast <const uint4 *>(src + head);
+	uint4 *d4 = reinterpret_cast <uint4 *>(dst + head);
+	for (uint64_t i = tid; i < body; i += n_threads) d4[i] = s4[i];
+	if (tid < bytes - tail0) dst[tail0 + tid] = src[tail0 + tid];
+}
+
+__global__ void __launch_bounds__(256) stream_out_kernel(StreamOutParams P)
+{
+	if (P.place[2] & (1u | 2u | 4u | 8u | 16u | 32u)) return;
+	uint64_t const tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x, nt = (uint64_t) gridDim.x * blockDim.x;
+	for (int s = 0; s < P.n_seg; ++s) stream_copy((uint8_t *) P.seg[s].dst, (const uint8_t *) P.seg[s].src, P.seg[s].bytes, tid, nt);
+	if (P.cig_dst) stream_copy((uint8_t *) (P.cig_dst + P.place[0]), (const uint8_t *) (P.cig_src + P.place[5]), P.place[3] * 4, tid, nt);
+	if (P.rr_dst) stream_copy((uint8_t *) (P.rr_dst + 4 * P.place[1]), (const uint8_t *) P.rr_src, P.place[4] * 32, tid, nt);
+}
+
 } // namespace
+
+void launch_stream_out(const StreamOutParams &P, cudaStream_t stream)
+{
+	stream_out_kernel<<<96, 256, 0, stream>>>(P);
+}
 
 uint64_t pack_tiles(uint64_t n) { return (n + PK_TILE - 1) / PK_TILE; }
 

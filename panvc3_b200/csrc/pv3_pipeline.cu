@@ -408,16 +408,10 @@ int host_enqueue(HostCall &hc)
 		if (!K.report) return fail(ctx, PV3_ERR_CUDA, "pv3_project: report buffer is not mapped");
 		K.out_cig_cap = hc.cig_room; K.out_rr_cap = hc.rr_room;
 		K.cig_off_bias = hc.cig_place; K.rr_off_bias = hc.rr_place;
-		if (zero_copy) {
-			K.out_dst_pos = (uint64_t *) d_dst_pos.alias; K.out_dst_pos32 = (uint32_t *) d_dst_pos32.alias;
-			K.out_flags = (uint32_t *) d_flags.alias; K.out_flags8 = (uint8_t *) d_flags8.alias;
-			K.out_cig_off = (uint64_t *) d_cig_off.alias; K.out_cig_len = (uint32_t *) d_cig_len.alias; K.out_cig_len16 = (uint16_t *) d_cig_len16.alias;
-			K.out_cig = d_cig.alias ? (uint32_t *) d_cig.alias + hc.cig_place : nullptr;
-			K.out_rr_off = (uint64_t *) d_rr_off.alias; K.out_rr_len = (uint32_t *) d_rr_len.alias; K.out_rr_len8 = (uint8_t *) d_rr_len8.alias;
-			K.out_rr = d_rr.alias ? (uint64_t *) d_rr.alias + 4 * hc.rr_place : nullptr;
-			K.out_mate_dst_pos = (uint64_t *) d_mate.alias; K.out_mate_dst_pos32 = (uint32_t *) d_mate32.alias;
-		} else {
-			// device staging laid out like the caller's arrays for this chunk: record fields indexed from rec0, arenas from the chunk's place
+		{
+			// Ordered output of the chunk in device staging laid out like the caller's arrays: record fields indexed from 0, the arenas
+			// from the chunk's place. It leaves either with the coalesced copy kernel (pinned destination: no host round trip) or,
+			// after a synchronisation, with plain copies (pageable destination).
 			size_t const sizes[12] = { m * 8, m * 4, m * 4, m, m * 8, m * 4, m * 2, m * 8, m * 4, m, m * 8, m * 4 };
 			for (int i = 0; i < 12; ++i) PV3_CUDA(ctx, ws.st[i].ensure_idle(sizes[i] + 64, stream));
 			K.rec0 = 0;
@@ -428,10 +422,10 @@ int host_enqueue(HostCall &hc)
 			K.out_rr_off = out->rr_off ? ws.st[7].as <uint64_t>() : nullptr; K.out_rr_len = out->rr_len ? ws.st[8].as <uint32_t>() : nullptr;
 			K.out_rr_len8 = out->rr_len8 ? ws.st[9].as <uint8_t>() : nullptr;
 			K.out_mate_dst_pos = out->mate_dst_pos ? ws.st[10].as <uint64_t>() : nullptr; K.out_mate_dst_pos32 = out->mate_dst_pos32 ? ws.st[11].as <uint32_t>() : nullptr;
-			// the ordered arenas of the chunk go back into its own (unordered) arena space's twin: a second pair of buffers
-			PV3_CUDA(ctx, ws.un[9].ensure_idle(arena_cap * 4 + rr_cap * 32 + 64, stream));
-			K.out_cig = ws.un[9].as <uint32_t>(); K.out_rr = (uint64_t *) (ws.un[9].as <uint8_t>() + align_up(arena_cap * 4, 32));
+			PV3_CUDA(ctx, ws.un[9].ensure_idle(arena_cap * 4 + rr_cap * 32 + 128, stream));
+			K.out_cig = ws.un[9].as <uint32_t>(); K.out_rr = (uint64_t *) (ws.un[9].as <uint8_t>() + align_up(arena_cap * 4 + 16, 32));
 			K.staged = 1;
+			K.cig_dst_word0 = zero_copy ? (((uint64_t) (uintptr_t) d_cig.alias) >> 2) + hc.cig_place : 0;
 		}
 		PV3_CUDA(ctx, cudaStreamWaitEvent(stream, c == 0 ? ctx->ev_misc[2] : ctx->sets[(c - 1) % 2].ev[5], 0));
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[2], stream));
@@ -439,6 +433,24 @@ int host_enqueue(HostCall &hc)
 		PV3_CUDA(ctx, cudaGetLastError());
 		hc.launches += 4;
 		PV3_CUDA(ctx, cudaEventRecord(ws.ev[5], stream));
+		if (zero_copy) {
+			StreamOutParams S;
+			memset(&S, 0, sizeof S);
+			auto seg = [&](void *alias, const void *src, size_t elem) {
+				if (!alias || !src) return;
+				S.seg[S.n_seg].dst = (uint8_t *) alias + b * elem; S.seg[S.n_seg].src = src; S.seg[S.n_seg].bytes = m * elem; ++S.n_seg;
+			};
+			seg(d_dst_pos.alias, K.out_dst_pos, 8); seg(d_dst_pos32.alias, K.out_dst_pos32, 4); seg(d_flags.alias, K.out_flags, 4); seg(d_flags8.alias, K.out_flags8, 1);
+			seg(d_cig_off.alias, K.out_cig_off, 8); seg(d_cig_len.alias, K.out_cig_len, 4); seg(d_cig_len16.alias, K.out_cig_len16, 2);
+			seg(d_rr_off.alias, K.out_rr_off, 8); seg(d_rr_len.alias, K.out_rr_len, 4); seg(d_rr_len8.alias, K.out_rr_len8, 1);
+			seg(d_mate.alias, K.out_mate_dst_pos, 8); seg(d_mate32.alias, K.out_mate_dst_pos32, 4);
+			S.cig_dst = d_cig.alias ? (uint32_t *) d_cig.alias + hc.cig_place : nullptr; S.cig_src = K.out_cig;
+			S.rr_dst = d_rr.alias ? (uint64_t *) d_rr.alias + 4 * hc.rr_place : nullptr; S.rr_src = K.out_rr;
+			S.place = K.place;
+			launch_stream_out(S, stream);
+			PV3_CUDA(ctx, cudaGetLastError());
+			hc.launches += 1;
+		}
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[3], stream));
 
 		if (!zero_copy) {
@@ -455,7 +467,7 @@ int host_enqueue(HostCall &hc)
 				{ out->rr_off ? out->rr_off + b : nullptr, K.out_rr_off, m * 8 }, { out->rr_len ? out->rr_len + b : nullptr, K.out_rr_len, m * 4 },
 				{ out->rr_len8 ? out->rr_len8 + b : nullptr, K.out_rr_len8, m },
 				{ out->mate_dst_pos ? out->mate_dst_pos + b : nullptr, K.out_mate_dst_pos, m * 8 }, { out->mate_dst_pos32 ? out->mate_dst_pos32 + b : nullptr, K.out_mate_dst_pos32, m * 4 },
-				{ out->cig ? out->cig + hc.cig_place + cb : nullptr, K.out_cig, report->cig_used * 4 },
+				{ out->cig ? out->cig + hc.cig_place + cb : nullptr, K.out_cig + report->cig_pad, report->cig_used * 4 },
 				{ out->rr ? out->rr + 4 * (hc.rr_place + rb) : nullptr, K.out_rr, report->rr_used * 32 },
 			};
 			for (auto const &bk : backs)
