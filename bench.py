@@ -513,6 +513,10 @@ def run_gpu_arm(args) -> None:
     seg = None
     out_alloc = None
     if world > 1:
+        # one layout for every rank's slice of the shared output: capacities are the maximum over the ranks
+        caps = torch.tensor([cig_cap, rr_cap], dtype=torch.int64, device=dev)
+        dist.all_reduce(caps, op=dist.ReduceOp.MAX)
+        cig_cap, rr_cap = int(caps[0]), int(caps[1])
         seg, whole, mine, out_alloc, per_rank = shared_output_views(n, cig_cap, rr_cap, world, rank, dist, ctx.lib)
     hb = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=True, packed=True, out_view=out_alloc)
     for _ in range(max(args.warmup, 1)):
