@@ -283,6 +283,17 @@ int pv3_msa_row_extract(pv3_ctx *, const char *text, uint64_t n, uint64_t *gap_w
 int pv3_msa_row_extract_device(pv3_ctx *, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped,
                                uint64_t *n_ungapped /* host */);
 
+/* No counterpart in the reference. pv3_msa_row_extract_device for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): needs no context and
+ * allocates nothing — the kernels' scratch (tile counts and offsets) lives in a fixed array in device memory (768 KiB, held by
+ * every GPU that loads the library until exit), which limits a call to 2^30 columns (PV3_ERR_CAPACITY beyond; message through
+ * pv3_last_error(NULL)). All pointers are device pointers on `device`, aligned as for pv3_msa_row_extract_device;
+ * n_ungapped (8 bytes, may be NULL) is a DEVICE pointer too. Asynchronous on cuda_stream (a cudaStream_t; NULL = the default
+ * stream), no synchronisation. All calls on a device share the scratch: calls that overlap on the GPU (different streams
+ * without ordering) race. */
+int pv3_msa_row_extract_noalloc(int device, void *cuda_stream, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped,
+                                uint64_t *n_ungapped /* device */);
+
 /* -- MSA index file (host only, no GPU needed) ---------------------------------------------------------------------------
  * The file `panvc3 index-msa` writes and `project-alignments --msa-index` reads: panvc3::msa_index through
  * cereal::PortableBinary{Output,Input}Archive (include/panvc3/msa_index.hh:40-192; written at

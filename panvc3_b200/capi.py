@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = [
     "pv3_rescore_alignments", "pv3_calculate_mapq",
     "pv3_index_remove_ref", "pv3_project_positions_device", "pv3_host_register", "pv3_host_unregister",
     "pv3_multi_create", "pv3_multi_destroy", "pv3_multi_devices", "pv3_multi_ctx", "pv3_multi_project", "pv3_multi_last_error",
+    "pv3_msa_row_extract_noalloc",
 ]
 
 
@@ -114,6 +115,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.pv3_multi_project.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut)]
     lib.pv3_multi_last_error.argtypes = [C.c_void_p]
     lib.pv3_multi_last_error.restype = C.c_char_p
+    lib.pv3_msa_row_extract_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.pv3_index_query.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.pv3_get_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
     lib.pv3_total_launches.argtypes = [C.c_void_p]

@@ -10,8 +10,11 @@
 // 32-bit words; it walks the row backwards so that the tail of pass 1's reads is still in the L2.
 // (A single-pass variant with a decoupled look-back measured 0.30 ms per 256 MiB row on B200 against 0.07 ms for pass 1
 // alone: each CTA sat on its registers for the look-back's L2 round trips. Two passes re-read the text but never wait.)
+#include <mutex>
+
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
+#include "pv3_ctx.h"
 
 namespace pv3 {
 
@@ -258,4 +261,61 @@ cudaError_t launch_msa_extract(const char *text, uint64_t n, uint64_t *gap_words
 	return cudaGetLastError();
 }
 
+// ---- allocation-free entry point (no counterpart in the reference) ------------
+// Callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it) get the
+// row extraction with its scratch — tile counts and tile offsets — in a file-scope device array instead of a context buffer.
+// Every GPU that loads the library holds the array until exit; every call on a device shares it (calls that overlap on the
+// GPU race) and it keeps the last call's contents: each call rewrites all words it reads (the tile counts of all its tiles,
+// the offsets, the total) before reading them.
+namespace {
+
+constexpr uint64_t NOALLOC_MAX_COLUMNS = 1ull << 30;                       // 65536 tiles of 16 KiB
+constexpr uint64_t NOALLOC_SCRATCH_WORDS = ((NOALLOC_MAX_COLUMNS / EX_TILE + 3) / 4 * 2) + NOALLOC_MAX_COLUMNS / EX_TILE + 1 + 3;   // 768 KiB
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned long long *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};              // device address of the array, per device
+std::mutex g_noalloc_mutex;
+
+// In host code `g_noalloc_scratch` is only a handle: its device address must come from cudaGetSymbolAddress, once per
+// device, with that device current.
+cudaError_t noalloc_scratch(int device, unsigned long long **out)
+{
+	std::lock_guard <std::mutex> lock(g_noalloc_mutex);
+	if (!g_noalloc_addr[device]) {
+		void *p = nullptr;
+		cudaError_t const e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+		if (e != cudaSuccess) return e;
+		g_noalloc_addr[device] = (unsigned long long *) p;
+	}
+	*out = g_noalloc_addr[device];
+	return cudaSuccess;
+}
+
+} // namespace
+
 } // namespace pv3
+
+extern "C" int pv3_msa_row_extract_noalloc(int device, void *cuda_stream, const char *text, uint64_t n, uint64_t *gap_words, char *ungapped,
+	uint64_t *n_ungapped)
+{
+	using namespace pv3;
+	if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(nullptr, PV3_ERR_INVALID, "pv3_msa_row_extract_noalloc: device %d out of range", device);
+	if (n > NOALLOC_MAX_COLUMNS)
+		return fail(nullptr, PV3_ERR_CAPACITY, "pv3_msa_row_extract_noalloc: %llu columns exceed the fixed scratch (at most %llu columns per call); use pv3_msa_row_extract_device",
+			(unsigned long long) n, (unsigned long long) NOALLOC_MAX_COLUMNS);
+	if (n && (!text || !gap_words)) return fail(nullptr, PV3_ERR_INVALID, "pv3_msa_row_extract_noalloc: NULL argument");
+	if ((uintptr_t) text % 16 || (uintptr_t) gap_words % 8 || (uintptr_t) ungapped % 4 || (uintptr_t) n_ungapped % 8)
+		return fail(nullptr, PV3_ERR_INVALID, "pv3_msa_row_extract_noalloc: text must be 16-byte, gap_words and n_ungapped 8-byte, ungapped 4-byte aligned");
+	cudaError_t e = cudaSetDevice(device);
+	unsigned long long *scratch = nullptr;
+	if (e == cudaSuccess) e = noalloc_scratch(device, &scratch);
+	if (e != cudaSuccess) return fail(nullptr, PV3_ERR_CUDA, "pv3_msa_row_extract_noalloc: %s", cudaGetErrorString(e));
+	cudaStream_t const stream = (cudaStream_t) cuda_stream;
+	e = launch_msa_extract(text, n, gap_words, ungapped, scratch, stream, nullptr);
+	if (e == cudaSuccess && n_ungapped)
+		e = cudaMemcpyAsync(n_ungapped, scratch + msa_extract_total_word(n), 8, cudaMemcpyDeviceToDevice, stream);
+	if (e != cudaSuccess) return fail(nullptr, PV3_ERR_CUDA, "pv3_msa_row_extract_noalloc: %s", cudaGetErrorString(e));
+	return PV3_OK;
+}
+
