@@ -11,8 +11,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpanvc3_b200.so")
-SOURCES = ["pv3_api.cu", "pv3_pipeline.cu", "pv3_rewrite.cu", "pv3_rewrite_thread.cu", "pv3_rewrite_word.cu", "pv3_realign.cu", "pv3_realign_thread.cu", "pv3_splice.cu", "pv3_pack.cu", "pv3_msa_build.cu", "pv3_annotate.cu", "pv3_mapq.cu", "pv3_index_file.cc"]
-HEADERS = ["pv3_device.cuh", "pv3_kernels.h", "pv3_runs.cuh", "pv3_k1w_core.h", "pv3_index_build.h", "pv3_ctx.h", os.path.join("..", "..", "include", "panvc3_b200.h")]
+SOURCES = ["pv3_api.cu", "pv3_pipeline.cu", "pv3_rewrite.cu", "pv3_rewrite_thread.cu", "pv3_rewrite_word.cu", "pv3_rewrite_seg.cu", "pv3_realign.cu", "pv3_realign_thread.cu", "pv3_splice.cu", "pv3_pack.cu", "pv3_msa_build.cu", "pv3_annotate.cu", "pv3_mapq.cu", "pv3_index_file.cc"]
+HEADERS = ["pv3_device.cuh", "pv3_kernels.h", "pv3_runs.cuh", "pv3_k1w_core.h", "pv3_segment_core.h", "pv3_index_build.h", "pv3_ctx.h", os.path.join("..", "..", "include", "panvc3_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

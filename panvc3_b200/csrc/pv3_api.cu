@@ -25,6 +25,7 @@ namespace pv3 {
 void WorkSet::release()
 {
 	for (DevBuf *b : { &counters, &jobs, &dp_arena, &pool, &deferred, &complex_list, &complex_ce, &big_list, &place, &scratch,
+			&deferred2, &plan_rec, &plan_seg0, &plan_nseg, &segs, &seg_out, &seg_ops,
 			&out_dst_pos, &out_flags, &out_cig_off, &out_cig_len, &out_arena, &out_rr_off, &out_rr_len, &out_rr, &out_mate }) b->release();
 	for (auto &b : in) b.release();
 	for (auto &b : un) b.release();

@@ -44,6 +44,8 @@ struct WorkSet {
 	cudaEvent_t  ev[6] = {};            // 0 kernels start, 1 rewrite end, 2 realign end, 3 splice end, 4 main rewrite kernel end, 5 pack end
 	cudaEvent_t  cev[4] = {};           // H2D begin / end, write-back begin / end
 	DevBuf   counters, jobs, dp_arena, pool, deferred, complex_list, complex_ce, big_list, place, scratch;
+	DevBuf   deferred2, plan_rec, plan_seg0, plan_nseg, segs, seg_out, seg_ops;       // long records as segments
+	uint64_t seg_cap = 0, seg_ops_cap = 0, seg_cap_hint = 0, seg_ops_hint = 0;
 	uint64_t pool_slot = 0, pool_slots = 0;
 	// chunk inputs (as uploaded), unpacked inputs (compact encoding), per-record outputs, arenas, staged ordered output
 	DevBuf   in[16], un[10], out_dst_pos, out_flags, out_cig_off, out_cig_len, out_arena, out_rr_off, out_rr_len, out_rr, out_mate;

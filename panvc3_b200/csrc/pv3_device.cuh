@@ -65,11 +65,15 @@ struct Counters {
 	unsigned long long dp_arena_cursor;
 	unsigned long long job_ticket;     // work-stealing counter of the DP kernel
 	unsigned long long n_deferred;     // records the thread-per-record kernel handed to the warp-per-record kernel
-	unsigned int       overflow;       // bit0: CIGAR arena, bit1: rr/jobs, bit2: DP op arena
+	unsigned int       overflow;       // bit0: CIGAR arena, bit1: rr/jobs, bit2: DP op arena, bit3: HBM trace slots, bit7: segment list, bit8: segment op arena
 	unsigned int       pad;
 	unsigned long long n_big_jobs;     // runs too large for the thread-per-run DP kernel (the warp-per-run kernel takes them)
 	unsigned long long big_cursor;     // entries of the big-run list written by the thread-per-run kernel
 	unsigned long long n_complex;      // records with I S H P D N ops the first launch of the word kernel left to the second
+	unsigned long long n_planned;      // deferred records cut into segments (pv3_rewrite_seg.cu)
+	unsigned long long seg_cursor;     // segments planned (the number NEEDED, also when the list overflowed)
+	unsigned long long seg_ops_cursor; // words of the segment op arena handed out (likewise)
+	unsigned long long n_deferred2;    // records left to the warp-per-record kernel after the segment pass
 };
 
 // BAM op codes

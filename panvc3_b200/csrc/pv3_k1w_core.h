@@ -45,8 +45,8 @@ namespace pv3 {
 namespace k1w {
 
 constexpr int      NW    = 10;          // 32-column words per span: 320 columns including the offset of c0 in its word
-constexpr int      NBRK  = 6;           // pass-through ops (I S H P with a non-zero count) per record / segment
-constexpr int      OUTQ  = 24;          // staged output ops per record / segment
+constexpr int      NBRK  = 12;          // pass-through ops (I S H P with a non-zero count) per record / segment
+constexpr int      OUTQ  = 32;         // staged output ops per record / segment
 constexpr uint32_t QMAX  = 192;         // query bases per record / segment
 constexpr uint32_t CLAMP = 1u << 20;
 constexpr uint32_t NOBRK = 0xffffffffu;

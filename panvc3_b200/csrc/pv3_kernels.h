@@ -40,6 +40,13 @@ struct K1Params {
 	uint64_t       *deferred;    // thread kernel: records it could not handle (capacity n)
 	uint64_t       *complex_list;// word kernel: records with events, handled by its second launch (capacity n)
 	uint64_t       *complex_ce;  // word kernel: start column and projected position of those records (2 per entry)
+	// long records as segments (pv3_segment_core.h): plan → segment kernel → assembly; what fails there goes to deferred2
+	uint64_t       *plan_rec, *plan_seg0; uint32_t *plan_nseg;     // per planned record: record, first segment, segment count (capacity n)
+	void           *segs;        // seg::SegDesc[seg_cap]
+	void           *seg_out;     // seg::SegOut[seg_cap]
+	uint64_t        seg_cap;
+	uint32_t       *seg_ops; uint64_t seg_ops_cap;                 // segment op arena
+	uint64_t       *deferred2;   // capacity n
 	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
 	uint64_t        rr_base;     // added to every stored rr_off
 };
@@ -142,6 +149,7 @@ struct ChunkReport {
 	unsigned long long cig_used, rr_used, n_flagged, n_realigned, dp_cells, dp_path, dp_max_pool, arena_need, jobs, n_deferred;
 	unsigned long long cig_base, rr_base;   // the chunk's place in the call's ordered arenas
 	unsigned long long cig_pad;             // staged output: words in front of the chunk's ops in the staging buffer
+	unsigned long long seg_need, seg_ops_need;
 	unsigned int       overflow;  // bits 0-3 as Counters::overflow (8: HBM trace slots), 16 / 32: caller's cig / rr capacity, 64: compact field
 	unsigned int       done;
 };
@@ -185,7 +193,10 @@ void launch_pack_out(const PackParams &P, cudaStream_t stream);
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
 void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record, run walk (v4-v13)
-void launch_k1_word(const K1Params &P, int n_sms, cudaStream_t stream);     // thread per record, word-parallel (v14; default)
+void launch_k1_word(const K1Params &P, int n_sms, cudaStream_t stream);
+// the deferred list of either thread kernel cut into segments of <= 64 reference bases, one thread per segment (long reads)
+void launch_k1_segments(const K1Params &P, int n_sms, cudaStream_t stream);     // plan + segment kernels (pv3_rewrite_seg.cu)
+void launch_k1_assemble(const K1Params &P, int n_sms, cudaStream_t stream);     // concatenation, run detection, outputs (pv3_rewrite.cu)     // thread per record, word-parallel (v14; default)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
 void launch_k3_thread(const K3Params &P, cudaStream_t stream);               // thread per run (small runs)
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);

@@ -147,14 +147,14 @@ __global__ void pack_place_kernel(PackParams P, const uint64_t *totals /* [3] */
 	ChunkReport r;
 	r.cig_used = cig_n; r.rr_used = rr_n; r.n_flagged = c.n_flagged; r.n_realigned = c.n_realigned; r.dp_cells = c.dp_cells;
 	r.dp_path = c.dp_path; r.dp_max_pool = c.dp_max_pool; r.arena_need = c.arena_cursor + c.dp_path; r.jobs = c.job_cursor;
-	r.n_deferred = c.n_deferred; r.cig_base = cig_base; r.rr_base = rr_base; r.cig_pad = pad; r.overflow = ovf; r.done = 1;
+	r.n_deferred = c.n_deferred; r.cig_base = cig_base; r.rr_base = rr_base; r.cig_pad = pad; r.seg_need = c.seg_cursor; r.seg_ops_need = c.seg_ops_cursor; r.overflow = ovf; r.done = 1;
 	*P.report = r;
 }
 
 __global__ void __launch_bounds__(PK_THREADS) pack_write_kernel(PackParams P)
 {
 	__shared__ uint64_t sm[2][9];
-	if (P.place[2] & ~0u & (1u | 2u | 4u | 8u | 16u | 32u)) return;       // a capacity was exceeded: the host grows and re-runs
+	if (P.place[2] & (1u | 2u | 4u | 8u | 16u | 32u | 128u | 256u)) return;       // a capacity was exceeded: the host grows and re-runs
 	uint64_t const i0 = (uint64_t) blockIdx.x * PK_TILE + (uint64_t) threadIdx.x * PK_PER;
 	uint32_t la[PK_PER], lb[PK_PER];
 	uint64_t a = 0, b = 0;
@@ -214,7 +214,7 @@ __device__ void stream_copy(uint8_t *dst, const uint8_t *src, uint64_t bytes, ui
 
 __global__ void __launch_bounds__(256) stream_out_kernel(StreamOutParams P)
 {
-	if (P.place[2] & (1u | 2u | 4u | 8u | 16u | 32u)) return;
+	if (P.place[2] & (1u | 2u | 4u | 8u | 16u | 32u | 128u | 256u)) return;
 	uint64_t const tid = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x, nt = (uint64_t) gridDim.x * blockDim.x;
 	for (int s = 0; s < P.n_seg; ++s) stream_copy((uint8_t *) P.seg[s].dst, (const uint8_t *) P.seg[s].src, P.seg[s].bytes, tid, nt);
 	if (P.cig_dst) stream_copy((uint8_t *) (P.cig_dst + P.place[0]), (const uint8_t *) (P.cig_src + P.place[5]), P.place[3] * 4, tid, nt);

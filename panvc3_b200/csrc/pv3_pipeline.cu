@@ -38,6 +38,17 @@ int ensure_work(pv3_ctx *ctx, WorkSet &ws, uint64_t n, uint64_t rr_cap)
 	PV3_CUDA(ctx, ws.deferred.ensure_idle(n * 8 + 8, s));
 	PV3_CUDA(ctx, ws.complex_list.ensure_idle(n * 8 + 8, s));
 	PV3_CUDA(ctx, ws.complex_ce.ensure_idle(n * 16 + 16, s));
+	PV3_CUDA(ctx, ws.deferred2.ensure_idle(n * 8 + 8, s));
+	PV3_CUDA(ctx, ws.plan_rec.ensure_idle(n * 8 + 8, s));
+	PV3_CUDA(ctx, ws.plan_seg0.ensure_idle(n * 8 + 8, s));
+	PV3_CUDA(ctx, ws.plan_nseg.ensure_idle(n * 4 + 8, s));
+	{
+		uint64_t const seg_cap = std::max <uint64_t>(ws.seg_cap_hint, n / 8 + 4096), seg_ops_cap = std::max <uint64_t>(ws.seg_ops_hint, n + 65536);
+		PV3_CUDA(ctx, ws.segs.ensure_idle(seg_cap * 40, s));
+		PV3_CUDA(ctx, ws.seg_out.ensure_idle(seg_cap * 16, s));
+		PV3_CUDA(ctx, ws.seg_ops.ensure_idle(seg_ops_cap * 4, s));
+		ws.seg_cap = seg_cap; ws.seg_ops_cap = seg_ops_cap;
+	}
 	uint64_t const dp_words = std::max <uint64_t>(ws.dp_arena_hint, n / 4 + 4096);
 	PV3_CUDA(ctx, ws.dp_arena.ensure_idle((dp_words + 1) * 4, s));
 	if (ws.pool_hint) {
@@ -77,6 +88,10 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 	P.deferred = ws.deferred.as <uint64_t>();
 	P.complex_list = ws.complex_list.as <uint64_t>();
 	P.complex_ce = ws.complex_ce.as <uint64_t>();
+	P.plan_rec = ws.plan_rec.as <uint64_t>(); P.plan_seg0 = ws.plan_seg0.as <uint64_t>(); P.plan_nseg = ws.plan_nseg.as <uint32_t>();
+	P.segs = ws.segs.p; P.seg_out = ws.seg_out.p; P.seg_cap = ws.seg_cap;
+	P.seg_ops = ws.seg_ops.as <uint32_t>(); P.seg_ops_cap = ws.seg_ops_cap;
+	P.deferred2 = ws.deferred2.as <uint64_t>();
 	P.arena_off = B.arena_off; P.rr_base = B.rr_base;
 
 	PV3_CUDA(ctx, cudaMemsetAsync(ws.counters.p, 0, sizeof(Counters), stream));
@@ -91,9 +106,21 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		else launch_k1_thread(P, ctx->n_sms, ctx->target_code_bytes, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ws.ev[4], stream));
+		// what the thread kernel could not take (long reads above all): cut into segments, one thread per segment, reassembled by
+		// a warp per record; whatever fails there is left to the warp-per-record kernel. All list lengths are read on the device.
 		K1Params P2 = P;
-		P2.rec_list = ws.deferred.as <uint64_t>();
-		P2.n_list_dev = &ws.counters.as <Counters>()->n_deferred;
+		bool const use_segments = !getenv("PV3_NO_SEGMENTS");
+		if (use_segments) {
+			launch_k1_segments(P, ctx->n_sms, stream);
+			launch_k1_assemble(P, ctx->n_sms, stream);
+			PV3_CUDA(ctx, cudaGetLastError());
+			P2.rec_list = ws.deferred2.as <uint64_t>();
+			P2.n_list_dev = &ws.counters.as <Counters>()->n_deferred2;
+			launches += 3;
+		} else {
+			P2.rec_list = ws.deferred.as <uint64_t>();
+			P2.n_list_dev = &ws.counters.as <Counters>()->n_deferred;
+		}
 		launch_k1(P2, ctx->n_sms, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		launches += 2;
@@ -138,15 +165,18 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 }
 
 // What a finished batch says about the next one's buffers. Returns the overflow bits that need a re-run.
-unsigned digest(WorkSet &ws, uint64_t n, unsigned overflow, uint64_t arena_need, uint64_t jobs, uint64_t dp_path, uint64_t dp_max_pool)
+unsigned digest(WorkSet &ws, uint64_t n, unsigned overflow, uint64_t arena_need, uint64_t jobs, uint64_t dp_path, uint64_t dp_max_pool,
+	uint64_t seg_need, uint64_t seg_ops_need)
 {
+	if (overflow & 128u) { ws.seg_cap_hint = seg_need + seg_need / 8 + 4096; ws.seg_ops_hint = std::max <uint64_t>(ws.seg_ops_hint, seg_need * 10); }
+	if (overflow & 256u) ws.seg_ops_hint = seg_ops_need + seg_ops_need / 8 + 4096;
 	if (overflow & 4u) ws.dp_arena_hint = dp_path + dp_path / 4 + 4096;
 	else if (dp_path + 4096 > ws.dp_arena_hint) ws.dp_arena_hint = std::max <uint64_t>(ws.dp_arena_hint, dp_path + dp_path / 8 + 1024);
 	if (overflow & 8u) ws.pool_hint = dp_max_pool;
 	if (overflow & 1u) ws.arena_cap_hint = arena_need + arena_need / 4 + 4096;
 	if (overflow & 2u) ws.rr_cap_hint = jobs + jobs / 4 + 1024;
 	ws.many_runs = jobs * 16 > n;
-	return overflow & (1u | 2u | 4u | 8u);
+	return overflow & (1u | 2u | 4u | 8u | 128u | 256u);
 }
 
 void harvest_timing(pv3_ctx *ctx, WorkSet &ws, float *ms /* rewrite, realign, splice, total, rewrite_main */)
@@ -198,7 +228,7 @@ int pv3_project_device(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		if (st) return st;
 		if (e != cudaSuccess) return fail(ctx, PV3_ERR_CUDA, "pv3_project_device: %s", cudaGetErrorString(e));
 		Counters const c = *ctx->h_counters;
-		unsigned const again = digest(ws, in->n, c.overflow, c.arena_cursor + c.dp_path, c.job_cursor, c.dp_path, c.dp_max_pool);
+		unsigned const again = digest(ws, in->n, c.overflow, c.arena_cursor + c.dp_path, c.job_cursor, c.dp_path, c.dp_max_pool, c.seg_cursor, c.seg_ops_cursor);
 		out->cig_used = (c.overflow & 1u) ? c.arena_cursor + c.dp_path : c.arena_cursor;
 		out->rr_used = c.job_cursor;
 		if (again & (1u | 2u)) {
@@ -492,7 +522,7 @@ int host_finish(HostCall &hc, uint64_t &cig_used, uint64_t &rr_used)
 		uint64_t const m = hc.cuts[c + 1] - hc.cuts[c];
 		if (!m) continue;
 		if (!r.done) return fail(ctx, PV3_ERR_CUDA, "pv3_project: chunk %llu did not report", (unsigned long long) c);
-		if (digest(ws, m, r.overflow, r.arena_need, r.jobs, r.dp_path, r.dp_max_pool)) again = true;
+		if (digest(ws, m, r.overflow, r.arena_need, r.jobs, r.dp_path, r.dp_max_pool, r.seg_need, r.seg_ops_need)) again = true;
 		if (r.overflow & (16u | 32u)) caller_short = true;
 		if (r.overflow & 64u) narrow = true;
 		cig_used += r.cig_used; rr_used += r.rr_used;

@@ -20,6 +20,7 @@
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
 #include "pv3_runs.cuh"
+#include "pv3_segment_core.h"
 
 namespace pv3 {
 
@@ -374,6 +375,93 @@ k1_rewrite_kernel(K1Params P, int group)
 		}
 		flush_group(P, g, stage);
 	}
+}
+
+// Assembly of the records cut into segments (pv3_rewrite_seg.cu): one warp per record concatenates its segments' op lists
+// through cigar_buffer::push_back's merge rule (cigar.cc:61-86) into the CIGAR arena, then the usual post-rewrite
+// bookkeeping (run detection, per-record outputs). A record with a failed segment goes to deferred2.
+__global__ void __launch_bounds__(K1_WARPS * 32)
+k1_assemble_kernel(K1Params P)
+{
+	if (*((volatile const unsigned int *) &P.counters->overflow) & (128u | 256u)) return;       // incomplete segment data: the host re-runs
+	unsigned const lane = lane_id();
+	uint64_t const n_items = (uint64_t) *((volatile const unsigned long long *) &P.counters->n_planned);
+	uint64_t const warp_global = (uint64_t) blockIdx.x * K1_WARPS + (threadIdx.x >> 5), n_warps = (uint64_t) gridDim.x * K1_WARPS;
+	const seg::SegOut *seg_out = (const seg::SegOut *) P.seg_out;
+	for (uint64_t i = warp_global; i < n_items; i += n_warps) {
+		uint64_t const rec = P.plan_rec[i], s0 = P.plan_seg0[i];
+		uint32_t const ns = P.plan_nseg[i];
+		// any failed segment? upper bound of the op count
+		bool bad = false;
+		uint32_t upper = 0;
+		for (uint32_t b = 0; b < ns; b += 32) {
+			seg::SegOut o; o.n_ops = 0; o.flags = 0;
+			if (b + lane < ns) o = seg_out[s0 + b + lane];
+			bad |= __any_sync(FULL, (o.flags & 2u) != 0);
+			upper += __reduce_add_sync(FULL, o.n_ops);
+		}
+		if (bad) {
+			if (lane == 0) { unsigned long long const slot = atomicAdd(&P.counters->n_deferred2, 1ull); P.deferred2[slot] = rec; }
+			continue;
+		}
+		RecordResult res; res.flags = 0; res.overflow = false; res.adjacent_id = false; res.n_ops = 0; res.dst_pos = 0;
+		uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec), rf = __ldg(P.dst_ref + rec);
+		if (sr >= P.n_rows || dr >= P.n_rows || rf >= P.n_refs) res.flags = PV3_FLAG_BAD_ID;        // (a record without segments only)
+		else {
+			RowDesc const S = P.rows[sr], D = P.rows[dr];
+			uint64_t const spos = __ldg(P.src_pos + rec);
+			uint64_t const col = (spos < S.n_zeros) ? select0_warp(S, spos + 1) : S.n_bits;        // rewrite_cigar.hh:51-56
+			res.dst_pos = rank0_warp(D, col);
+			if (P.qual_off) {
+				uint64_t const ql = __ldg(P.qual_off + rec + 1) - __ldg(P.qual_off + rec);
+				if (ql && ql != query_length(P, rec)) res.flags |= PV3_FLAG_BAD_QUAL;
+			}
+		}
+		uint64_t const base = arena_alloc(P, upper);
+		uint32_t n_out = 0;
+		if (base != ~0ull) {
+			uint32_t *out = P.arena + base;
+			uint32_t carry_op = OP_NONE, carry_cnt = 0;
+			bool adj = false;
+			for (uint32_t s = 0; s < ns; ++s) {
+				seg::SegOut const o = seg_out[s0 + s];                                              // warp-uniform
+				uint32_t const n = o.n_ops;
+				if (!n) continue;
+				uint32_t const v = lane < n ? P.seg_ops[o.off + lane] : 0u;                         // n <= OUTQ = 32
+				uint32_t const first = __shfl_sync(FULL, v, 0), last = __shfl_sync(FULL, v, (int) n - 1);
+				uint32_t const start = ((first & 0xfu) == carry_op) ? 1u : 0u;
+				if (start) carry_cnt += first >> 4;
+				adj |= (o.flags & 1u) != 0;
+				if (n == start) continue;                                                           // the whole segment went into the open op
+				uint32_t const next_op = __shfl_sync(FULL, v, (int) start) & 0xfu;
+				if (carry_op != OP_NONE) {
+					if (lane == 0) out[n_out] = (carry_cnt << 4) | carry_op;
+					++n_out;
+					adj |= (carry_op | next_op) == 3u;                                              // I next to D across the boundary
+				}
+				if (lane >= start && lane + 1 < n) out[n_out + lane - start] = v;
+				n_out += n - 1 - start;
+				carry_op = last & 0xfu; carry_cnt = last >> 4;
+			}
+			if (carry_op != OP_NONE) { if (lane == 0) out[n_out] = (carry_cnt << 4) | carry_op; ++n_out; }   // cigar_buffer::finish
+			res.n_ops = n_out; res.adjacent_id = adj;
+			__syncwarp();
+			__threadfence_block();
+			finish_record(P, rec, res, out);
+		} else {
+			res.n_ops = 0;
+			finish_record(P, rec, res, P.arena);
+		}
+		if (lane == 0) {
+			P.cig_out_off[rec] = (base == ~0ull) ? 0 : base + P.arena_off;
+			P.cig_out_len[rec] = (base == ~0ull || res.flags) ? 0 : res.n_ops;
+		}
+	}
+}
+
+void launch_k1_assemble(const K1Params &P, int n_sms, cudaStream_t stream)
+{
+	k1_assemble_kernel<<<(unsigned) n_sms * 8, K1_WARPS * 32, 0, stream>>>(P);
 }
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)

@@ -1,0 +1,117 @@
+// panvc3_b200 — long records as segments (host + device code; tests/cpp/k1w_emul.cc runs it on the CPU against the oracle).
+//
+// rewrite_cigar() (include/panvc3/rewrite_cigar.hh:59-153) carries three things from one reference-consuming base to the
+// next: src_pos, query_pos and prev_excess. The first two are running sums of the input ops; the third is, after ANY
+// reference-consuming base, rank0_dst(column of that base) + (dst[column] == 0) (identity proved in pv3_rewrite.cu). So a
+// record can be cut anywhere between two reference-consuming bases — inside an M / = / X / D / N op too — and every piece
+// rewritten on its own, provided the piece's span starts at the column right AFTER the previous piece's last base (the
+// source-gap columns up to its first base are that base's leading deletions) or, for the first piece, at the column of
+// the record's first base (rewrite_cigar.hh:51-56: no leading deletion there). Pass-through ops (I S H P) stay with the
+// piece in which they are met. The pieces' op lists are then concatenated through cigar_buffer::push_back's merge rule
+// (libpanvc3/cigar.cc:61-86). Every piece fits the word-parallel core's quotas (pv3_k1w_core.h), so a 10-kb read becomes
+// ~100 independent threads' worth of work instead of one warp walking 10^4 columns.
+#pragma once
+
+#include "pv3_k1w_core.h"
+
+namespace pv3 {
+namespace seg {
+
+constexpr uint32_t RSEG     = 64;      // reference-consuming bases per segment
+constexpr uint32_t QSEG     = 96;      // query bases per segment (M = X bases + small I / S ops)
+constexpr uint32_t BIG_PASS = 32;      // an I / S op longer than this is a segment of its own (nothing of the query is compared in it)
+constexpr uint32_t MAXOPS   = 16;      // input ops per segment
+constexpr uint32_t UNPLANNABLE = 0xffffffffu;
+
+enum : uint32_t { KIND_CORE = 0, KIND_PASS = 1 };
+
+struct SegDesc {
+	uint64_t rec;
+	uint32_t k0, k1;                 // input ops [k0, k1) of the record
+	uint32_t first_cnt, last_cnt;    // counts of op k0 / op k1 - 1 inside this segment when they are cut (~0: whole op)
+	uint32_t ref_start, q_start;     // reference-consuming / query bases of the record before the segment
+	uint32_t kind;
+	uint32_t pad;
+};
+
+struct SegOut {
+	uint64_t off;                    // first op in the segment op arena
+	uint32_t n_ops;
+	uint32_t flags;                  // bit 0: an I abuts a D inside the segment; bit 1: the segment could not be done here
+};
+
+// Walks the ops of one record and calls emit(kind, k0, k1, first_cnt, last_cnt, ref_start, q_start) for every segment, in
+// order. Returns the number of segments, or UNPLANNABLE (an op outside MIDNSHP=X, counts beyond 32 bits of running sums).
+template <typename t_emit>
+PV3_HD uint32_t plan_segments(const uint32_t *cig, uint32_t nc, t_emit &&emit)
+{
+	uint32_t n_seg = 0;
+	uint64_t ref_total = 0, q_total = 0;
+	uint32_t k0 = 0, first_cnt = ~0u, ref_acc = 0, q_acc = 0, n_pass = 0, n_in = 0;
+	bool open = false;                                         // the current segment holds something
+	auto close = [&](uint32_t k1, uint32_t last_cnt) {
+		if (open) { emit((uint32_t) KIND_CORE, k0, k1, first_cnt, last_cnt, (uint32_t) ref_total, (uint32_t) q_total); ++n_seg; }
+		ref_total += ref_acc; q_total += q_acc;
+		ref_acc = q_acc = n_pass = n_in = 0; first_cnt = ~0u; open = false;
+	};
+	for (uint32_t k = 0; k < nc; ++k) {
+		uint32_t const v = k1w::ldg(cig + k), op = v & 0xfu, cnt = v >> 4;
+		if (op > k1w::W_X) return UNPLANNABLE;
+		if (ref_total + ref_acc > 0x7fffffffull || q_total + q_acc > 0x7fffffffull) return UNPLANNABLE;
+		if ((0x72u >> op) & 1u) {                                  // I S H P
+			bool const qcons = (op == k1w::W_I || op == k1w::W_S);
+			if (qcons && cnt > BIG_PASS) {
+				close(k, ~0u);
+				emit((uint32_t) KIND_PASS, k, k + 1, ~0u, ~0u, (uint32_t) ref_total, (uint32_t) q_total); ++n_seg;
+				q_total += cnt;
+				k0 = k + 1;
+				continue;
+			}
+			if (open && (n_in == MAXOPS || (cnt && n_pass == (uint32_t) k1w::NBRK) || (qcons && q_acc + cnt > QSEG))) close(k, ~0u);
+			if (!open) { k0 = k; open = true; }
+			n_pass += cnt ? 1u : 0u;
+			q_acc += qcons ? cnt : 0u;
+			++n_in;
+		} else {
+			bool const mlike = !(op == k1w::W_D || op == k1w::W_N);
+			uint32_t remaining = cnt;
+			if (!cnt) {                                               // consumes nothing; stays where it is met
+				if (open && n_in == MAXOPS) close(k, ~0u);
+				if (!open) { k0 = k; open = true; }
+				++n_in;
+				continue;
+			}
+			while (remaining) {
+				uint32_t room = RSEG - ref_acc;
+				if (mlike && QSEG - q_acc < room) room = QSEG - q_acc;
+				if (open && (room == 0 || n_in == MAXOPS)) { close(k, ~0u); continue; }   // (a cut op never ends a segment here: see below)
+				if (!open) { k0 = k; open = true; first_cnt = (remaining != cnt) ? remaining : ~0u; room = (mlike && QSEG < RSEG) ? QSEG : RSEG; }
+				uint32_t const take = remaining < room ? remaining : room;
+				ref_acc += take; q_acc += mlike ? take : 0u; remaining -= take;
+				if (remaining) close(k + 1, take);                    // the op continues in the next segment
+				else ++n_in;
+			}
+		}
+	}
+	close(nc, ~0u);
+	return n_seg;
+}
+
+// A KIND_PASS segment: its ops pushed as they are (cigar_buffer::push_back merges equal neighbours, ignores zero counts).
+template <int ST>
+PV3_HD uint32_t emit_pass_segment(const uint32_t *cig, uint32_t k0, uint32_t k1, k1w::Lane <ST> const &L)
+{
+	uint32_t n = 0, carry_op = k1w::W_NONE, carry_cnt = 0;
+	for (uint32_t k = k0; k < k1; ++k) {
+		uint32_t const v = k1w::ldg(cig + k), op = v & 0xfu, cnt = v >> 4;
+		if (!cnt) continue;
+		if (op == carry_op) { carry_cnt += cnt; continue; }
+		if (carry_op != k1w::W_NONE) { if (n < (uint32_t) k1w::OUTQ) L.fin[n * ST] = (carry_cnt << 4) | carry_op; ++n; }
+		carry_op = op; carry_cnt = cnt;
+	}
+	if (carry_op != k1w::W_NONE) { if (n < (uint32_t) k1w::OUTQ) L.fin[n * ST] = (carry_cnt << 4) | carry_op; ++n; }
+	return n;
+}
+
+} // namespace seg
+} // namespace pv3

@@ -11,6 +11,7 @@
 
 #include "../../panvc3_b200/csrc/pv3_k1w_core.h"
 #include "../../panvc3_b200/csrc/pv3_index_build.h"
+#include "../../panvc3_b200/csrc/pv3_segment_core.h"
 
 using namespace pv3;
 
@@ -152,5 +153,90 @@ uint64_t k1w_emul_batch(void *p, uint64_t n, const uint32_t *src_row, const uint
 }
 
 int k1w_outq() { return k1w::OUTQ; }
+
+// Records as segments (pv3_segment_core.h): plan, the word-parallel core per segment, cigar_buffer-style concatenation.
+// status: 0 done, 1 the general kernel would take the record. ops: [n][cap] words, n_ops[n]. Returns the segments planned.
+uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const uint32_t *dst_row, const uint32_t *dst_ref, const uint64_t *src_pos,
+	const uint64_t *seq_off, const uint8_t *seq, const uint64_t *cig_off, const uint32_t *cig,
+	uint8_t *status, uint64_t *dst_pos, uint32_t *n_ops, uint32_t *ops, uint64_t cap)
+{
+	Index &ix = *(Index *) p;
+	uint64_t total_segs = 0;
+	std::vector <uint32_t> q4;
+	std::vector <seg::SegDesc> segs;
+	for (uint64_t rec = 0; rec < n; ++rec) {
+		status[rec] = 1; n_ops[rec] = 0;
+		Row const &S = ix.rows[src_row[rec]], &D = ix.rows[dst_row[rec]];
+		Ref const &R = ix.refs[dst_ref[rec]];
+		uint64_t const spos0 = src_pos[rec], nq = seq_off[rec + 1] - seq_off[rec], nc = cig_off[rec + 1] - cig_off[rec];
+		const uint32_t *rc = cig + cig_off[rec];
+		uint64_t const c0 = (spos0 < S.n_zeros) ? select0(S, spos0 + 1) : S.n_bits;
+		dst_pos[rec] = rank0(D, c0);
+		if (S.n_bits != D.n_bits || nc >= (1u << 20)) continue;
+		segs.clear();
+		uint32_t const ns = seg::plan_segments(rc, (uint32_t) nc, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs) {
+			seg::SegDesc d; d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.pad = 0;
+			segs.push_back(d);
+		});
+		if (ns == seg::UNPLANNABLE) continue;
+		total_segs += ns;
+		bool fail = false;
+		uint32_t carry_op = k1w::W_NONE, carry_cnt = 0, n_out = 0;
+		uint32_t *out = ops + rec * cap;
+		auto push = [&](uint32_t v) {
+			uint32_t const op = v & 0xfu, cnt = v >> 4;
+			if (!cnt) return;
+			if (op == carry_op) { carry_cnt += cnt; return; }
+			if (carry_op != k1w::W_NONE) { if (n_out < cap) out[n_out] = (carry_cnt << 4) | carry_op; ++n_out; }
+			carry_op = op; carry_cnt = cnt;
+		};
+		for (auto const &d : segs) {
+			uint32_t cmp[k1w::NW], ins[k1w::NW], del[k1w::NW], xm[k1w::NW], brk[k1w::NBRK], fin[k1w::OUTQ];
+			k1w::Lane <1> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
+			uint32_t no = 0;
+			if (d.kind == seg::KIND_PASS) no = seg::emit_pass_segment <1>(rc, d.k0, d.k1, L);
+			else {
+				uint64_t const spos = spos0 + d.ref_start;
+				if (spos > S.n_zeros) { fail = true; break; }
+				uint64_t c_start;
+				if (d.ref_start == 0) { if (spos >= S.n_zeros) { fail = true; break; } c_start = select0(S, spos + 1); }
+				else c_start = select0(S, spos) + 1;                     // right after the column of the previous segment's last base
+				uint64_t const e_start = rank0(D, c_start);
+				if (e_start > R.n || d.q_start > nq) { fail = true; break; }
+				uint64_t const q_left = nq - d.q_start;
+				uint32_t const nq_seg = (uint32_t) (q_left < k1w::QMAX ? q_left : k1w::QMAX);
+				uint32_t const qrel = (uint32_t) (rec * 5u + d.k0) % 23u;
+				q4.assign((qrel + nq_seg + 7) / 8 + 4, 0xeeeeeeeeu);
+				for (uint32_t i = 0; i < nq_seg; ++i) {
+					uint8_t const rank = seq[seq_off[rec] + d.q_start + i];
+					if (rank > 7) fail = true;
+					uint32_t const a = qrel + i;
+					q4[a >> 3] = (q4[a >> 3] & ~(0xfu << (4 * (a & 7)))) | ((uint32_t) (rank & 0xf) << (4 * (a & 7)));
+				}
+				if (fail) break;
+				k1w::SpanIn I;
+				I.Sp = S.words.data() + (c_start >> 6); I.Dp = D.words.data() + (c_start >> 6); I.c_lo6 = (uint32_t) c_start & 63u;
+				I.src_left = S.n_zeros - spos; I.e_start = e_start; I.ref_n = R.n; I.nq = nq_seg; I.q_start = 0;
+				k1w::OpRange opr; opr.cig = rc; opr.k0 = d.k0; opr.k1 = d.k1; opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt; opr.first_val = rc[d.k0];
+				k1w::SpanState st;
+				if (k1w::build_span <1, true>(I, opr, L, st)) { fail = true; break; }
+				uint64_t const ea = e_start & ~31ull;
+				k1w::compare_span <1, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u,
+					reinterpret_cast <const uint32_t *>(R.codes4.data() + (ea >> 1)), (uint32_t) (e_start - ea));
+				k1w::mark_runs <1, true>(L, st.n_brk, st.w_end);
+				bool adj = false;
+				no = k1w::emit_ops <1, true>(L, st.n_brk, opr, st.w_end, adj);
+			}
+			if (no > (uint32_t) k1w::OUTQ) { fail = true; break; }
+			for (uint32_t j = 0; j < no; ++j) push(fin[j]);
+		}
+		if (fail) continue;
+		if (carry_op != k1w::W_NONE) { if (n_out < cap) out[n_out] = (carry_cnt << 4) | carry_op; ++n_out; }
+		if (n_out > cap) continue;
+		n_ops[rec] = n_out;
+		status[rec] = 0;
+	}
+	return total_segs;
+}
 
 } // extern "C"

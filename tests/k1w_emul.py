@@ -40,6 +40,8 @@ def lib():
         _lib.k1w_emul_batch.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 13
         _lib.k1w_emul_batch.restype = C.c_uint64
         _lib.k1w_set_mode.argtypes = [C.c_int]
+        _lib.k1w_emul_segments.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 12 + [C.c_uint64]
+        _lib.k1w_emul_segments.restype = C.c_uint64
     return _lib
 
 
@@ -77,3 +79,18 @@ class EmulIndex:
         out = ProjectedBatch(dst_pos=dst_pos, flags=np.zeros(n, np.uint32), cig_off=cig_off, cig_len=n_ops, cig=ops.reshape(-1),
                              rr_off=np.zeros(n, np.uint64), rr_len=np.zeros(n, np.uint32), rr=np.zeros((1, 4), np.uint64))
         return status, out, adj
+
+    def rewrite_segments(self, batch: RecordBatch, cap: int = 4096):
+        """Records cut into segments (pv3_segment_core.h): (status[n], ProjectedBatch, segments planned)."""
+        n = batch.n
+        status = np.ones(n, np.uint8)
+        dst_pos = np.zeros(n, np.uint64)
+        n_ops = np.zeros(n, np.uint32)
+        ops = np.zeros((max(n, 1), cap), np.uint32)
+        p = lambda a: a.ctypes.data
+        segs = self.l.k1w_emul_segments(self.h, n, p(batch.src_row), p(batch.dst_row), p(batch.dst_ref), p(batch.src_pos), p(batch.seq_off),
+                                        p(batch.seq) if batch.seq.size else None, p(batch.cig_off), p(batch.cig) if batch.cig.size else None,
+                                        p(status), p(dst_pos), p(n_ops), p(ops), cap)
+        out = ProjectedBatch(dst_pos=dst_pos, flags=np.zeros(n, np.uint32), cig_off=np.arange(n, dtype=np.uint64) * np.uint64(cap), cig_len=n_ops,
+                             cig=ops.reshape(-1), rr_off=np.zeros(n, np.uint64), rr_len=np.zeros(n, np.uint32), rr=np.zeros((1, 4), np.uint64))
+        return status, out, int(segs)

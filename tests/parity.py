@@ -11,7 +11,7 @@ from panvc3_b200.workload import Msa
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-def assert_same(got: ProjectedBatch, exp: ProjectedBatch, batch: RecordBatch | None = None, what: str = "", flags_exact: bool = False):
+def assert_same(got: ProjectedBatch, exp: ProjectedBatch, batch: RecordBatch | None = None, what: str = "", flags_exact: bool = True):
     """Bit-exact per record: flags (zero / non-zero, or exact), dst_pos, CIGAR words, realigned ranges."""
     assert got.n == exp.n, f"{what}: record count {got.n} != {exp.n}"
     gf, ef = np.asarray(got.flags), np.asarray(exp.flags)

@@ -762,3 +762,33 @@ def test_multi_context_single_device_shards(gpu, port, workflow_msa):
             o, l = got.cig_off[cuts[g]:cuts[g + 1]], got.cig_len[cuts[g]:cuts[g + 1]]
             assert np.array_equal(o - o[0], _exclusive(l))
         mc.close()
+
+
+@pytest.mark.parametrize("style,with_qual", [("M", True), ("EQX", False)])
+def test_long_reads_segment_path(gpu, port, monkeypatch, style, with_qual):
+    """BASELINE configs[4] shape: 10-kb reads go through the segment kernels (plan → one thread per 64-base segment → warp
+    assembly), with and without them (PV3_NO_SEGMENTS: the warp-per-record kernel takes every long record), both thread
+    kernels in front, host and device entry; run detection and realignment across segment boundaries included."""
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.workload import sample_reads, synth_msa
+    msa = synth_msa(3_000_000, 3, seed=77, p_gap=0.004, mean_gap=6, snp=0.002, anticorrelated=0.001)
+    b = sample_reads(msa, 10_000, 10_000, seed=8, sub=0.01, ins=0.0008, dele=0.0008, clip_frac=0.2, cigar_style=style, with_qual=with_qual)
+    idx = device_index(msa)
+    oi = port.make_index(*casegen.index_inputs(msa))
+    exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+    assert int(exp.rr_len.sum()) > 1000 and int(exp.cig_len.max()) > 100
+    idx.ctx.set_params(0, -1)
+    for path in (0, 2):
+        idx.ctx.set_kernel_path(path)
+        got = idx.ctx.project(b)
+        assert_same(got, exp, b, f"long reads, segments, path {path}", flags_exact=True)
+        assert idx.ctx.timing()["n_deferred"] == b.n
+    idx.ctx.set_kernel_path(0)
+    import torch
+    dout = project_device(idx.ctx, DeviceBatch(b, torch.device("cuda", 0)))
+    assert_same(dout.to_host(), exp, b, "long reads, segments, device entry", flags_exact=True)
+    if style == "M":
+        monkeypatch.setenv("PV3_NO_SEGMENTS", "1")
+        assert_same(idx.ctx.project(b), exp, b, "long reads, warp-per-record kernel only", flags_exact=True)
+        monkeypatch.delenv("PV3_NO_SEGMENTS")
+        assert_same(idx.ctx.project(b.to_bam4()), exp, b, "long reads, segments, BAM-packed SEQ", flags_exact=True)
