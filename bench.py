@@ -90,7 +90,8 @@ def load_workload(n: int, rank: int = 0, workload: str = "config2", index_only: 
     if batch is not None and os.environ.get("PV3_BENCH_ORDER", "") == "sorted":
         batch = batch.coordinate_sorted()
         name += " [coordinate-sorted]"
-    regen = lambda r, m: (make(r, n).slice(0, m), None)
+    # (this generator is not prefix-stable in n: the own rank's records are taken from its batch, another rank's are generated again)
+    regen = lambda r, m: ((batch if (r == rank and batch is not None) else make(r, n)).slice(0, m), None)
     return Workload(name, casegen.index_inputs(msa), batch, None, regen, msa)
 
 
