@@ -44,9 +44,11 @@
 namespace pv3 {
 namespace k1w {
 
-constexpr int      NW    = 10;          // 32-column words per span: 320 columns including the offset of c0 in its word
-constexpr int      NBRK  = 12;          // pass-through ops (I S H P with a non-zero count) per record / segment
-constexpr int      OUTQ  = 32;         // staged output ops per record / segment
+// Quotas of one instantiation of the core. ST: threads per tile (the stride of the per-thread arrays, 1 on the host);
+// NW: 32-column words per span (including the offset of the start column in its word); NBRK: pass-through ops (I S H P
+// with a non-zero count); OUTQ: staged output ops.
+template <int t_st> struct CfgRecord  { static constexpr int ST = t_st, NW = 10, NBRK = 6, OUTQ = 24; };   // whole 150-bp records (K1W)
+template <int t_st> struct CfgSegment { static constexpr int ST = t_st, NW = 7,  NBRK = 8, OUTQ = 32; };   // <= 128-base segments of long records (K1S)
 constexpr uint32_t QMAX  = 192;         // query bases per record / segment
 constexpr uint32_t CLAMP = 1u << 20;
 constexpr uint32_t NOBRK = 0xffffffffu;
@@ -88,7 +90,7 @@ PV3_HD uint32_t nonzero_nibbles_hi(uint32_t t)
 }
 
 // Per-thread view of the tile's arrays: element i of an array is p[i * ST] (ST = threads per tile on the device, 1 on the host).
-template <int ST> struct Lane {
+template <typename C> struct Lane {
 	uint32_t *cmp, *ins, *del, *xm;     // [NW]   span masks, bit = column (LSB first) relative to the 32-column word of c0
 	                                    //        (after mark_runs: cmp = any op, ins = code bit 1, del = code bit 0, xm = run starts)
 	uint32_t *brk;                      // [NBRK] pass-through ops in input order: column position | input op index << 12
@@ -137,10 +139,11 @@ PV3_HD OpsInfo scan_ops(OpRange const &R)
 // Loads the NW 32-column words of both rows from the word that holds the start column and builds the span masks.
 // Sp / Dp: the 64-bit words holding the start column; c_lo6: start column & 63. The span ends with the column of the
 // tot_ref-th source base at or after the start column. Returns false when the span does not end within NW words.
-template <int ST>
-PV3_HD bool load_span(const uint64_t *Sp, const uint64_t *Dp, uint32_t c_lo6, uint32_t tot_ref, Lane <ST> const &L,
+template <typename C>
+PV3_HD bool load_span(const uint64_t *Sp, const uint64_t *Dp, uint32_t c_lo6, uint32_t tot_ref, Lane <C> const &L,
 	uint32_t &span_begin, uint32_t &span_end, uint32_t &n_dbase)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	constexpr int NL = NW / 2 + 1;
 	bool const half = (c_lo6 >> 5) != 0;
 	uint32_t const off = c_lo6 & 31u, m0 = 0xffffffffu << off;
@@ -190,9 +193,10 @@ PV3_HD bool load_span(const uint64_t *Sp, const uint64_t *Dp, uint32_t c_lo6, ui
 // go in front of; the source bases of D-like ops are collected in xm (free until compare_span) and then moved from cmp to
 // del and dropped from ins (rewrite_cigar.hh:119-147). Event columns come from a cursor over the span's source bases that
 // only moves forward. Returns false when the record has more than NBRK pass-through ops.
-template <int ST>
-PV3_HD bool apply_events(OpRange const &R, uint32_t tot_ref, uint32_t span_begin, uint32_t span_end, Lane <ST> const &L, uint32_t &n_brk)
+template <typename C>
+PV3_HD bool apply_events(OpRange const &R, uint32_t tot_ref, uint32_t span_begin, uint32_t span_end, Lane <C> const &L, uint32_t &n_brk)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	uint32_t b = 0, wc = 0, bc = 0, xc = L.cmp[0] | L.ins[0];
 	bool ok = true, any_d = false;
 	n_brk = 0;
@@ -253,10 +257,11 @@ PV3_HD void load16n(const uint32_t *base, uint32_t a, uint32_t &lo, uint32_t &hi
 // nibble qrel. rs: packed target codes (RefDesc::codes4) as words from a 32-base boundary, base e_start at nibble ra0.
 // The loop body has ONE merge point (no continue / break inside): ncu of the first version showed the lanes of a warp
 // running the compare block in separate passes (12.7 of 32 lanes active) when the body had several exits.
-template <int ST, bool EV>
-PV3_HD void compare_span(Lane <ST> const &L, uint32_t n_brk, const uint32_t *cig, uint32_t w_end,
+template <typename C, bool EV>
+PV3_HD void compare_span(Lane <C> const &L, uint32_t n_brk, const uint32_t *cig, uint32_t w_end,
 	const uint32_t *qs, uint32_t qrel, uint32_t q_start, const uint32_t *rs, uint32_t ra0)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	uint32_t bi = 0;
 	uint32_t brk = (EV && n_brk) ? L.brk[0] : NOBRK;
 	uint32_t brk_pos = (EV && n_brk) ? (brk & 0xfffu) : NOBRK;
@@ -309,9 +314,10 @@ PV3_HD void compare_span(Lane <ST> const &L, uint32_t n_brk, const uint32_t *cig
 // through the empty columns by carry propagation (adding the empty-column mask to the bits that enter its runs), one add
 // per code bit and word — no loop over runs. Pass-through ops force a start at the first column at or after their position.
 // In place: cmp ← columns with an op, ins ← code bit 1, del ← code bit 0, xm ← run starts.
-template <int ST, bool EV>
-PV3_HD void mark_runs(Lane <ST> const &L, uint32_t n_brk, uint32_t w_end)
+template <typename C, bool EV>
+PV3_HD void mark_runs(Lane <C> const &L, uint32_t n_brk, uint32_t w_end)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	uint32_t top0 = 0, top1 = 0, run0 = 0, run1 = 0, bj = 0;
 	bool seen = false, force = false;
 	PV3_NOUNROLL
@@ -345,9 +351,10 @@ PV3_HD void mark_runs(Lane <ST> const &L, uint32_t n_brk, uint32_t w_end)
 // cigar_buffer::push_back site (cigar.cc:61-86) on the common path. The length of a run is the difference of the op-column
 // ranks of two consecutive run starts. Returns the op count (cigar_buffer::finish included); more than OUTQ means the list
 // overflowed (the caller defers the record).
-template <int ST, bool EV>
-PV3_HD uint32_t emit_ops(Lane <ST> const &L, uint32_t n_brk, OpRange const &R, uint32_t w_end, bool &adjacent_id)
+template <typename C, bool EV>
+PV3_HD uint32_t emit_ops(Lane <C> const &L, uint32_t n_brk, OpRange const &R, uint32_t w_end, bool &adjacent_id)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	uint32_t bi = 0;
 	uint32_t brk = (EV && n_brk) ? L.brk[0] : NOBRK;
 	uint32_t brk_pos = (EV && n_brk) ? (brk & 0xfffu) : NOBRK;
@@ -426,9 +433,10 @@ struct SpanState {
 
 // 0: masks built; 1: the record must go to the general kernel; 2 (EV = false only): the record has events — it goes to the
 // list of the second launch.
-template <int ST, bool EV>
-PV3_HD int build_span(SpanIn const &I, OpRange const &R, Lane <ST> const &L, SpanState &st)
+template <typename C, bool EV>
+PV3_HD int build_span(SpanIn const &I, OpRange const &R, Lane <C> const &L, SpanState &st)
 {
+	constexpr int ST = C::ST, NW = C::NW, NBRK = C::NBRK, OUTQ = C::OUTQ; (void) ST; (void) NW; (void) NBRK; (void) OUTQ;
 	OpsInfo const oi = scan_ops(R);
 	st.tot_ref = oi.tot_ref; st.simple = oi.simple; st.n_brk = 0;
 	st.span_begin = st.span_end = st.w_end = st.n_dbase = 0; st.n_qbase = oi.tot_q;
@@ -436,10 +444,10 @@ PV3_HD int build_span(SpanIn const &I, OpRange const &R, Lane <ST> const &L, Spa
 	if ((uint64_t) oi.tot_ref > I.src_left || oi.tot_ref > (uint32_t) NW * 32u) return 1;            // POS_OOB or a long span
 	if ((uint64_t) I.q_start + oi.tot_q > (uint64_t) I.nq || I.nq > QMAX) return 1;                     // QUERY_OOB is possible
 	if (!EV && !oi.simple) return 2;
-	if (!load_span(I.Sp, I.Dp, I.c_lo6, oi.tot_ref, L, st.span_begin, st.span_end, st.n_dbase)) return 1;
+	if (!load_span <C>(I.Sp, I.Dp, I.c_lo6, oi.tot_ref, L, st.span_begin, st.span_end, st.n_dbase)) return 1;
 	if (I.e_start + st.n_dbase > I.ref_n) return 1;                                                    // REF_OOB is possible
 	st.w_end = (st.span_end + 31u) >> 5;
-	if (EV && !oi.simple && !apply_events(R, oi.tot_ref, st.span_begin, st.span_end, L, st.n_brk)) return 1;
+	if (EV && !oi.simple && !apply_events <C>(R, oi.tot_ref, st.span_begin, st.span_end, L, st.n_brk)) return 1;
 	return 0;
 }
 

@@ -14,6 +14,7 @@
 #include <cstring>
 
 #include "pv3_ctx.h"
+#include "pv3_segment_core.h"
 
 using namespace pv3;
 
@@ -44,8 +45,8 @@ int ensure_work(pv3_ctx *ctx, WorkSet &ws, uint64_t n, uint64_t rr_cap)
 	PV3_CUDA(ctx, ws.plan_nseg.ensure_idle(n * 4 + 8, s));
 	{
 		uint64_t const seg_cap = std::max <uint64_t>(ws.seg_cap_hint, n / 8 + 4096), seg_ops_cap = std::max <uint64_t>(ws.seg_ops_hint, n + 65536);
-		PV3_CUDA(ctx, ws.segs.ensure_idle(seg_cap * 40, s));
-		PV3_CUDA(ctx, ws.seg_out.ensure_idle(seg_cap * 16, s));
+		PV3_CUDA(ctx, ws.segs.ensure_idle(seg_cap * sizeof(seg::SegDesc), s));
+		PV3_CUDA(ctx, ws.seg_out.ensure_idle(seg_cap * sizeof(seg::SegOut), s));
 		PV3_CUDA(ctx, ws.seg_ops.ensure_idle(seg_ops_cap * 4, s));
 		ws.seg_cap = seg_cap; ws.seg_ops_cap = seg_ops_cap;
 	}

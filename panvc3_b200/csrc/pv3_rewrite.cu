@@ -395,10 +395,10 @@ k1_assemble_kernel(K1Params P)
 		bool bad = false;
 		uint32_t upper = 0;
 		for (uint32_t b = 0; b < ns; b += 32) {
-			seg::SegOut o; o.n_ops = 0; o.flags = 0;
-			if (b + lane < ns) o = seg_out[s0 + b + lane];
-			bad |= __any_sync(FULL, (o.flags & 2u) != 0);
-			upper += __reduce_add_sync(FULL, o.n_ops);
+			uint32_t n = 0, fl = 0;
+			if (b + lane < ns) { n = seg_out[s0 + b + lane].n_ops; fl = seg_out[s0 + b + lane].flags; }
+			bad |= __any_sync(FULL, (fl & 2u) != 0);
+			upper += __reduce_add_sync(FULL, n);
 		}
 		if (bad) {
 			if (lane == 0) { unsigned long long const slot = atomicAdd(&P.counters->n_deferred2, 1ull); P.deferred2[slot] = rec; }
@@ -418,35 +418,37 @@ k1_assemble_kernel(K1Params P)
 			}
 		}
 		uint64_t const base = arena_alloc(P, upper);
-		uint32_t n_out = 0;
 		if (base != ~0ull) {
+			// 32 segments per step, lane = segment. A segment's first op merges with the open op iff it equals the last op of
+			// the previous non-empty segment (an absorbed one-op segment has that same op); every other op gets a slot of its
+			// own, and a merged first op adds its count to the slot written last before it — the head of its run.
 			uint32_t *out = P.arena + base;
-			uint32_t carry_op = OP_NONE, carry_cnt = 0;
+			uint32_t n_out = 0, carry_op = OP_NONE;
 			bool adj = false;
-			for (uint32_t s = 0; s < ns; ++s) {
-				seg::SegOut const o = seg_out[s0 + s];                                              // warp-uniform
-				uint32_t const n = o.n_ops;
-				if (!n) continue;
-				uint32_t const v = lane < n ? P.seg_ops[o.off + lane] : 0u;                         // n <= OUTQ = 32
-				uint32_t const first = __shfl_sync(FULL, v, 0), last = __shfl_sync(FULL, v, (int) n - 1);
-				uint32_t const start = ((first & 0xfu) == carry_op) ? 1u : 0u;
-				if (start) carry_cnt += first >> 4;
-				adj |= (o.flags & 1u) != 0;
-				if (n == start) continue;                                                           // the whole segment went into the open op
-				uint32_t const next_op = __shfl_sync(FULL, v, (int) start) & 0xfu;
-				if (carry_op != OP_NONE) {
-					if (lane == 0) out[n_out] = (carry_cnt << 4) | carry_op;
-					++n_out;
-					adj |= (carry_op | next_op) == 3u;                                              // I next to D across the boundary
-				}
-				if (lane >= start && lane + 1 < n) out[n_out + lane - start] = v;
-				n_out += n - 1 - start;
-				carry_op = last & 0xfu; carry_cnt = last >> 4;
+			for (uint32_t b = 0; b < ns; b += 32) {
+				seg::SegOut o; o.off = 0; o.n_ops = 0; o.flags = 0; o.first = 0; o.last = 0;
+				if (b + lane < ns) o = seg_out[s0 + b + lane];
+				unsigned const nonempty = __ballot_sync(FULL, o.n_ops != 0);
+				unsigned const below = nonempty & lanemask_lt();
+				uint32_t prev_last = __shfl_sync(FULL, o.last & 0xfu, below ? 31 - __clz(below) : 0);
+				if (!below) prev_last = carry_op;
+				bool const merges = o.n_ops != 0 && (o.first & 0xfu) == prev_last;
+				uint32_t const w = o.n_ops - (merges ? 1u : 0u);
+				uint32_t incl = w;
+				#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) { uint32_t const t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
+				uint32_t const at = n_out + incl - w;                                        // this segment's first slot
+				adj |= __any_sync(FULL, (o.flags & 1u) != 0 || (o.n_ops != 0 && !merges && (prev_last | (o.first & 0xfu)) == 3u));
+				for (uint32_t j = merges ? 1u : 0u; j < o.n_ops; ++j) out[at + j - (merges ? 1u : 0u)] = P.seg_ops[o.off + j];
+				__syncwarp();
+				if (merges) atomicAdd(out + at - 1, (o.first >> 4) << 4);                    // at >= 1: an open op exists
+				__syncwarp();
+				n_out += __shfl_sync(FULL, incl, 31);
+				if (nonempty) carry_op = __shfl_sync(FULL, o.last & 0xfu, 31 - __clz(nonempty));
 			}
-			if (carry_op != OP_NONE) { if (lane == 0) out[n_out] = (carry_cnt << 4) | carry_op; ++n_out; }   // cigar_buffer::finish
 			res.n_ops = n_out; res.adjacent_id = adj;
-			__syncwarp();
 			__threadfence_block();
+			__syncwarp();
 			finish_record(P, rec, res, out);
 		} else {
 			res.n_ops = 0;

@@ -23,14 +23,16 @@ namespace pv3 {
 namespace {
 
 constexpr int      ST       = 32;      // threads per CTA = segments per tile (one warp)
-constexpr uint32_t S_QSLOT  = 21;      // words of staged query per segment (odd: conflict-free lanes): 15 lead + 96 bases + read-ahead
+typedef k1w::CfgSegment <ST> SC;
+constexpr uint32_t S_QSLOT  = 27;      // words of staged query per segment (odd: conflict-free lanes): 15 lead + 160 bases + read-ahead
+constexpr int      S_LOADS  = 11;      // 16-byte loads that cover 15 + 160 bytes
 
 struct TileS {
-	uint32_t cmp[k1w::NW][ST], ins[k1w::NW][ST], del[k1w::NW][ST], xm[k1w::NW][ST];
-	uint32_t brk[k1w::NBRK][ST];
+	uint32_t cmp[SC::NW][ST], ins[SC::NW][ST], del[SC::NW][ST], xm[SC::NW][ST];
+	uint32_t brk[SC::NBRK][ST];
 	union {
 		uint32_t qs[ST * S_QSLOT];
-		uint32_t fin[k1w::OUTQ][ST];
+		uint32_t fin[SC::OUTQ][ST];
 	};
 };
 
@@ -72,8 +74,23 @@ k1_plan_kernel(K1Params P)
 		uint64_t const rec = P.deferred[i];
 		uint64_t const cbase = __ldg(P.cig_off + rec), nc64 = __ldg(P.cig_off + rec + 1) - cbase;
 		const uint32_t *cig = P.cig + cbase;
-		uint32_t ns = seg::UNPLANNABLE;
-		if (nc64 < (1ull << 20)) ns = seg::plan_segments(cig, (uint32_t) nc64, [](uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {});
+		uint32_t ns = seg::UNPLANNABLE, total_ref = 0, rseg = seg::RSEG, qseg = seg::QSEG;
+		auto nothing = [](uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {};
+		// the walk over the two rows needs a record the reference would not abort on (ids, start position, enough source bases)
+		uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec);
+		uint64_t const spos = __ldg(P.src_pos + rec);
+		seg::RowCursor cur; cur.S = nullptr; cur.D = nullptr; cur.c = 0; cur.e = 0;
+		if (nc64 < (1ull << 20) && sr < P.n_rows && dr < P.n_rows) {
+			RowDesc const S = P.rows[sr], D = P.rows[dr];
+			if (S.n_bits == D.n_bits && spos < S.n_zeros) {
+				cur.S = S.words; cur.D = D.words;
+				cur.c = select0_thread(S, spos + 1);          // rewrite_cigar.hh:51
+				cur.e = rank0_thread(D, cur.c);               // :52
+				if (seg::dense_record(cur.S, cur.D, cur.c, nc64, query_length(P, rec))) { rseg = seg::RSEG_DENSE; qseg = seg::QSEG_DENSE; }
+				ns = seg::plan_segments(cig, (uint32_t) nc64, nothing, &total_ref, rseg, qseg);
+				if (ns != seg::UNPLANNABLE && (uint64_t) total_ref > S.n_zeros - spos) ns = seg::UNPLANNABLE;
+			}
+		}
 		if (ns == seg::UNPLANNABLE) {
 			unsigned long long const slot = atomicAdd(&P.counters->n_deferred2, 1ull);
 			P.deferred2[slot] = rec;
@@ -85,11 +102,13 @@ k1_plan_kernel(K1Params P)
 		if (base + ns > P.seg_cap) { atomicOr(&P.counters->overflow, 128u); continue; }
 		seg::SegDesc *out = segs + base;
 		uint32_t w = 0;
-		seg::plan_segments(cig, (uint32_t) nc64, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs) {
+		seg::plan_segments(cig, (uint32_t) nc64, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs, uint32_t rc) {
 			seg::SegDesc d;
-			d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.pad = 0;
+			d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.ref_count = rc;
+			d.c_start = cur.c; d.e_start = cur.e;                 // the first base's column, or right behind the previous segment's last base
+			if (rc) cur.advance(rc);
 			out[w++] = d;
-		});
+		}, nullptr, rseg, qseg);
 	}
 }
 
@@ -104,7 +123,7 @@ k1_segment_kernel(K1Params P)
 	uint64_t const n_tiles = (n_items + ST - 1) / ST;
 	const seg::SegDesc *segs = (const seg::SegDesc *) P.segs;
 	seg::SegOut *seg_out = (seg::SegOut *) P.seg_out;
-	k1w::Lane <ST> L;
+	k1w::Lane <SC> L;
 	L.cmp = &sm.cmp[0][tid]; L.ins = &sm.ins[0][tid]; L.del = &sm.del[0][tid]; L.xm = &sm.xm[0][tid];
 	L.brk = &sm.brk[0][tid]; L.fin = &sm.fin[0][tid];
 	bool const packed = P.seq_len != nullptr;
@@ -137,12 +156,10 @@ k1_segment_kernel(K1Params P)
 					uint64_t const qoff = __ldg(P.seq_off + rec);
 					uint64_t const nq = packed ? (uint64_t) __ldg(P.seq_len + rec) : __ldg(P.seq_off + rec + 1) - qoff;
 					uint64_t const spos = __ldg(P.src_pos + rec) + d.ref_start;
-					if (S.n_bits != D.n_bits || spos > S.n_zeros || (d.ref_start == 0 && spos >= S.n_zeros) || d.q_start > nq) fail = true;
+					if (d.q_start > nq) fail = true;
 					else {
-						// first segment of a record: the column of its first base (rewrite_cigar.hh:51); later ones: right after the
-						// column of the previous segment's last base
-						uint64_t const c_start = d.ref_start == 0 ? select0_thread(S, spos + 1) : select0_thread(S, spos) + 1;
-						e_start = rank0_thread(D, c_start);
+						uint64_t const c_start = d.c_start;                  // found by the planner (no select / rank here)
+						e_start = d.e_start;
 						if (e_start > R.n) fail = true;
 						else {
 							uint64_t const q_left = nq - d.q_start;
@@ -152,20 +169,23 @@ k1_segment_kernel(K1Params P)
 							uint64_t const q_addr = (uint64_t) (uintptr_t) P.seq + qoff + q_byte, q_addr16 = q_addr & ~15ull;
 							uint32_t const q_lead = (uint32_t) (q_addr - q_addr16);
 							uint32_t const nbytes = packed ? (nq_seg + (d.q_start & 1u) + 1u) / 2u : nq_seg;
-							uint32_t const n16 = (nbytes + q_lead + 15u) / 16u;               // <= 7
+							uint32_t const n16 = (nbytes + q_lead + 15u) / 16u;               // <= S_LOADS
 							const uint4 *g = reinterpret_cast <const uint4 *>((uintptr_t) q_addr16);
 							uint32_t *slot = &sm.qs[tid * S_QSLOT];
 							uint32_t bad_rank = 0;
-							uint4 v[7];
-							#pragma unroll
-							for (int j = 0; j < 7; ++j) if ((uint32_t) j < n16) v[j] = ld_stream16s(g + j);
-							#pragma unroll
-							for (int j = 0; j < 7; ++j) {
-								if ((uint32_t) j < n16) {
-									if (!packed) { uint2 const t = pack16s(v[j], bad_rank); slot[2 * j] = t.x; slot[2 * j + 1] = t.y; }
-									else if (j < 4) {
-										slot[4 * j] = bam4_word_to_ranks_s(v[j].x); slot[4 * j + 1] = bam4_word_to_ranks_s(v[j].y);
-										slot[4 * j + 2] = bam4_word_to_ranks_s(v[j].z); slot[4 * j + 3] = bam4_word_to_ranks_s(v[j].w);
+							for (uint32_t j0 = 0; j0 < n16; j0 += S_LOADS) {                    // all loads of a segment in flight at once (two rounds of six cost 20 %: latency)
+								uint4 v[S_LOADS];
+								#pragma unroll
+								for (int j = 0; j < S_LOADS; ++j) if (j0 + j < n16) v[j] = ld_stream16s(g + j0 + j);
+								#pragma unroll
+								for (int j = 0; j < S_LOADS; ++j) {
+									uint32_t const i = j0 + j;
+									if (i < n16) {
+										if (!packed) { uint2 const t = pack16s(v[j], bad_rank); slot[2 * i] = t.x; slot[2 * i + 1] = t.y; }
+										else {
+											slot[4 * i] = bam4_word_to_ranks_s(v[j].x); slot[4 * i + 1] = bam4_word_to_ranks_s(v[j].y);
+											slot[4 * i + 2] = bam4_word_to_ranks_s(v[j].z); slot[4 * i + 3] = bam4_word_to_ranks_s(v[j].w);
+										}
 									}
 								}
 							}
@@ -177,7 +197,7 @@ k1_segment_kernel(K1Params P)
 								k1w::SpanIn I;
 								I.Sp = S.words + (c_start >> 6); I.Dp = D.words + (c_start >> 6); I.c_lo6 = (uint32_t) c_start & 63u;
 								I.src_left = S.n_zeros - spos; I.e_start = e_start; I.ref_n = R.n; I.nq = nq_seg; I.q_start = 0;
-								if (k1w::build_span <ST, true>(I, opr, L, st)) fail = true;
+								if (k1w::build_span <SC, true>(I, opr, L, st)) fail = true;
 								else core = true;
 							}
 						}
@@ -188,14 +208,14 @@ k1_segment_kernel(K1Params P)
 		__syncwarp();
 		if (core) {
 			uint64_t const ea = e_start & ~31ull;
-			k1w::compare_span <ST, true>(L, st.n_brk, opr.cig, st.w_end, &sm.qs[tid * S_QSLOT], qrel, 0u,
+			k1w::compare_span <SC, true>(L, st.n_brk, opr.cig, st.w_end, &sm.qs[tid * S_QSLOT], qrel, 0u,
 				reinterpret_cast <const uint32_t *>(R.codes4 + (ea >> 1)), (uint32_t) (e_start - ea));
-			k1w::mark_runs <ST, true>(L, st.n_brk, st.w_end);
+			k1w::mark_runs <SC, true>(L, st.n_brk, st.w_end);
 		}
 		__syncthreads();        // the staged query is dead from here on: fin overwrites it
-		if (core) n_ops = k1w::emit_ops <ST, true>(L, st.n_brk, opr, st.w_end, adj);
-		else if (active && !fail) n_ops = seg::emit_pass_segment <ST>(opr.cig, d.k0, d.k1, L);      // KIND_PASS
-		if (n_ops > (uint32_t) k1w::OUTQ) { fail = true; }
+		if (core) n_ops = k1w::emit_ops <SC, true>(L, st.n_brk, opr, st.w_end, adj);
+		else if (active && !fail) n_ops = seg::emit_pass_segment <SC>(opr.cig, d.k0, d.k1, L);      // KIND_PASS
+		if (n_ops > (uint32_t) SC::OUTQ) { fail = true; }
 		if (fail) n_ops = 0;
 		// segment op arena: one atomic per warp
 		uint32_t incl = n_ops;
@@ -213,6 +233,7 @@ k1_segment_kernel(K1Params P)
 			o.off = base == ~0ull ? 0 : base + (incl - n_ops);
 			o.n_ops = base == ~0ull ? 0 : n_ops;
 			o.flags = (adj ? 1u : 0u) | (fail ? 2u : 0u);
+			o.first = n_ops ? sm.fin[0][tid] : 0u; o.last = n_ops ? sm.fin[n_ops - 1][tid] : 0u; o.pad = 0;
 			seg_out[s] = o;
 			if (base != ~0ull) for (uint32_t j = 0; j < n_ops; ++j) P.seg_ops[o.off + j] = sm.fin[j][tid];
 		}

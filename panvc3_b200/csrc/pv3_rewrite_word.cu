@@ -22,17 +22,18 @@ namespace pv3 {
 namespace {
 
 constexpr int      WT       = 32;                    // threads per CTA = records per tile (one warp)
+typedef k1w::CfgRecord <WT> WC;
 constexpr uint32_t W_QSTAGE = WT * 156;              // query bases staged per tile
 
 constexpr uint32_t W_QSLOT  = 29;                    // LIST mode: words of staged query per record (odd: conflict-free lanes), 232 nibbles
 
 template <bool LIST> struct TileW {
-	uint32_t cmp[k1w::NW][WT], ins[k1w::NW][WT], del[k1w::NW][WT], xm[k1w::NW][WT];
-	uint32_t brk[k1w::NBRK][WT];
+	uint32_t cmp[WC::NW][WT], ins[WC::NW][WT], del[WC::NW][WT], xm[WC::NW][WT];
+	uint32_t brk[WC::NBRK][WT];
 	union {
 		uint2    q4[W_QSTAGE / 16 + 2];              // !LIST: the tile's packed query, 16 bases per element (dead after C2)
 		uint32_t qs[LIST ? WT * W_QSLOT : 1];        //  LIST: one slot per record
-		uint32_t fin[k1w::OUTQ][WT];                 // final ops
+		uint32_t fin[WC::OUTQ][WT];                 // final ops
 	};
 };
 
@@ -95,7 +96,7 @@ k1_word_kernel(K1Params P)
 	unsigned const tid = threadIdx.x, lane = tid;
 	uint64_t const n_items = LIST ? (uint64_t) *P.n_list_dev : P.n;
 	uint64_t const n_tiles = (n_items + WT - 1) / WT;
-	k1w::Lane <WT> L;
+	k1w::Lane <WC> L;
 	L.cmp = &sm.cmp[0][tid]; L.ins = &sm.ins[0][tid]; L.del = &sm.del[0][tid]; L.xm = &sm.xm[0][tid];
 	L.brk = &sm.brk[0][tid]; L.fin = &sm.fin[0][tid];
 	bool const packed = P.seq_len != nullptr;                               // BAM 4-bit input: offsets count bytes, two bases each
@@ -207,7 +208,7 @@ k1_word_kernel(K1Params P)
 					I.src_left = S.n_zeros - spos; I.e_start = e0; I.ref_n = R.n;
 					I.nq = (uint32_t) nq; I.q_start = 0;
 					opr.cig = P.cig + cbase; opr.k0 = 0; opr.k1 = nc; opr.first_cnt = ~0u; opr.last_cnt = ~0u; opr.first_val = first_op;
-					int const rc = k1w::build_span <WT, EV>(I, opr, L, st);
+					int const rc = k1w::build_span <WC, EV>(I, opr, L, st);
 					defer = rc == 1;
 					complex_rec = rc == 2;
 				}
@@ -252,9 +253,9 @@ k1_word_kernel(K1Params P)
 		if (work) {
 			const uint32_t *qs = LIST ? &sm.qs[tid * W_QSLOT] : reinterpret_cast <const uint32_t *>(sm.q4);
 			uint32_t const qrel = LIST ? (q_lead << (packed ? 1 : 0)) : ((q_lead + (uint32_t) (qoff - tq0)) << (packed ? 1 : 0));
-			k1w::compare_span <WT, EV>(L, st.n_brk, opr.cig, st.w_end, qs, qrel, 0u,
+			k1w::compare_span <WC, EV>(L, st.n_brk, opr.cig, st.w_end, qs, qrel, 0u,
 				reinterpret_cast <const uint32_t *>(R.codes4 + (e0a >> 1)), (uint32_t) (e0 - e0a));
-			k1w::mark_runs <WT, EV>(L, st.n_brk, st.w_end);
+			k1w::mark_runs <WC, EV>(L, st.n_brk, st.w_end);
 		}
 		__syncthreads();        // the staged query is dead from here on: fin overwrites it
 
@@ -264,8 +265,8 @@ k1_word_kernel(K1Params P)
 		bool affine = false;
 		if (work) {
 			bool adjacent_id = false;
-			n_ops = k1w::emit_ops <WT, EV>(L, st.n_brk, opr, st.w_end, adjacent_id);
-			if (n_ops > (uint32_t) k1w::OUTQ) defer = true;
+			n_ops = k1w::emit_ops <WC, EV>(L, st.n_brk, opr, st.w_end, adjacent_id);
+			if (n_ops > (uint32_t) WC::OUTQ) defer = true;
 			if (!defer && P.stage == 0) {
 				if (n_ops == 0) flags |= PV3_FLAG_EMPTY_CIGAR;                               // cigar.cc:16-18 UB
 				else if (adjacent_id) {

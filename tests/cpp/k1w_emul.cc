@@ -14,6 +14,8 @@
 #include "../../panvc3_b200/csrc/pv3_segment_core.h"
 
 using namespace pv3;
+typedef k1w::CfgRecord <1> RC;
+typedef k1w::CfgSegment <1> SC;
 
 namespace {
 
@@ -115,8 +117,8 @@ uint64_t k1w_emul_batch(void *p, uint64_t n, const uint32_t *src_row, const uint
 		}
 		int path = 0;
 		if (!defer) {
-			uint32_t cmp[k1w::NW], ins[k1w::NW], del[k1w::NW], xm[k1w::NW], brk[k1w::NBRK], fin[k1w::OUTQ];
-			k1w::Lane <1> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
+			uint32_t cmp[RC::NW], ins[RC::NW], del[RC::NW], xm[RC::NW], brk[RC::NBRK], fin[RC::OUTQ];
+			k1w::Lane <RC> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
 			k1w::SpanIn I;
 			I.Sp = S.words.data() + (c0 >> 6); I.Dp = D.words.data() + (c0 >> 6); I.c_lo6 = (uint32_t) c0 & 63u;
 			I.src_left = S.n_zeros - spos; I.e_start = e0; I.ref_n = R.n; I.nq = (uint32_t) nq; I.q_start = 0;
@@ -126,24 +128,24 @@ uint64_t k1w_emul_batch(void *p, uint64_t n, const uint32_t *src_row, const uint
 			const uint32_t *rs = reinterpret_cast <const uint32_t *>(R.codes4.data() + (e0a >> 1));
 			uint32_t no = 0; bool adj = false;
 			// first launch: records without events; second launch (EV = true): the others
-			int rc = g_events_everywhere ? 2 : k1w::build_span <1, false>(I, opr, L, st);
+			int rc = g_events_everywhere ? 2 : k1w::build_span <RC, false>(I, opr, L, st);
 			if (rc == 0) {
-				k1w::compare_span <1, false>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
-				k1w::mark_runs <1, false>(L, st.n_brk, st.w_end);
-				no = k1w::emit_ops <1, false>(L, st.n_brk, opr, st.w_end, adj);
+				k1w::compare_span <RC, false>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
+				k1w::mark_runs <RC, false>(L, st.n_brk, st.w_end);
+				no = k1w::emit_ops <RC, false>(L, st.n_brk, opr, st.w_end, adj);
 			} else if (rc == 2) {
-				rc = k1w::build_span <1, true>(I, opr, L, st);
+				rc = k1w::build_span <RC, true>(I, opr, L, st);
 				path = st.simple ? 0 : 2;
 				if (rc == 0) {
-					k1w::compare_span <1, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
-					k1w::mark_runs <1, true>(L, st.n_brk, st.w_end);
-					no = k1w::emit_ops <1, true>(L, st.n_brk, opr, st.w_end, adj);
+					k1w::compare_span <RC, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u, rs, (uint32_t) (e0 - e0a));
+					k1w::mark_runs <RC, true>(L, st.n_brk, st.w_end);
+					no = k1w::emit_ops <RC, true>(L, st.n_brk, opr, st.w_end, adj);
 				}
 			}
-			if (rc != 0 || no > (uint32_t) k1w::OUTQ) defer = true;
+			if (rc != 0 || no > (uint32_t) RC::OUTQ) defer = true;
 			else {
 				n_ops[rec] = no; adjacent[rec] = adj;
-				memcpy(ops + rec * k1w::OUTQ, fin, no * 4);
+				memcpy(ops + rec * RC::OUTQ, fin, no * 4);
 			}
 		}
 		status[rec] = defer ? 1 : (uint8_t) path;
@@ -152,7 +154,7 @@ uint64_t k1w_emul_batch(void *p, uint64_t n, const uint32_t *src_row, const uint
 	return deferred;
 }
 
-int k1w_outq() { return k1w::OUTQ; }
+int k1w_outq() { return RC::OUTQ; }
 
 // Records as segments (pv3_segment_core.h): plan, the word-parallel core per segment, cigar_buffer-style concatenation.
 // status: 0 done, 1 the general kernel would take the record. ops: [n][cap] words, n_ops[n]. Returns the segments planned.
@@ -174,11 +176,19 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 		dst_pos[rec] = rank0(D, c0);
 		if (S.n_bits != D.n_bits || nc >= (1u << 20)) continue;
 		segs.clear();
-		uint32_t const ns = seg::plan_segments(rc, (uint32_t) nc, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs) {
-			seg::SegDesc d; d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.pad = 0;
+		uint32_t total_ref = 0;
+		if (spos0 >= S.n_zeros) continue;
+		uint32_t rseg = seg::RSEG, qseg = seg::QSEG;
+		if (seg::dense_record(S.words.data(), D.words.data(), c0, nc, nq)) { rseg = seg::RSEG_DENSE; qseg = seg::QSEG_DENSE; }
+		uint32_t ns = seg::plan_segments(rc, (uint32_t) nc, [](uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}, &total_ref, rseg, qseg);
+		if (ns == seg::UNPLANNABLE || (uint64_t) total_ref > S.n_zeros - spos0) continue;
+		seg::RowCursor cur; cur.S = S.words.data(); cur.D = D.words.data(); cur.c = c0; cur.e = dst_pos[rec];
+		seg::plan_segments(rc, (uint32_t) nc, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs, uint32_t rcnt) {
+			seg::SegDesc d; d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.ref_count = rcnt;
+			d.c_start = cur.c; d.e_start = cur.e;
+			if (rcnt) cur.advance(rcnt);
 			segs.push_back(d);
-		});
-		if (ns == seg::UNPLANNABLE) continue;
+		}, nullptr, rseg, qseg);
 		total_segs += ns;
 		bool fail = false;
 		uint32_t carry_op = k1w::W_NONE, carry_cnt = 0, n_out = 0;
@@ -191,20 +201,17 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 			carry_op = op; carry_cnt = cnt;
 		};
 		for (auto const &d : segs) {
-			uint32_t cmp[k1w::NW], ins[k1w::NW], del[k1w::NW], xm[k1w::NW], brk[k1w::NBRK], fin[k1w::OUTQ];
-			k1w::Lane <1> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
+			uint32_t cmp[SC::NW], ins[SC::NW], del[SC::NW], xm[SC::NW], brk[SC::NBRK], fin[SC::OUTQ];
+			k1w::Lane <SC> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
 			uint32_t no = 0;
-			if (d.kind == seg::KIND_PASS) no = seg::emit_pass_segment <1>(rc, d.k0, d.k1, L);
+			if (d.kind == seg::KIND_PASS) no = seg::emit_pass_segment <SC>(rc, d.k0, d.k1, L);
 			else {
 				uint64_t const spos = spos0 + d.ref_start;
-				if (spos > S.n_zeros) { fail = true; break; }
-				uint64_t c_start;
-				if (d.ref_start == 0) { if (spos >= S.n_zeros) { fail = true; break; } c_start = select0(S, spos + 1); }
-				else c_start = select0(S, spos) + 1;                     // right after the column of the previous segment's last base
-				uint64_t const e_start = rank0(D, c_start);
+				uint64_t const c_start = d.c_start, e_start = d.e_start;        // the planner's walk; cross-checked against select / rank
+				if (c_start != (d.ref_start == 0 ? select0(S, spos + 1) : select0(S, spos) + 1) || e_start != rank0(D, c_start)) abort();
 				if (e_start > R.n || d.q_start > nq) { fail = true; break; }
 				uint64_t const q_left = nq - d.q_start;
-				uint32_t const nq_seg = (uint32_t) (q_left < k1w::QMAX ? q_left : k1w::QMAX);
+				uint32_t const nq_seg = (uint32_t) (q_left < seg::QSEG ? q_left : seg::QSEG);   // (the kernel stages up to QSEG bases whatever the segment size)
 				uint32_t const qrel = (uint32_t) (rec * 5u + d.k0) % 23u;
 				q4.assign((qrel + nq_seg + 7) / 8 + 4, 0xeeeeeeeeu);
 				for (uint32_t i = 0; i < nq_seg; ++i) {
@@ -219,15 +226,15 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 				I.src_left = S.n_zeros - spos; I.e_start = e_start; I.ref_n = R.n; I.nq = nq_seg; I.q_start = 0;
 				k1w::OpRange opr; opr.cig = rc; opr.k0 = d.k0; opr.k1 = d.k1; opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt; opr.first_val = rc[d.k0];
 				k1w::SpanState st;
-				if (k1w::build_span <1, true>(I, opr, L, st)) { fail = true; break; }
+				if (k1w::build_span <SC, true>(I, opr, L, st)) { fail = true; break; }
 				uint64_t const ea = e_start & ~31ull;
-				k1w::compare_span <1, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u,
+				k1w::compare_span <SC, true>(L, st.n_brk, opr.cig, st.w_end, q4.data(), qrel, 0u,
 					reinterpret_cast <const uint32_t *>(R.codes4.data() + (ea >> 1)), (uint32_t) (e_start - ea));
-				k1w::mark_runs <1, true>(L, st.n_brk, st.w_end);
+				k1w::mark_runs <SC, true>(L, st.n_brk, st.w_end);
 				bool adj = false;
-				no = k1w::emit_ops <1, true>(L, st.n_brk, opr, st.w_end, adj);
+				no = k1w::emit_ops <SC, true>(L, st.n_brk, opr, st.w_end, adj);
 			}
-			if (no > (uint32_t) k1w::OUTQ) { fail = true; break; }
+			if (no > (uint32_t) SC::OUTQ) { fail = true; break; }
 			for (uint32_t j = 0; j < no; ++j) push(fin[j]);
 		}
 		if (fail) continue;
