@@ -53,6 +53,7 @@ struct WorkSet {
 	uint64_t arena_cap_hint = 0, rr_cap_hint = 0, dp_arena_hint = 0, pool_hint = 0;
 	bool     qual_bulk = false;         // the last chunk here realigned many records: upload QUAL in full instead of reading it in place
 	bool     many_runs = false;
+	uint64_t expect_deferred = 0;       // the last batch's deferred records (+ 25 %): sizes the grids of the deferred-record kernels
 	void release();
 };
 

@@ -195,8 +195,11 @@ void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // w
 void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record, run walk (v4-v13)
 void launch_k1_word(const K1Params &P, int n_sms, cudaStream_t stream);
 // the deferred list of either thread kernel cut into segments of <= 64 reference bases, one thread per segment (long reads)
-void launch_k1_segments(const K1Params &P, int n_sms, cudaStream_t stream);     // plan + segment kernels (pv3_rewrite_seg.cu)
-void launch_k1_assemble(const K1Params &P, int n_sms, cudaStream_t stream);     // concatenation, run detection, outputs (pv3_rewrite.cu)     // thread per record, word-parallel (v14; default)
+// `expected`: the deferred records the host expects (last batch's count, read lengths): sizes the resident grids, which read
+// the real counts on the device — a wrong guess costs time, never results
+void launch_k1_segments(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream);     // plan + segment kernels (pv3_rewrite_seg.cu)
+void launch_k1_assemble(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream);     // concatenation, run detection, outputs (pv3_rewrite.cu)
+void launch_k1_list(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream);         // warp-per-record kernel over a device-counted list     // thread per record, word-parallel (v14; default)
 void launch_k3(const K3Params &P, int n_sms, uint64_t grid_warps, cudaStream_t stream);
 void launch_k3_thread(const K3Params &P, cudaStream_t stream);               // thread per run (small runs)
 void launch_k4(const K1Params &P, uint64_t n_jobs, const uint32_t *dp_arena, cudaStream_t stream);

@@ -29,6 +29,7 @@ struct DevBatch {
 	pv3_batch_in  in;         // device pointers (compact fields unused)
 	pv3_batch_out out;        // device pointers: per-record arrays, arena (cig, cig_cap), rr (rr, rr_cap), mate_dst_pos
 	uint64_t      arena_off = 0, rr_base = 0;
+	uint64_t      expect_deferred = 0;   // host-side guess: records the thread kernel will not take (long reads)
 };
 
 int ensure_work(pv3_ctx *ctx, WorkSet &ws, uint64_t n, uint64_t rr_cap)
@@ -111,9 +112,10 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		// a warp per record; whatever fails there is left to the warp-per-record kernel. All list lengths are read on the device.
 		K1Params P2 = P;
 		bool const use_segments = !getenv("PV3_NO_SEGMENTS");
+		uint64_t const expected = std::min <uint64_t>(in.n, std::max <uint64_t>(ws.expect_deferred, B.expect_deferred));
 		if (use_segments) {
-			launch_k1_segments(P, ctx->n_sms, stream);
-			launch_k1_assemble(P, ctx->n_sms, stream);
+			launch_k1_segments(P, ctx->n_sms, expected, stream);
+			launch_k1_assemble(P, ctx->n_sms, expected, stream);
 			PV3_CUDA(ctx, cudaGetLastError());
 			P2.rec_list = ws.deferred2.as <uint64_t>();
 			P2.n_list_dev = &ws.counters.as <Counters>()->n_deferred2;
@@ -122,7 +124,7 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 			P2.rec_list = ws.deferred.as <uint64_t>();
 			P2.n_list_dev = &ws.counters.as <Counters>()->n_deferred;
 		}
-		launch_k1(P2, ctx->n_sms, stream);
+		launch_k1_list(P2, ctx->n_sms, use_segments ? expected / 16 + 64 : expected, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		launches += 2;
 	} else {
@@ -167,7 +169,7 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 
 // What a finished batch says about the next one's buffers. Returns the overflow bits that need a re-run.
 unsigned digest(WorkSet &ws, uint64_t n, unsigned overflow, uint64_t arena_need, uint64_t jobs, uint64_t dp_path, uint64_t dp_max_pool,
-	uint64_t seg_need, uint64_t seg_ops_need)
+	uint64_t seg_need, uint64_t seg_ops_need, uint64_t n_deferred)
 {
 	if (overflow & 128u) { ws.seg_cap_hint = seg_need + seg_need / 8 + 4096; ws.seg_ops_hint = std::max <uint64_t>(ws.seg_ops_hint, seg_need * 10); }
 	if (overflow & 256u) ws.seg_ops_hint = seg_ops_need + seg_ops_need / 8 + 4096;
@@ -177,6 +179,7 @@ unsigned digest(WorkSet &ws, uint64_t n, unsigned overflow, uint64_t arena_need,
 	if (overflow & 1u) ws.arena_cap_hint = arena_need + arena_need / 4 + 4096;
 	if (overflow & 2u) ws.rr_cap_hint = jobs + jobs / 4 + 1024;
 	ws.many_runs = jobs * 16 > n;
+	ws.expect_deferred = n_deferred + n_deferred / 4;
 	return overflow & (1u | 2u | 4u | 8u | 128u | 256u);
 }
 
@@ -229,7 +232,7 @@ int pv3_project_device(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		if (st) return st;
 		if (e != cudaSuccess) return fail(ctx, PV3_ERR_CUDA, "pv3_project_device: %s", cudaGetErrorString(e));
 		Counters const c = *ctx->h_counters;
-		unsigned const again = digest(ws, in->n, c.overflow, c.arena_cursor + c.dp_path, c.job_cursor, c.dp_path, c.dp_max_pool, c.seg_cursor, c.seg_ops_cursor);
+		unsigned const again = digest(ws, in->n, c.overflow, c.arena_cursor + c.dp_path, c.job_cursor, c.dp_path, c.dp_max_pool, c.seg_cursor, c.seg_ops_cursor, c.n_deferred);
 		out->cig_used = (c.overflow & 1u) ? c.arena_cursor + c.dp_path : c.arena_cursor;
 		out->rr_used = c.job_cursor;
 		if (again & (1u | 2u)) {
@@ -419,6 +422,7 @@ int host_enqueue(HostCall &hc)
 		B.out.rr_off = ws.out_rr_off.as <uint64_t>(); B.out.rr_len = ws.out_rr_len.as <uint32_t>();
 		B.out.rr = ws.out_rr.as <uint64_t>(); B.out.rr_cap = rr_cap;
 		B.out.mate_dst_pos = mates ? ws.out_mate.as <uint64_t>() : nullptr;
+		if ((s1 - s0) * (packed ? 2 : 1) > 192 * m) B.expect_deferred = m;      // long reads: none fits the thread kernel
 		int st = ensure_work(ctx, ws, m, rr_cap);
 		if (st) return st;
 		st = enqueue_kernels(ctx, ws, B, hc.launches);
@@ -523,7 +527,7 @@ int host_finish(HostCall &hc, uint64_t &cig_used, uint64_t &rr_used)
 		uint64_t const m = hc.cuts[c + 1] - hc.cuts[c];
 		if (!m) continue;
 		if (!r.done) return fail(ctx, PV3_ERR_CUDA, "pv3_project: chunk %llu did not report", (unsigned long long) c);
-		if (digest(ws, m, r.overflow, r.arena_need, r.jobs, r.dp_path, r.dp_max_pool, r.seg_need, r.seg_ops_need)) again = true;
+		if (digest(ws, m, r.overflow, r.arena_need, r.jobs, r.dp_path, r.dp_max_pool, r.seg_need, r.seg_ops_need, r.n_deferred)) again = true;
 		if (r.overflow & (16u | 32u)) caller_short = true;
 		if (r.overflow & 64u) narrow = true;
 		cig_used += r.cig_used; rr_used += r.rr_used;

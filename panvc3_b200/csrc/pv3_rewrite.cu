@@ -461,9 +461,19 @@ k1_assemble_kernel(K1Params P)
 	}
 }
 
-void launch_k1_assemble(const K1Params &P, int n_sms, cudaStream_t stream)
+void launch_k1_assemble(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream)
 {
-	k1_assemble_kernel<<<(unsigned) n_sms * 8, K1_WARPS * 32, 0, stream>>>(P);
+	uint64_t ctas = expected / K1_WARPS + 4;
+	if (ctas > (uint64_t) n_sms * 8) ctas = (uint64_t) n_sms * 8;
+	k1_assemble_kernel<<<(unsigned) ctas, K1_WARPS * 32, 0, stream>>>(P);
+}
+
+void launch_k1_list(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream)
+{
+	// list length known only on the device: a resident grid strides over it, one record per warp
+	uint64_t ctas = expected / K1_WARPS + 8;
+	if (ctas > (uint64_t) n_sms * 4) ctas = (uint64_t) n_sms * 4;
+	k1_rewrite_kernel<<<(unsigned) ctas, K1_WARPS * 32, 0, stream>>>(P, 1);
 }
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream)

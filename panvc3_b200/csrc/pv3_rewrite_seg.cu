@@ -241,7 +241,7 @@ k1_segment_kernel(K1Params P)
 	}
 }
 
-void launch_k1_segments(const K1Params &P, int n_sms, cudaStream_t stream)
+void launch_k1_segments(const K1Params &P, int n_sms, uint64_t expected, cudaStream_t stream)
 {
 	static int per_sm = 0;
 	size_t const bytes = sizeof(TileS);
@@ -251,8 +251,12 @@ void launch_k1_segments(const K1Params &P, int n_sms, cudaStream_t stream)
 		if (getenv("PV3_TRACE")) fprintf(stderr, "[pv3 trace] k1_segment_kernel: %zu bytes of shared memory per tile, %d CTAs per SM\n", bytes, per_sm);
 	}
 	// both grids are resident and read their item counts on the device (no host round trip after the thread kernel)
-	k1_plan_kernel<<<(unsigned) n_sms * 8, 128, 0, stream>>>(P);
-	k1_segment_kernel<<<(unsigned) n_sms * per_sm, ST, bytes, stream>>>(P);
+	// (a handful of expected records: small grids — filling 148 x 24 CTAs that find nothing to do costs 15 us per launch)
+	uint64_t plan_ctas = (expected + 127) / 128 + 4, seg_ctas = expected * 4 + 32;
+	if (plan_ctas > (uint64_t) n_sms * 8) plan_ctas = (uint64_t) n_sms * 8;
+	if (seg_ctas > (uint64_t) n_sms * per_sm) seg_ctas = (uint64_t) n_sms * per_sm;
+	k1_plan_kernel<<<(unsigned) plan_ctas, 128, 0, stream>>>(P);
+	k1_segment_kernel<<<(unsigned) seg_ctas, ST, bytes, stream>>>(P);
 }
 
 } // namespace pv3
