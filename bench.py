@@ -480,6 +480,11 @@ def run_gpu_arm(args) -> None:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     pv3_build.build()
+    if args.dp_legs_only:                      # the DP kernels alone (what the ncu captures of K3 / K3T run)
+        if rank == 0:
+            emit({"metric": "realignment DP cell updates", "unit": "GCUPS", "n_gpus": 1, "data": "synthetic",
+                  "realign_dp": realign_dp_leg(dev, 250_000, args.steps), "realign_dp_wide_windows": wide_dp_leg(dev, args.steps)})
+        return
     workload = args.workload or default_workload(world)
     peak, peak_src = measured_peak_gbs()
 
@@ -661,6 +666,7 @@ def run_gpu_arm(args) -> None:
                 del sl
                 ctx.set_stream(None)
                 line["realign_dp"] = realign_dp_leg(dev, 250_000, 3)
+                line["realign_dp_wide_windows"] = wide_dp_leg(dev, 3)
             if not args.no_chr_leg:
                 line["chr_scale"] = chr_scale_leg(dev, stream, args, peak)
         if world == 1 and not args.no_cpu_baseline:
@@ -704,6 +710,35 @@ def realign_dp_leg(dev, n: int, steps: int) -> dict:
     return {"workload": wl.name, "records": n, "runs": st["rr_used"], "dp_cells": st["dp_cells"], "ms_dp_kernels": t,
             "gcups": st["dp_cells"] / (t * 1e-3) / 1e9 if t > 0 else None,
             "note": "runs here are a few bases wide (mean 17 cells): the figure is bounded by per-run overhead, not by cell updates"}
+
+
+def wide_dp_leg(dev, steps: int) -> list:
+    """The DP kernels on wide windows (one run of W x W cells per read: founders that diverge over W columns), edit distance
+    (no QUAL, gap opening 0) and affine with the quality LUT — the shapes where cell updates, not per-run overhead, decide."""
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import wide_window_workload
+    res = []
+    for window, blocks in ((64, 65536), (256, 8192), (1024, 1024)):
+        for with_qual in (False, True):
+            rows, refs, batch = wide_window_workload(window, blocks, 5, with_qual=with_qual)
+            idx = MsaIndex.from_rows(rows, refs, device=dev.index)
+            c = idx.ctx
+            c.set_params(0, -1)
+            db = DeviceBatch(batch, dev)
+            out = project_device(c, db)
+            for _ in range(2):
+                project_device(c, db, out)
+            ms = []
+            for _ in range(steps):
+                project_device(c, db, out)
+                ms.append(c.timing()["ms_realign"])
+            st = dict(out.stats)
+            t = statistics.mean(ms)
+            res.append({"window": window, "runs": st["rr_used"], "mode": "affine_quality_lut" if with_qual else "edit_distance",
+                        "dp_cells": st["dp_cells"], "ms_dp_kernels": t, "gcups": st["dp_cells"] / (t * 1e-3) / 1e9 if t > 0 else None})
+            del db, out, idx, c
+    return res
 
 
 def chr_scale_leg(dev, stream, args, peak: float) -> dict:
@@ -758,6 +793,7 @@ def main() -> None:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-wide-leg", action="store_true", help="skip the e2e leg with round 1's wide encoding")
     ap.add_argument("--no-dp-leg", action="store_true", help="skip the sorted-input and realignment-throughput legs")
+    ap.add_argument("--dp-legs-only", action="store_true", help="only the realignment legs (indel-heavy and wide windows), no headline line")
     ap.add_argument("--no-chr-leg", action="store_true", help="skip the chromosome-scale leg of the one-GPU run")
     ap.add_argument("--no-nccl-gather", action="store_true", help="skip the A/B leg of the NCCL ordered gather (N > 1)")
     ap.add_argument("--no-parity-check", action="store_true")

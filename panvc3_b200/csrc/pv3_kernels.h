@@ -69,13 +69,18 @@ __device__ __forceinline__ uint64_t query_length(K1Params const &P, uint64_t rec
 }
 #endif
 
-// Scratch bytes one DP job needs: byte trace (Q+1)x(R+1), strip boundary arrays (H, up: int32; tup: byte), staged
-// reference ranks.
-__host__ __device__ inline unsigned long long dp_pool_bytes(uint32_t R, uint32_t Q, bool /*affine*/)
+// Scratch of one DP job of the warp-per-run kernel. Trace: per strip of 32 query rows, R + 31 steps rounded up to blocks of 32 steps, in groups of four steps, 32 lanes
+// per group, a 32-bit word (affine: one byte per cell) or a byte (edit distance: two bits per cell) per lane and group. Strip
+// boundary arrays (H, vertical gap state, its trace bit: 4 bytes each per column) only when there is more than one strip.
+__host__ __device__ inline uint32_t dp_trace_groups(uint32_t R) { return ((R + 62u) >> 5) << 3; }
+__host__ __device__ inline unsigned long long dp_trace_bytes(uint32_t R, uint32_t Q, bool affine)
 {
-	unsigned long long const cols = (unsigned long long) R + 1, rows = (unsigned long long) Q + 1;
-	unsigned long long const a4 = ~3ull;
-	return ((rows * cols + 3) & a4) + 8 * cols + ((cols + 3) & a4) + ((cols + 3) & a4);
+	unsigned long long const strips = ((unsigned long long) Q + 31) >> 5;
+	return strips * dp_trace_groups(R) * 32ull * (affine ? 4ull : 1ull);
+}
+__host__ __device__ inline unsigned long long dp_pool_bytes(uint32_t R, uint32_t Q, bool affine)
+{
+	return dp_trace_bytes(R, Q, affine) + (Q > 32u ? 12ull * ((unsigned long long) R + 1) : 0ull);
 }
 
 // Runs small enough for the thread-per-run DP kernel (K3T): the whole DP state of one run fits a thread's local arrays.

@@ -10,6 +10,8 @@
 // libpanvc3/alignment_projector.cc:57-151 (rewrite, find runs, realign each, splice) and the 16-slot task ring around it
 // (include/panvc3/spsc_queue.hh, project-alignments/project_alignments.cc:597-631).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -111,8 +113,12 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		// what the thread kernel could not take (long reads above all): cut into segments, one thread per segment, reassembled by
 		// a warp per record; whatever fails there is left to the warp-per-record kernel. All list lengths are read on the device.
 		K1Params P2 = P;
-		bool const use_segments = !getenv("PV3_NO_SEGMENTS");
+		// Which route the deferred records take is a matter of speed only (both are exact): a handful — short reads beyond a
+		// quota — go straight to the warp-per-record kernel (one launch: four launches that each find a dozen records cost
+		// 50 us of latency), many — long reads — through the segment kernels. The host's guess: the last batch's count and,
+		// where it can see them, the read lengths.
 		uint64_t const expected = std::min <uint64_t>(in.n, std::max <uint64_t>(ws.expect_deferred, B.expect_deferred));
+		bool const use_segments = !getenv("PV3_NO_SEGMENTS") && (expected >= 256 || getenv("PV3_SEGMENTS_ALWAYS"));
 		if (use_segments) {
 			launch_k1_segments(P, ctx->n_sms, expected, stream);
 			launch_k1_assemble(P, ctx->n_sms, expected, stream);
@@ -597,9 +603,17 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		HostCall hc;
 		hc.ctx = ctx; hc.in = in; hc.out = out; hc.rec_begin = 0; hc.rec_end = in->n;
 		hc.cig_place = hc.rr_place = 0; hc.cig_room = out->cig_cap; hc.rr_room = out->rr ? out->rr_cap : 0;
+		static bool const trace = getenv("PV3_TRACE") != nullptr;
+		auto const t0 = std::chrono::steady_clock::now();
 		st = host_enqueue(hc);
+		auto const t1 = std::chrono::steady_clock::now();
 		// whatever happened, nothing of this call may still be in flight when it returns: the caller owns the buffers again
 		cudaError_t const e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->stream2);
+		if (trace) {
+			auto const t2 = std::chrono::steady_clock::now();
+			fprintf(stderr, "[pv3 trace] pv3_project: %llu records, %llu launches; host enqueue %.3f ms, wait %.3f ms\n", (unsigned long long) in->n,
+				(unsigned long long) hc.launches, std::chrono::duration <double, std::milli>(t1 - t0).count(), std::chrono::duration <double, std::milli>(t2 - t1).count());
+		}
 		if (st) return st;
 		if (e0 != cudaSuccess || e1 != cudaSuccess) return fail(ctx, PV3_ERR_CUDA, "pv3_project: %s", cudaGetErrorString(e0 != cudaSuccess ? e0 : e1));
 		uint64_t cig_used = 0, rr_used = 0;

@@ -431,3 +431,43 @@ def sample_reads_words(msa: MsaWords, n: int, read_len: int, seed: int, sub: flo
     if paired:
         mates = tuple(np.concatenate([m[i] for m in mparts]) for i in range(3))
     return batch, mates
+
+
+def wide_window_workload(window: int, n_blocks: int, seed: int, with_qual: bool = False, flank: int = 16, sub_every: int = 7):
+    """A two-row MSA whose rows diverge in blocks — `window` columns where only the source row has bases, then `window`
+    columns where only the target row has them, `flank` shared columns between blocks — and one read per block that spans
+    it. The rewrite gives `…= windowI windowD …=` for every read, so each is ONE realignment run whose DP matrix is about
+    window x window cells (the wide-window shape of the DP kernels: structural variants between founders).
+    The query resembles the target's block (one substitution every `sub_every` bases) so that the traceback is mostly diagonal.
+    Returns (gap_rows, refs, RecordBatch)."""
+    from .batch import RecordBatch, pack_bits
+    rng = np.random.default_rng(seed)
+    F, W, T = int(flank), int(window), int(n_blocks)
+    period = F + 2 * W
+    n_cols = T * period + F
+    col = np.arange(n_cols, dtype=np.int64)
+    ph = col % period
+    in_tail = col >= T * period
+    src_gap = (ph >= F + W) & ~in_tail
+    dst_gap = (ph >= F) & (ph < F + W) & ~in_tail
+    gap_rows = [(pack_bits(src_gap), n_cols), (pack_bits(dst_gap), n_cols)]
+    # target contig: per block `flank` bases + `window` bases, then the closing flank
+    tgt = _ACGT[rng.integers(0, 4, T * (F + W) + F)]
+    rank_of = np.full(256, 3, np.uint8)
+    for ch, r in zip(b"ACGNT", range(5)):
+        rank_of[ch] = r
+    tr = rank_of[tgt]
+    qlen = 2 * F + W
+    seq = np.empty((T, qlen), np.uint8)
+    starts = np.arange(T, dtype=np.int64) * (F + W)
+    idx = starts[:, None] + np.arange(qlen, dtype=np.int64)[None, :]
+    seq[:] = tr[idx]                                     # flank + block + next flank of the target, as dna5 ranks
+    mid = seq[:, F:F + W]
+    mid[:, ::sub_every] = (mid[:, ::sub_every] + 1) % 3  # substitutions (ranks 0..2: never N)
+    n = T
+    batch = RecordBatch(src_row=np.zeros(n, np.uint32), dst_row=np.ones(n, np.uint32), dst_ref=np.zeros(n, np.uint32),
+                        src_pos=starts.astype(np.uint64), seq_off=np.arange(n + 1, dtype=np.uint64) * np.uint64(qlen), seq=seq.reshape(-1),
+                        cig_off=np.arange(n + 1, dtype=np.uint64), cig=np.full(n, (qlen << 4) | 0, np.uint32),
+                        qual_off=(np.arange(n + 1, dtype=np.uint64) * np.uint64(qlen)) if with_qual else None,
+                        qual=rng.integers(0, 42, n * qlen).astype(np.uint8) if with_qual else None)
+    return gap_rows, [tgt.tobytes()], batch

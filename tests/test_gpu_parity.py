@@ -778,6 +778,7 @@ def test_long_reads_segment_path(gpu, port, monkeypatch, style, with_qual):
     exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
     assert int(exp.rr_len.sum()) > 1000 and int(exp.cig_len.max()) > 100
     idx.ctx.set_params(0, -1)
+    monkeypatch.setenv("PV3_SEGMENTS_ALWAYS", "1")     # (the device entry only takes them once a batch has shown many deferred records)
     for path in (0, 2):
         idx.ctx.set_kernel_path(path)
         got = idx.ctx.project(b)
@@ -792,3 +793,22 @@ def test_long_reads_segment_path(gpu, port, monkeypatch, style, with_qual):
         assert_same(idx.ctx.project(b), exp, b, "long reads, warp-per-record kernel only", flags_exact=True)
         monkeypatch.delenv("PV3_NO_SEGMENTS")
         assert_same(idx.ctx.project(b.to_bam4()), exp, b, "long reads, segments, BAM-packed SEQ", flags_exact=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("window,blocks", [(64, 40), (96, 33), (300, 9), (700, 5)])
+def test_wide_window_workload(gpu, port, window, blocks):
+    """The wide-window DP bench shape (workload.wide_window_workload) against the oracle: one W x W run per read, edit
+    distance and affine quality scoring, both DP kernels' dispatch rules."""
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import wide_window_workload
+    for with_qual in (False, True):
+        rows, refs, b = wide_window_workload(window, blocks, 17 + window, with_qual=with_qual)
+        idx = MsaIndex.from_rows(rows, refs)
+        oi = port.make_index(rows, refs)
+        for go, ge in [(0, -1), (-2, -1)]:
+            exp = oi.project_batch(b, go, ge)
+            assert int(exp.rr_len.sum()) == blocks
+            for dp_min in (16384, 0):
+                idx.ctx.set_dp_thread_min(dp_min)
+                assert_same(idx.project_batch(b, go, ge), exp, b, f"wide window {window} qual={with_qual} go={go} dp_min={dp_min}")
