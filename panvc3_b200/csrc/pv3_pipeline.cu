@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "pv3_ctx.h"
 #include "pv3_segment_core.h"
@@ -277,6 +278,23 @@ struct HostCall {
 
 // Enqueues everything for the records [rec_begin, rec_end) of the call on the context's two streams. No synchronisation
 // unless a buffer has to grow while an earlier chunk is still in flight on its stream, or the caller's memory is pageable.
+std::vector <cudaEvent_t> g_timeline;      // PV3_TRACE_TIMELINE: six events per chunk (single-context debugging aid)
+
+void dump_timeline(uint64_t n_chunks)
+{
+	if (g_timeline.empty()) return;
+	static const char *names[6] = { "h2d_begin", "h2d_end", "kernels_end", "pack_begin", "pack_end", "out_end" };
+	for (uint64_t c = 0; c < n_chunks; ++c) {
+		fprintf(stderr, "[pv3 timeline] chunk %llu:", (unsigned long long) c);
+		for (int k = 0; k < 6; ++k) {
+			float t = -1;
+			if (cudaEventElapsedTime(&t, g_timeline[0], g_timeline[c * 6 + k]) != cudaSuccess) { cudaGetLastError(); t = -1; }
+			fprintf(stderr, " %s %.3f", names[k], t);
+		}
+		fprintf(stderr, "\n");
+	}
+}
+
 int host_enqueue(HostCall &hc)
 {
 	pv3_ctx *ctx = hc.ctx;
@@ -328,6 +346,10 @@ int host_enqueue(HostCall &hc)
 	bool const mates = compact ? in->mate_row16 != nullptr : in->mate_row != nullptr;
 	const uint8_t *qual_alias = has_qual ? (const uint8_t *) mapped_alias(in->qual) : nullptr;
 
+	static bool const trace_tl = getenv("PV3_TRACE_TIMELINE") != nullptr;      // debugging aid: per-chunk device timeline on stderr
+	std::vector <cudaEvent_t> &tl = g_timeline;
+	if (trace_tl && tl.empty()) { tl.resize(MAX_CHUNKS * 6); for (auto &e : tl) cudaEventCreate(&e); }
+	auto mark = [&](uint64_t c, int k, cudaStream_t st) { if (trace_tl) cudaEventRecord(tl[c * 6 + k], st); };
 	PV3_CUDA(ctx, cudaMemsetAsync(ctx->running.p, 0, 16, streams[0]));
 	PV3_CUDA(ctx, cudaEventRecord(ctx->ev_misc[2], streams[0]));
 	for (uint64_t c = 0; c < n_chunks; ++c) {
@@ -366,9 +388,11 @@ int host_enqueue(HostCall &hc)
 		if (qual_bulk) add(12, in->qual + q0, q1 - q0);
 		for (int i = 0; i < n_copies; ++i) PV3_CUDA(ctx, ws.in[copies[i].slot].ensure_idle((copies[i].bytes ? copies[i].bytes : 16) + 64, stream));
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[0], stream));
+		mark(c, 0, stream);
 		for (int i = 0; i < n_copies; ++i)
 			if (copies[i].bytes) PV3_CUDA(ctx, cudaMemcpyAsync(ws.in[copies[i].slot].p, copies[i].src, copies[i].bytes, cudaMemcpyHostToDevice, stream));
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[1], stream));
+		mark(c, 1, stream);
 
 		// ---- device batch ------------------------------------------------------------------------------------------------
 		DevBatch B;
@@ -468,12 +492,15 @@ int host_enqueue(HostCall &hc)
 			K.staged = 1;
 			K.cig_dst_word0 = zero_copy ? (((uint64_t) (uintptr_t) d_cig.alias) >> 2) + hc.cig_place : 0;
 		}
+		mark(c, 2, stream);
 		PV3_CUDA(ctx, cudaStreamWaitEvent(stream, c == 0 ? ctx->ev_misc[2] : ctx->sets[(c - 1) % 2].ev[5], 0));
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[2], stream));
+		mark(c, 3, stream);
 		launch_pack_out(K, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		hc.launches += 4;
 		PV3_CUDA(ctx, cudaEventRecord(ws.ev[5], stream));
+		mark(c, 4, stream);
 		if (zero_copy) {
 			StreamOutParams S;
 			memset(&S, 0, sizeof S);
@@ -493,6 +520,7 @@ int host_enqueue(HostCall &hc)
 			hc.launches += 1;
 		}
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[3], stream));
+		mark(c, 5, stream);
 
 		if (!zero_copy) {
 			// pageable destination: wait for the chunk, then plain copies of exactly what it produced
@@ -611,6 +639,7 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		cudaError_t const e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->stream2);
 		if (trace) {
 			auto const t2 = std::chrono::steady_clock::now();
+			dump_timeline(hc.n_chunks);
 			fprintf(stderr, "[pv3 trace] pv3_project: %llu records, %llu launches; host enqueue %.3f ms, wait %.3f ms\n", (unsigned long long) in->n,
 				(unsigned long long) hc.launches, std::chrono::duration <double, std::milli>(t1 - t0).count(), std::chrono::duration <double, std::milli>(t2 - t1).count());
 		}
