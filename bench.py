@@ -753,11 +753,18 @@ def chr_scale_leg(dev, stream, args, peak: float) -> dict:
     c.set_stream(stream.cuda_stream)
     with torch.cuda.stream(stream):
         leg = device_leg(c, dev, stream, wl, wl.batch, wl.mates, max(3, args.steps // 2), 3, peak)
+        from panvc3_b200.workload import sorted_bam_window
+        sb, sm = sorted_bam_window(wl.msa, n, READ_LEN, SEED + 5)
+        sleg = device_leg(c, dev, stream, wl, sb, sm, max(3, args.steps // 2), 3, peak)
     c.set_stream(None)
-    rf = leg["roofline"]
+    rf, srf = leg["roofline"], sleg["roofline"]
     return {"workload": wl.name, "rows": len(wl.index_inputs[0]), "records": n, "value": n / (leg["ms_per_step"] * 1e-3), "unit": UNIT,
             "ms_per_step": leg["ms_per_step"], "kernels_ms": leg["kernels_ms"],
-            "roofline": {"kernel": rf["kernel"], "kernel_ms": rf["kernel_ms"], "frac": rf["frac"], "bytes_per_record": rf["bytes_per_record"], "frac_survey_formula": rf["frac_survey_formula"]}}
+            "roofline": {"kernel": rf["kernel"], "kernel_ms": rf["kernel_ms"], "frac": rf["frac"], "bytes_per_record": rf["bytes_per_record"], "frac_survey_formula": rf["frac_survey_formula"]},
+            "sorted_bam_window": {"what": "the same index; the batch is 10^6 CONSECUTIVE records of a coordinate-sorted BAM of 10^8 reads (one founder, a quarter of its length, "
+                                          "sorted by position) — what project_alignments receives in the reference's workflow; the figures above sample every read anywhere in the MSA",
+                                  "value": n / (sleg["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": sleg["ms_per_step"], "kernels_ms": sleg["kernels_ms"],
+                                  "k1_thread_kernel_ms": srf["kernel_ms"], "roofline_frac": srf["frac"], "frac_survey_formula": srf["frac_survey_formula"]}}
 
 
 _RESULT_FD = None

@@ -49,6 +49,11 @@ struct K1Params {
 	uint64_t       *deferred2;   // capacity n
 	uint64_t        arena_off;   // added to every stored cig_off (chunked host pipeline: arena of chunk c starts here)
 	uint64_t        rr_base;     // added to every stored rr_off
+	// thread kernel only: mate positions projected in its phase A (the mate sits a few hundred columns from the read: the
+	// directory and word sectors are the ones just fetched; a separate pass misses DRAM for all of them again at chromosome scale)
+	const uint32_t *mate_row;    // null: no mates here
+	const uint64_t *mate_pos;
+	uint64_t       *mate_dst_pos;
 };
 
 // BAM 4-bit base code ("=ACMGRSVTWYHKDBN") → seqan3::dna5 rank, as seqan3 converts when it reads a BAM SEQ into dna5

@@ -77,6 +77,7 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 	pv3_batch_out const &out = B.out;
 	K1Params P;
 	memset(&P, 0, sizeof P);
+	bool mates_done = false;
 	P.n = in.n;
 	P.src_row = in.src_row; P.dst_row = in.dst_row; P.dst_ref = in.dst_ref; P.src_pos = in.src_pos;
 	P.seq_off = in.seq_off; P.seq = in.seq; P.seq_len = in.seq_len; P.qual_off = in.qual_off; P.qual = in.qual;
@@ -108,7 +109,11 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		const char *e = getenv("PV3_K1_KERNEL");
 		bool const word = ctx->kernel_path == 2 || (ctx->kernel_path == 0 && e && e[0] == 'w');
 		if (word) launch_k1_word(P, ctx->n_sms, stream);
-		else launch_k1_thread(P, ctx->n_sms, ctx->target_code_bytes, stream);
+		else {
+			K1Params PT = P;
+			if (in.mate_row && out.mate_dst_pos) { PT.mate_row = in.mate_row; PT.mate_pos = in.mate_pos; PT.mate_dst_pos = out.mate_dst_pos; mates_done = true; }
+			launch_k1_thread(PT, ctx->n_sms, ctx->target_code_bytes, stream);
+		}
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ws.ev[4], stream));
 		// what the thread kernel could not take (long reads above all): cut into segments, one thread per segment, reassembled by
@@ -166,7 +171,7 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		launches += 3;
 	} else PV3_CUDA(ctx, cudaEventRecord(ws.ev[2], stream));
 	PV3_CUDA(ctx, cudaEventRecord(ws.ev[3], stream));
-	if (in.mate_row && out.mate_dst_pos) {
+	if (in.mate_row && out.mate_dst_pos && !mates_done) {
 		launch_positions(ctx->row_desc.as <RowDesc>(), (uint32_t) ctx->rows.size(), in.n, in.mate_row, in.dst_row, in.mate_pos, out.mate_dst_pos, stream);
 		PV3_CUDA(ctx, cudaGetLastError());
 		launches += 1;

@@ -230,6 +230,12 @@ k1_thread_kernel(K1Params P)
 				}
 			}
 		}
+		if (P.mate_row && active) {                                              // sequence_entry::project_position (msa_index.hh:253-258), as positions_kernel
+			uint32_t const mr = __ldg(P.mate_row + rec), dr = __ldg(P.dst_row + rec);
+			uint64_t mo = ~0ull;
+			if (mr < P.n_rows && dr < P.n_rows) mo = rank0_thread(P.rows[dr], select0_thread(P.rows[mr], __ldg(P.mate_pos + rec) + 1));
+			P.mate_dst_pos[rec] = mo;
+		}
 		// a query rank above 7 anywhere in the tile: the nibble compare cannot represent it, the general kernel takes the tile
 		if (__syncthreads_or((int) bad_rank)) defer = true;
 

@@ -320,9 +320,9 @@ READ_BLOCK = 50_000      # reads are generated in blocks with their own seeds: t
 
 
 def _sample_block(msa: MsaWords, n: int, read_len: int, seed, sub: float, ins: float, dele: float, clip_frac: float, with_qual: bool,
-                  paired: bool):
+                  paired: bool, founder: int | None = None, word_range: tuple[int, int] | None = None):
     rng = np.random.default_rng(seed)
-    founders = rng.integers(1, msa.n_rows, n)
+    founders = rng.integers(1, msa.n_rows, n) if founder is None else np.full(n, int(founder), dtype=np.int64)
     win_words = (read_len + 3 + 64 + 63) // 64 + 1       # a read's span plus slack; windows with too few bases are resampled
     L = read_len
     p_any = lambda p: 1.0 - (1.0 - p) ** L
@@ -341,7 +341,8 @@ def _sample_block(msa: MsaWords, n: int, read_len: int, seed, sub: float, ins: f
     todo = np.arange(n)
     while todo.size:                                     # resample reads whose window holds too few founder bases (long gaps, row ends)
         m = todo.size
-        sw = rng.integers(0, max(msa.gap_words[0].size - win_words, 1), m)
+        w_lo, w_hi = (0, max(msa.gap_words[0].size - win_words, 1)) if word_range is None else word_range
+        sw = rng.integers(w_lo, max(min(w_hi, msa.gap_words[0].size - win_words), w_lo + 1), m)
         f = founders[todo]
         got = np.zeros(m, dtype=bool)
         for fr in np.unique(f):
@@ -431,6 +432,23 @@ def sample_reads_words(msa: MsaWords, n: int, read_len: int, seed: int, sub: flo
     if paired:
         mates = tuple(np.concatenate([m[i] for m in mparts]) for i in range(3))
     return batch, mates
+
+
+def sorted_bam_window(msa: MsaWords, n: int, read_len: int, seed: int, total_reads: int = 100_000_000, **kw):
+    """`n` CONSECUTIVE records of a coordinate-sorted BAM holding `total_reads` reads spread evenly over the founders — what
+    project_alignments actually receives in the reference's workflow (test-workflow/Snakefile sorts before projecting): one
+    founder, positions inside the stretch of it that n / total_reads of the reads cover, sorted by position.
+    Returns (RecordBatch, mates) like sample_reads_words."""
+    per_founder = max(total_reads // (msa.n_rows - 1), n)
+    n_words = int(msa.gap_words[0].size)
+    span = max(int(n_words * (n / per_founder)), 64)
+    rng = np.random.default_rng([seed, 77])
+    founder = int(rng.integers(1, msa.n_rows))
+    w0 = int(rng.integers(0, max(n_words - span, 1)))
+    batch, mates = _sample_block(msa, n, read_len, [seed, 78], kw.get("sub", 0.005), kw.get("ins", 0.0005), kw.get("dele", 0.0005),
+                                 kw.get("clip_frac", 0.02), kw.get("with_qual", True), kw.get("paired", True), founder=founder, word_range=(w0, w0 + span))
+    order = np.argsort(batch.src_pos, kind="stable")
+    return batch.take(order), (tuple(a[order] for a in mates) if mates is not None else None)
 
 
 def wide_window_workload(window: int, n_blocks: int, seed: int, with_qual: bool = False, flank: int = 16, sub_every: int = 7):
