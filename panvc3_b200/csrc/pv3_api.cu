@@ -112,6 +112,7 @@ int pv3_create(pv3_ctx **out, int device)
 	ctx->n_sms = prop.multiProcessorCount;
 	default_quality_lut(ctx->lut);
 	if (const char *e = getenv("PV3_CHUNK_RECORDS")) { long long v = atoll(e); if (v >= 1024) ctx->chunk_records = (uint64_t) v; }
+	if (const char *e = getenv("PV3_CHUNK_EDGE_LAST")) { long long v = atoll(e); if (v >= 0) ctx->chunk_edge_last = (uint64_t) v; }
 	if (const char *e = getenv("PV3_CHUNK_EDGE")) { long long v = atoll(e); if (v >= 0) ctx->chunk_edge = (uint64_t) v; }
 	bool ok = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess
 		&& cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) == cudaSuccess;

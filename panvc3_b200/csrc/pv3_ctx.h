@@ -83,6 +83,7 @@ struct pv3_ctx {
 	int32_t      lut[84];
 	int          stage = 0;
 	uint64_t     chunk_records = 500000;     // records per chunk of the host pipeline (PV3_CHUNK_RECORDS overrides)
+	uint64_t     chunk_edge_last = 0;        // records of the last chunk when it should differ from the first (PV3_CHUNK_EDGE_LAST; 0 = chunk_edge)
 	uint64_t     chunk_edge = 125000;        // records of the first and the last chunk: a short pipeline fill and drain (PV3_CHUNK_EDGE; 0 = equal chunks)
 	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all
 	int          kernel_path = 0;            // 0: thread-per-record run-walk kernel + warp-per-record for deferred records; 1: warp-per-record only;

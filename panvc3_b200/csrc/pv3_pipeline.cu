@@ -317,13 +317,14 @@ int host_enqueue(HostCall &hc)
 	{
 		uint64_t *cuts = hc.cuts;
 		uint64_t const edge = (n_chunks >= 2 && ctx->chunk_edge && n > 4 * ctx->chunk_edge) ? ctx->chunk_edge : 0;
+		uint64_t const last = edge ? (ctx->chunk_edge_last ? std::min(ctx->chunk_edge_last, edge) : edge) : 0;     // the drain is the exposed one
 		if (edge) {
-			uint64_t n_mid = (n - 2 * edge + ctx->chunk_records / 2) / ctx->chunk_records;
+			uint64_t n_mid = (n - edge - last + ctx->chunk_records / 2) / ctx->chunk_records;
 			if (n_mid < 1) n_mid = 1;
 			if (n_mid > 62) n_mid = 62;
 			n_chunks = n_mid + 2;
 			cuts[0] = 0;
-			for (uint64_t c = 0; c <= n_mid; ++c) cuts[c + 1] = (edge + (n - 2 * edge) * c / n_mid) / 128 * 128;
+			for (uint64_t c = 0; c <= n_mid; ++c) cuts[c + 1] = (edge + (n - edge - last) * c / n_mid) / 128 * 128;
 			cuts[n_chunks] = n;
 		} else {
 			for (uint64_t c = 0; c < n_chunks; ++c) cuts[c] = (n * c / n_chunks) / 128 * 128;

@@ -14,7 +14,7 @@
 // score arrive from lane l-1 by shuffle, the horizontal gap state stays in the lane.  Strip boundaries (row i0) live in
 // three arrays, read and written through 32-column windows in shared memory; the trace is stored anti-diagonal-major (the 32
 // cells of a step side by side, four steps per word: one coalesced store per four steps), a byte per cell for the affine
-// modes and two bits for edit distance, in shared memory when it fits (6 KB per warp) and in an HBM slot otherwise.
+// modes and two bits for edit distance, in shared memory when it fits (8 KB per warp) and in an HBM slot otherwise.
 // Integer ALU work only — not a dense contraction, no tensor cores.
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
@@ -23,7 +23,7 @@
 namespace pv3 {
 
 constexpr int      K3_WARPS  = 8;
-constexpr uint32_t SMEM_POOL = 6144;   // bytes per warp
+constexpr uint32_t SMEM_POOL = 8192;   // bytes per warp: a 64 x 64 affine trace with its boundary arrays fits (3 CTAs per SM either way: 80 registers)
 
 enum : uint32_t { T_D = 1, T_UO = 2, T_U = 4, T_LO = 8, T_L = 16 };
 enum : int { DIR_NONE = -1, DIR_DIAG = 0, DIR_UP = 1, DIR_LEFT = 2 };
@@ -57,7 +57,7 @@ struct StripStage {
 };
 
 uint32_t k3_smem_pool_bytes() { return SMEM_POOL; }
-uint64_t k3_default_grid_warps(int n_sms) { return (uint64_t) n_sms * 4 * K3_WARPS; }
+uint64_t k3_default_grid_warps(int n_sms) { return (uint64_t) n_sms * 3 * K3_WARPS; }     // 3 CTAs per SM are resident (80 registers, 72 KB of shared memory)
 
 template <bool PACKED>   // PACKED: SEQ in BAM's 4-bit packing (K1Params::seq_len)
 __global__ void __launch_bounds__(K3_WARPS * 32)
