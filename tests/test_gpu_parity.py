@@ -812,3 +812,39 @@ def test_wide_window_workload(gpu, port, window, blocks):
             for dp_min in (16384, 0):
                 idx.ctx.set_dp_thread_min(dp_min)
                 assert_same(idx.project_batch(b, go, ge), exp, b, f"wide window {window} qual={with_qual} go={go} dp_min={dp_min}")
+
+
+def test_chromosome_shape_paired_reads_all_paths(gpu, port):
+    """BASELINE configs[2]'s shape scaled down: an MSA built as gap words with REF + 9 founders, paired 150-bp reads sampled
+    anywhere in it and as a sorted-BAM window, mates projected in the same call (project_alignments.cc:721-732 + :880-906) —
+    through the thread kernel (mates inside it), the warp and word kernels (separate position pass), the device entry and the
+    host entry with the compact encoding."""
+    import torch
+    from panvc3_b200.device import DeviceBatch, project_device
+    from panvc3_b200.projector import MsaIndex
+    from panvc3_b200.workload import sample_reads_words, sorted_bam_window, synth_msa_words
+    msa = synth_msa_words(6_000_000, 9, seed=31, p_gap=0.003, mean_gap=8, snp=0.002)
+    gap_rows, refs = msa.index_inputs()
+    assert len(gap_rows) == 10
+    idx = MsaIndex.from_rows(gap_rows, refs)
+    oi = port.make_index(gap_rows, refs)
+    idx.ctx.set_params(0, -1)
+    for what, (b, mates) in (("anywhere", sample_reads_words(msa, 60_000, 150, seed=4, ins=0.002, dele=0.002)),
+                             ("sorted window", sorted_bam_window(msa, 40_000, 150, seed=6, total_reads=2_000_000))):
+        exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+        assert not exp.flags.any()
+        k = 4000
+        mexp = np.array([oi.project_position(int(r), 0, int(p)) for r, p in zip(mates[0][:k], mates[2][:k])], dtype=np.uint64)
+        for path in (0, 1, 2):
+            idx.ctx.set_kernel_path(path)
+            got = idx.ctx.project(b, mates=mates)
+            assert_same(got, exp, b, f"{what}, host entry, path {path}")
+            assert np.array_equal(got.mate_dst_pos[:k], mexp), f"{what}: mate positions, path {path}"
+        idx.ctx.set_kernel_path(0)
+        got = idx.ctx.project(b.to_bam4(), mates=mates, compact=b.to_bam4().compact_arrays(mates))
+        assert_same(got, exp, b, f"{what}, compact encoding")
+        assert np.array_equal(got.mate_dst_pos[:k], mexp)
+        dout = project_device(idx.ctx, DeviceBatch(b, torch.device("cuda", 0), mates=mates))
+        dh = dout.to_host()
+        assert_same(dh, exp, b, f"{what}, device entry")
+        assert np.array_equal(dh.mate_dst_pos[:k], mexp)
