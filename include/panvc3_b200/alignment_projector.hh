@@ -150,6 +150,16 @@ namespace panvc3_b200 {
 		char const *last_error() const { return pv3_last_error(m_ctx); }
 		static constexpr bool needs_offsets = false;       // pv3_project orders the arenas over the whole batch
 
+		// Device time of the DP + traceback kernels of the last projection call, in milliseconds. The reference's CLI times
+		// each realignment between the two delegate callbacks (project_alignments.cc:932-944); on the GPU all runs of a batch
+		// are realigned together, so the callbacks cannot bracket them — a caller that reports "time spent realigning" adds
+		// this figure per call instead.
+		double last_realignment_ms() const
+		{
+			pv3_timing t{};
+			return PV3_OK == pv3_get_timing(m_ctx, &t) ? double(t.ms_realign) : 0.0;
+		}
+
 		// msa_index::sequence_entry::project_position (msa_index.hh:253-258)
 		std::uint64_t project_position(std::uint32_t const src_row, std::uint32_t const dst_row, std::uint64_t const pos)
 		{
@@ -337,7 +347,8 @@ namespace panvc3_b200 {
 	{
 		virtual ~basic_alignment_projector_delegate() {}
 		// On the GPU all runs of a record are realigned inside one call, so both callbacks fire once per realigned run
-		// after the call returns; they cannot bracket the DP (documented deviation).
+		// after the call returns; they cannot bracket the DP (documented deviation). A timer driven by them reads
+		// ~0 ns: use device_index::last_realignment_ms() for the time the DP kernels took.
 		virtual void alignment_projector_begin_realignment(basic_alignment_projector <t_traits> const &) = 0;
 		virtual void alignment_projector_end_realignment(basic_alignment_projector <t_traits> const &) = 0;
 	};
