@@ -89,6 +89,19 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src)
 	return ((uint64_t) hi << 32) | lo;
 }
 
+__device__ __forceinline__ uint64_t shfl_up_u64(uint64_t v, int delta)
+{
+	unsigned lo = __shfl_up_sync(FULL, (unsigned) v, delta);
+	unsigned hi = __shfl_up_sync(FULL, (unsigned) (v >> 32), delta);
+	return ((uint64_t) hi << 32) | lo;
+}
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int mask)
+{
+	unsigned lo = __shfl_xor_sync(FULL, (unsigned) v, mask);
+	unsigned hi = __shfl_xor_sync(FULL, (unsigned) (v >> 32), mask);
+	return ((uint64_t) hi << 32) | lo;
+}
+
 // Position (0..31) of the k-th (1-based) set bit of x; caller guarantees popc(x) >= k. Branch-free popcount descent.
 __device__ __forceinline__ unsigned select_in_u32(unsigned x, unsigned k)
 {

@@ -293,7 +293,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 			bool const affine = has_qual || P.gap_open != 0;
 			unsigned long long cells = 0, path = 0, pool = 0, max_pool = 0;
 			uint32_t n_big = 0;
-			n_runs = scan_runs<false>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine, false, &n_big);
+			n_runs = scan_runs_warp<false>(ops, res.n_ops, res.dst_pos, rec, nq, ref_n, nullptr, nullptr, res.flags, cells, path, pool, max_pool, affine, &n_big);
 			if (!res.flags && n_runs) {
 				if (lane == 0) {
 					job_base = atomicAdd(&P.counters->job_cursor, (unsigned long long) n_runs);
@@ -309,7 +309,7 @@ __device__ void finish_record(const K1Params &P, uint64_t rec, RecordResult &res
 					if (lane == 0) atomicOr(&P.counters->overflow, 2u);
 				} else {
 					uint32_t f = 0; unsigned long long a = 0, b = 0, c = 0, d = 0;
-					scan_runs<true>(ops, 1, res.n_ops, res.dst_pos, rec, nq, ref_n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine, lane == 0);
+					scan_runs_warp<true>(ops, res.n_ops, res.dst_pos, rec, nq, ref_n, P.jobs + job_base, P.rr + 4 * job_base, f, a, b, c, d, affine);
 				}
 			} else n_runs = 0;
 		}
