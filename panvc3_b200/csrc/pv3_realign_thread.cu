@@ -37,10 +37,17 @@ __device__ __forceinline__ int pick(uint32_t t)
 
 } // namespace
 
+constexpr unsigned K3T_THREADS = 256;
+
 template <bool PACKED>   // PACKED: SEQ in BAM's 4-bit packing (K1Params::seq_len)
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(K3T_THREADS)
 k3_thread_kernel(K3Params P)
 {
+	// A warp runs as long as its largest run (round-2 capture: 9.2 of 32 lanes active, runs of 1 to 49 cells side by side), so
+	// the CTA first sorts its 256 consecutive runs by cell count (counting sort in shared memory): the warps then hold
+	// octiles of the size distribution instead of random mixtures.
+	__shared__ uint32_t s_hist[64];
+	__shared__ uint16_t s_perm[K3T_THREADS];
 	K1Params const &B = P.k1;
 	unsigned const lane = lane_id();
 	int32_t const gext = B.gap_ext, gopen = B.gap_open + B.gap_ext;   // affine_gap_policy.hpp:183-190
@@ -48,9 +55,31 @@ k3_thread_kernel(K3Params P)
 	// rewrite and the DP. Few small runs: the warp-per-run kernel takes them all (it reads the same counters and decides alike).
 	uint64_t const n_jobs = dp_n_jobs(B.counters, P.n_jobs);
 	if (!dp_use_thread_kernel(B.counters, n_jobs, P.dp_thread_min)) return;
-	uint64_t const stride = (uint64_t) gridDim.x * blockDim.x;
-	for (uint64_t jbase = ((uint64_t) blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; jbase < n_jobs; jbase += stride) {
-	uint64_t const jid = jbase + lane;
+	uint64_t const stride = (uint64_t) gridDim.x * K3T_THREADS;
+	for (uint64_t cbase = (uint64_t) blockIdx.x * K3T_THREADS; cbase < n_jobs; cbase += stride) {
+	{
+		uint64_t const j0 = cbase + threadIdx.x;
+		uint32_t key = 63;                                           // past the end
+		if (j0 < n_jobs) {
+			uint32_t const r = B.jobs[j0].ref_len, q = B.jobs[j0].qry_len;
+			key = dp_job_is_small(r, q) ? r * q : 62u;                 // (R + 1)(Q + 1) <= 64 ⇒ R Q <= 49; the warp kernel's runs together
+		}
+		if (threadIdx.x < 64) s_hist[threadIdx.x] = 0;
+		__syncthreads();
+		uint32_t const in_bin = atomicAdd(&s_hist[key], 1u);
+		__syncthreads();
+		if (threadIdx.x < 32) {
+			uint32_t const a = s_hist[2 * lane], b = s_hist[2 * lane + 1];
+			uint32_t incl = a + b;
+			#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { uint32_t const t = __shfl_up_sync(FULL, incl, d); if ((int) lane >= d) incl += t; }
+			s_hist[2 * lane] = incl - a - b; s_hist[2 * lane + 1] = incl - b;
+		}
+		__syncthreads();
+		s_perm[s_hist[key] + in_bin] = (uint16_t) threadIdx.x;
+		__syncthreads();
+	}
+	uint64_t const jid = cbase + s_perm[threadIdx.x];
 
 	uint32_t R = 0, Q = 0, qry_loc = 0;
 	uint64_t rec = 0, ref_loc = 0;
@@ -208,8 +237,8 @@ void launch_k3_thread(const K3Params &P, cudaStream_t stream)
 {
 	// P.n_jobs known (> 0): one pass over the runs; ~0: read on the device, a resident grid strides over them
 	if (!P.n_jobs) return;
-	unsigned const threads = 128;
-	uint64_t const want = P.n_jobs == ~0ull ? (uint64_t) P.grid_hint : (P.n_jobs + threads - 1) / threads;
+	unsigned const threads = K3T_THREADS;
+	uint64_t const want = P.n_jobs == ~0ull ? (uint64_t) (P.grid_hint + 1) / 2 : (P.n_jobs + threads - 1) / threads;
 	unsigned const blocks = (unsigned) (want ? want : 1);
 	if (P.k1.seq_len) k3_thread_kernel <true><<<blocks, threads, 0, stream>>>(P);
 	else k3_thread_kernel <false><<<blocks, threads, 0, stream>>>(P);
