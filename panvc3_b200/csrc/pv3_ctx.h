@@ -52,6 +52,8 @@ struct WorkSet {
 	DevBuf   st[12];
 	uint64_t arena_cap_hint = 0, rr_cap_hint = 0, dp_arena_hint = 0, pool_hint = 0;
 	bool     qual_bulk = false;         // the last chunk here realigned many records: upload QUAL in full instead of reading it in place
+	int      k1t_layout = -1;           // layout of this set's last thread-kernel launch (-1: not tunable) and its records
+	uint64_t k1t_records = 0;
 	bool     many_runs = false;
 	uint64_t expect_deferred = 0;       // the last batch's deferred records (+ 25 %): sizes the grids of the deferred-record kernels
 	void release();
@@ -77,6 +79,10 @@ struct pv3_ctx {
 	std::vector <pv3::RowDesc> h_row_desc;
 	std::vector <pv3::RefDesc> h_ref_desc;
 	uint64_t     index_bytes = 0;
+	// Thread kernel layout for a large target, chosen by measurement: ns per record of the two layouts (moving average of the
+	// kernel's event-timed launches), the other one probed again every 32nd launch and whenever a layout's time moves by more
+	// than 15 % (the input changed, e.g. from scattered to coordinate-sorted records).
+	struct LayoutTuner { float ns_per_rec[2] = { 0, 0 }; uint32_t seen[2] = { 0, 0 }; uint32_t launches = 0; bool reprobe = false; } tuner;
 	uint64_t     target_code_bytes = 0;   // packed target codes of all references (chooses the thread kernel's layout)
 
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults

@@ -202,7 +202,9 @@ void launch_unpack_in(const UnpackParams &P, cudaStream_t stream);
 void launch_pack_out(const PackParams &P, cudaStream_t stream);
 
 void launch_k1(const K1Params &P, int n_sms, cudaStream_t stream);          // warp per record (general)
-void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream);   // thread per record, run walk (v4-v13)
+void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream, int layout = -1);
+bool k1_thread_layout_is_tunable(uint64_t target_code_bytes);                 // large target and no PV3_K1T_VARIANT override
+   // thread per record, run walk (v4-v13)
 void launch_k1_word(const K1Params &P, int n_sms, cudaStream_t stream);
 // the deferred list of either thread kernel cut into segments of <= 64 reference bases, one thread per segment (long reads)
 // `expected`: the deferred records the host expects (last batch's count, read lengths): sizes the resident grids, which read

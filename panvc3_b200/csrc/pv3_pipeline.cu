@@ -112,7 +112,15 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 		else {
 			K1Params PT = P;
 			if (in.mate_row && out.mate_dst_pos) { PT.mate_row = in.mate_row; PT.mate_pos = in.mate_pos; PT.mate_dst_pos = out.mate_dst_pos; mates_done = true; }
-			launch_k1_thread(PT, ctx->n_sms, ctx->target_code_bytes, stream);
+			ws.k1t_layout = -1; ws.k1t_records = in.n;
+			if (k1_thread_layout_is_tunable(ctx->target_code_bytes)) {
+				auto &T = ctx->tuner;
+				uint32_t const c = T.launches++;
+				int const best = (T.seen[0] && T.seen[1]) ? (T.ns_per_rec[1] < T.ns_per_rec[0] ? 1 : 0) : (T.seen[0] ? 1 : 0);
+				ws.k1t_layout = (T.seen[0] && T.seen[1] && ((c & 31u) == 31u || T.reprobe)) ? 1 - best : best;
+				T.reprobe = false;
+			}
+			launch_k1_thread(PT, ctx->n_sms, ctx->target_code_bytes, stream, ws.k1t_layout);
 		}
 		PV3_CUDA(ctx, cudaGetLastError());
 		PV3_CUDA(ctx, cudaEventRecord(ws.ev[4], stream));
@@ -202,8 +210,22 @@ void harvest_timing(pv3_ctx *ctx, WorkSet &ws, float *ms /* rewrite, realign, sp
 	if (cudaEventElapsedTime(&t, ws.ev[1], ws.ev[2]) == cudaSuccess) ms[1] += t;
 	if (cudaEventElapsedTime(&t, ws.ev[2], ws.ev[3]) == cudaSuccess) ms[2] += t;
 	if (cudaEventElapsedTime(&t, ws.ev[0], ws.ev[3]) == cudaSuccess) ms[3] += t;
-	if (cudaEventElapsedTime(&t, ws.ev[0], ws.ev[4]) == cudaSuccess) ms[4] += t;
-	(void) ctx;
+	if (cudaEventElapsedTime(&t, ws.ev[0], ws.ev[4]) == cudaSuccess) {
+		ms[4] += t;
+		if (ws.k1t_layout >= 0 && ws.k1t_records >= 65536) {          // (small launches are latency, not layout)
+			auto &T = ctx->tuner;
+			float const ns = t * 1e6f / (float) ws.k1t_records;
+			float const old = T.ns_per_rec[ws.k1t_layout];
+			bool const moved = T.seen[ws.k1t_layout] && (ns > 1.15f * old || ns < 0.85f * old);
+			T.ns_per_rec[ws.k1t_layout] = (T.seen[ws.k1t_layout] && !moved) ? 0.5f * (old + ns) : ns;
+			T.seen[ws.k1t_layout] = 1;
+			if (moved) T.reprobe = true;
+			static bool const trace = getenv("PV3_TRACE") != nullptr;
+			if (trace) fprintf(stderr, "[pv3 trace] thread kernel layout %d: %.3f ns per record (staged %.3f, through L1 %.3f)%s\n", ws.k1t_layout, ns,
+				T.ns_per_rec[0], T.ns_per_rec[1], moved ? " — moved, probing the other layout" : "");
+		}
+		ws.k1t_layout = -1;
+	}
 }
 
 // device alias of pinned (mapped) host memory, or null when the pointer is pageable / foreign

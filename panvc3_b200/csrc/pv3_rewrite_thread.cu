@@ -560,11 +560,18 @@ static void launch_variant(const K1Params &P, int n_sms, cudaStream_t stream)
 // 4 = as 2 without the prefetch.
 constexpr uint64_t L1_RESIDENT_TARGET_BYTES = 512 * 1024;   // between the 0.2 MB and 2 MB measurements
 
-void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream)
+bool k1_thread_layout_is_tunable(uint64_t target_code_bytes) { return target_code_bytes > L1_RESIDENT_TARGET_BYTES && !getenv("PV3_K1T_VARIANT"); }
+
+// layout: -1 = by target size; 0 = staged windows, 1 = through L1 — the caller's measured choice for a large target (with a
+// large target the better layout depends on the ORDER of the records: staged wins when they are scattered over the genome,
+// through-L1 when neighbours share windows, as in a coordinate-sorted BAM; configs[2], ms per 10^6 records, staged /
+// through-L1: scattered 0.566 / 0.672, sorted window 0.317 / 0.226 — profiles/r2_v25_chr_layout_variants.json)
+void launch_k1_thread(const K1Params &P, int n_sms, uint64_t target_code_bytes, cudaStream_t stream, int layout)
 {
 	const char *e = getenv("PV3_K1T_VARIANT");                          // read per launch: the parity tests switch layouts in-process
 	int const forced = (e && *e >= '0' && *e <= '4') ? (*e - '0') : -1;
-	int const variant = forced >= 0 ? forced : (target_code_bytes <= L1_RESIDENT_TARGET_BYTES ? 4 : 0);
+	int const by_size = target_code_bytes <= L1_RESIDENT_TARGET_BYTES ? 4 : 0;
+	int const variant = forced >= 0 ? forced : (by_size == 4 || layout < 0) ? by_size : (layout == 0 ? 0 : 2);
 	switch (variant) {
 		case 0: launch_variant <0>(P, n_sms, stream); break;
 		case 1: launch_variant <1>(P, n_sms, stream); break;
