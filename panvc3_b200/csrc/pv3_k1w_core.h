@@ -47,9 +47,8 @@ namespace k1w {
 // Quotas of one instantiation of the core. ST: threads per tile (the stride of the per-thread arrays, 1 on the host);
 // NW: 32-column words per span (including the offset of the start column in its word); NBRK: pass-through ops (I S H P
 // with a non-zero count); OUTQ: staged output ops.
-template <int t_st> struct CfgRecord  { static constexpr int ST = t_st, NW = 10, NBRK = 6, OUTQ = 24; };   // whole 150-bp records (K1W)
-template <int t_st> struct CfgSegment { static constexpr int ST = t_st, NW = 7,  NBRK = 8, OUTQ = 32; };   // <= 128-base segments of long records (K1S)
-constexpr uint32_t QMAX  = 192;         // query bases per record / segment
+template <int t_st> struct CfgRecord  { static constexpr int ST = t_st, NW = 10, NBRK = 6, OUTQ = 24; static constexpr uint32_t QMAX = 192; };   // whole 150-bp records (K1W)
+template <int t_st> struct CfgSegment { static constexpr int ST = t_st, NW = 7,  NBRK = 8, OUTQ = 32; static constexpr uint32_t QMAX = 192; };   // <= 128-base segments of long records (K1S)
 constexpr uint32_t CLAMP = 1u << 20;
 constexpr uint32_t NOBRK = 0xffffffffu;
 
@@ -442,7 +441,7 @@ PV3_HD int build_span(SpanIn const &I, OpRange const &R, Lane <C> const &L, Span
 	st.span_begin = st.span_end = st.w_end = st.n_dbase = 0; st.n_qbase = oi.tot_q;
 	if (oi.bad) return 1;
 	if ((uint64_t) oi.tot_ref > I.src_left || oi.tot_ref > (uint32_t) NW * 32u) return 1;            // POS_OOB or a long span
-	if ((uint64_t) I.q_start + oi.tot_q > (uint64_t) I.nq || I.nq > QMAX) return 1;                     // QUERY_OOB is possible
+	if ((uint64_t) I.q_start + oi.tot_q > (uint64_t) I.nq || I.nq > C::QMAX) return 1;                     // QUERY_OOB is possible
 	if (!EV && !oi.simple) return 2;
 	if (!load_span <C>(I.Sp, I.Dp, I.c_lo6, oi.tot_ref, L, st.span_begin, st.span_end, st.n_dbase)) return 1;
 	if (I.e_start + st.n_dbase > I.ref_n) return 1;                                                    // REF_OOB is possible

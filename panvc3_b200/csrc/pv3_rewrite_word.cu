@@ -197,7 +197,7 @@ k1_word_kernel(K1Params P)
 					e0 = rank0_thread(D, c0);                                                      // :52
 				}
 				c0_keep = c0;
-				if (S.n_bits != D.n_bits || e0 > R.n || nc64 >= 0x8000ull || spos >= S.n_zeros || nq > k1w::QMAX) defer = true;   // unusual: the general kernel guards it
+				if (S.n_bits != D.n_bits || e0 > R.n || nc64 >= 0x8000ull || spos >= S.n_zeros || nq > WC::QMAX) defer = true;   // unusual: the general kernel guards it
 				if (!defer && !flags) {
 					// the window of packed target codes C2 will read: towards L1 while the masks are built
 					const uint8_t *rp = R.codes4 + ((e0 & ~31ull) >> 1);

@@ -19,6 +19,7 @@ namespace seg {
 
 constexpr uint32_t RSEG     = 128;     // reference-consuming bases per segment ...
 constexpr uint32_t QSEG     = 160;     // ... and query bases per segment (M = X bases + small I / S ops): the quotas of the core must hold them
+// (256 / 288 with an 11-word core was measured slower: 15.4 instead of 14.2 ms per 5 x 10^5 10-kb reads — fewer resident tiles, two staging rounds)
 constexpr uint32_t RSEG_DENSE = 64;    // the same where the record or the MSA around it is dense in events (see choose_segment_size):
 constexpr uint32_t QSEG_DENSE = 96;    // more ops per base, and a segment's output has to fit SegCfg::OUTQ
 constexpr uint32_t BIG_PASS = 32;      // an I / S op longer than this is a segment of its own (nothing of the query is compared in it)
