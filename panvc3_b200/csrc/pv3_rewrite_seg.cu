@@ -63,10 +63,56 @@ __device__ __forceinline__ uint32_t bam4_word_to_ranks_s(uint32_t w)
 
 } // namespace
 
+// The planner's cursor (seg::RowCursor) with the next 512 columns of both rows in shared memory: a thread walks ~160 words of
+// each row per 10-kb read, and with one dependent global load per word the plan kernel was a chain of L2 round trips (IPC 0.66,
+// `lg_throttle` and `long_scoreboard` at 11 cycles per issue each). Here eight words per row are fetched together (four 16-byte
+// loads in flight) and the walk reads them from shared memory. Same results as RowCursor::advance (which the CPU emulation
+// checks against select / rank); rows are padded with 72 all-ones words, so reading ahead is safe.
+constexpr int PLAN_THREADS = 128, PLAN_CHUNK = 8;
+struct PlanCache { uint64_t s[PLAN_CHUNK][PLAN_THREADS], d[PLAN_CHUNK][PLAN_THREADS]; };
+
+struct CachedRowCursor {
+	const uint64_t *S, *D;
+	uint64_t c, e;
+	uint64_t w0;                       // first word in the cache (even), ~0: nothing cached
+	PlanCache *pc; unsigned t;
+	__device__ __forceinline__ void fill(uint64_t w)
+	{
+		w0 = w & ~1ull;                  // 16-byte aligned (rows are 16-byte aligned allocations)
+		const ulonglong2 *ps = reinterpret_cast <const ulonglong2 *>(S + w0), *pd = reinterpret_cast <const ulonglong2 *>(D + w0);
+		ulonglong2 a[PLAN_CHUNK / 2], b[PLAN_CHUNK / 2];
+		#pragma unroll
+		for (int i = 0; i < PLAN_CHUNK / 2; ++i) { a[i] = __ldg(ps + i); b[i] = __ldg(pd + i); }
+		#pragma unroll
+		for (int i = 0; i < PLAN_CHUNK / 2; ++i) {
+			pc->s[2 * i][t] = ~a[i].x; pc->s[2 * i + 1][t] = ~a[i].y;
+			pc->d[2 * i][t] = ~b[i].x; pc->d[2 * i + 1][t] = ~b[i].y;
+		}
+	}
+	__device__ __forceinline__ void advance(uint32_t k)      // right behind the k-th source base at or after c (k >= 1, the row has it)
+	{
+		uint64_t w = c >> 6;
+		uint64_t from = ~0ull << (c & 63u);
+		for (;;) {
+			if (w0 == ~0ull || w < w0 || w >= w0 + PLAN_CHUNK) fill(w);
+			uint64_t const sw = pc->s[w - w0][t] & from, dw = pc->d[w - w0][t] & from;
+			uint32_t const n = seg::popc64(sw);
+			if (k <= n) {
+				uint32_t const pos = seg::select64(sw, k);
+				e += seg::popc64(pos == 63u ? dw : (dw & ((2ull << pos) - 1ull)));
+				c = w * 64 + pos + 1;
+				return;
+			}
+			k -= n; e += seg::popc64(dw); ++w; from = ~0ull;
+		}
+	}
+};
+
 // One thread per deferred record. Records that cannot be planned go straight to deferred2.
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(PLAN_THREADS)
 k1_plan_kernel(K1Params P)
 {
+	__shared__ PlanCache cache;
 	uint64_t const n_items = (uint64_t) *((volatile const unsigned long long *) &P.counters->n_deferred);
 	uint64_t const stride = (uint64_t) gridDim.x * blockDim.x;
 	seg::SegDesc *segs = (seg::SegDesc *) P.segs;
@@ -79,7 +125,7 @@ k1_plan_kernel(K1Params P)
 		// the walk over the two rows needs a record the reference would not abort on (ids, start position, enough source bases)
 		uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec);
 		uint64_t const spos = __ldg(P.src_pos + rec);
-		seg::RowCursor cur; cur.S = nullptr; cur.D = nullptr; cur.c = 0; cur.e = 0;
+		CachedRowCursor cur; cur.S = nullptr; cur.D = nullptr; cur.c = 0; cur.e = 0; cur.w0 = ~0ull; cur.pc = &cache; cur.t = threadIdx.x;
 		if (nc64 < (1ull << 20) && sr < P.n_rows && dr < P.n_rows) {
 			RowDesc const S = P.rows[sr], D = P.rows[dr];
 			if (S.n_bits == D.n_bits && spos < S.n_zeros) {
@@ -104,7 +150,7 @@ k1_plan_kernel(K1Params P)
 		uint32_t w = 0;
 		seg::plan_segments(cig, (uint32_t) nc64, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs, uint32_t rc) {
 			seg::SegDesc d;
-			d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.ref_count = rc;
+			d.rec = rec; d.k0 = k0; d.n_k = (uint8_t) (k1 - k0); d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = (uint8_t) kind; d.ref_count = (uint16_t) rc;
 			d.c_start = cur.c; d.e_start = cur.e;                 // the first base's column, or right behind the previous segment's last base
 			if (rc) cur.advance(rc);
 			out[w++] = d;
@@ -112,7 +158,7 @@ k1_plan_kernel(K1Params P)
 	}
 }
 
-__global__ void __launch_bounds__(ST)
+__global__ void __launch_bounds__(ST)      // (94 registers, 20 tiles per SM; capped at 80 for 24 tiles it spills and is 20 % slower)
 k1_segment_kernel(K1Params P)
 {
 	extern __shared__ __align__(16) uint8_t smem_raw_s[];
@@ -145,9 +191,9 @@ k1_segment_kernel(K1Params P)
 			d = segs[s];
 			uint64_t const rec = d.rec;
 			uint64_t const cbase = __ldg(P.cig_off + rec);
-			opr.cig = P.cig + cbase; opr.k0 = d.k0; opr.k1 = d.k1; opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt;
+			opr.cig = P.cig + cbase; opr.k0 = d.k0; opr.k1 = d.k1(); opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt;
 			if (d.kind == seg::KIND_CORE) {
-				opr.first_val = d.k1 > d.k0 ? __ldg(opr.cig + d.k0) : 0u;
+				opr.first_val = d.n_k != 0 ? __ldg(opr.cig + d.k0) : 0u;
 				uint32_t const sr = __ldg(P.src_row + rec), dr = __ldg(P.dst_row + rec), rf = __ldg(P.dst_ref + rec);
 				if (sr >= P.n_rows || dr >= P.n_rows || rf >= P.n_refs) fail = true;      // the general kernel flags the record
 				else {
@@ -214,7 +260,7 @@ k1_segment_kernel(K1Params P)
 		}
 		__syncthreads();        // the staged query is dead from here on: fin overwrites it
 		if (core) n_ops = k1w::emit_ops <SC, true>(L, st.n_brk, opr, st.w_end, adj);
-		else if (active && !fail) n_ops = seg::emit_pass_segment <SC>(opr.cig, d.k0, d.k1, L);      // KIND_PASS
+		else if (active && !fail) n_ops = seg::emit_pass_segment <SC>(opr.cig, d.k0, d.k1(), L);      // KIND_PASS
 		if (n_ops > (uint32_t) SC::OUTQ) { fail = true; }
 		if (fail) n_ops = 0;
 		// segment op arena: one atomic per warp
@@ -255,7 +301,7 @@ void launch_k1_segments(const K1Params &P, int n_sms, uint64_t expected, cudaStr
 	uint64_t plan_ctas = (expected + 127) / 128 + 4, seg_ctas = expected * 4 + 32;
 	if (plan_ctas > (uint64_t) n_sms * 8) plan_ctas = (uint64_t) n_sms * 8;
 	if (seg_ctas > (uint64_t) n_sms * per_sm) seg_ctas = (uint64_t) n_sms * per_sm;
-	k1_plan_kernel<<<(unsigned) plan_ctas, 128, 0, stream>>>(P);
+	k1_plan_kernel<<<(unsigned) plan_ctas, PLAN_THREADS, 0, stream>>>(P);
 	k1_segment_kernel<<<(unsigned) seg_ctas, ST, bytes, stream>>>(P);
 }
 

@@ -28,15 +28,18 @@ constexpr uint32_t UNPLANNABLE = 0xffffffffu;
 
 enum : uint32_t { KIND_CORE = 0, KIND_PASS = 1 };
 
-struct SegDesc {
+struct alignas(16) SegDesc {         // 48 bytes: three 16-byte stores by the planner, three loads by the segment kernel
 	uint64_t rec;
-	uint32_t k0, k1;                 // input ops [k0, k1) of the record
-	uint32_t first_cnt, last_cnt;    // counts of op k0 / op k1 - 1 inside this segment when they are cut (~0: whole op)
-	uint32_t ref_start, q_start;     // reference-consuming / query bases of the record before the segment
-	uint32_t kind;
-	uint32_t ref_count;              // reference-consuming bases of the segment
 	uint64_t c_start, e_start;       // its start column and rank0_dst(start column): found by the planner's walk over the two rows
+	uint32_t k0;                     // input ops [k0, k0 + n_k) of the record
+	uint32_t first_cnt, last_cnt;    // counts of the first / last op inside this segment when they are cut (~0: whole op)
+	uint32_t ref_start, q_start;     // reference-consuming / query bases of the record before the segment
+	uint16_t ref_count;              // reference-consuming bases of the segment (<= RSEG)
+	uint8_t  n_k;                    // <= MAXOPS
+	uint8_t  kind;
+	PV3_HD uint32_t k1() const { return k0 + n_k; }
 };
+static_assert(sizeof(SegDesc) == 48, "SegDesc layout");
 
 typedef k1w::CfgSegment <32> SegCfg;     // the quotas the planner cuts for (ST is irrelevant to it)
 

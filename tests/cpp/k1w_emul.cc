@@ -184,7 +184,7 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 		if (ns == seg::UNPLANNABLE || (uint64_t) total_ref > S.n_zeros - spos0) continue;
 		seg::RowCursor cur; cur.S = S.words.data(); cur.D = D.words.data(); cur.c = c0; cur.e = dst_pos[rec];
 		seg::plan_segments(rc, (uint32_t) nc, [&](uint32_t kind, uint32_t k0, uint32_t k1, uint32_t fc, uint32_t lc, uint32_t rs, uint32_t qs, uint32_t rcnt) {
-			seg::SegDesc d; d.rec = rec; d.k0 = k0; d.k1 = k1; d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = kind; d.ref_count = rcnt;
+			seg::SegDesc d; d.rec = rec; d.k0 = k0; d.n_k = (uint8_t) (k1 - k0); d.first_cnt = fc; d.last_cnt = lc; d.ref_start = rs; d.q_start = qs; d.kind = (uint8_t) kind; d.ref_count = (uint16_t) rcnt;
 			d.c_start = cur.c; d.e_start = cur.e;
 			if (rcnt) cur.advance(rcnt);
 			segs.push_back(d);
@@ -204,7 +204,7 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 			uint32_t cmp[SC::NW], ins[SC::NW], del[SC::NW], xm[SC::NW], brk[SC::NBRK], fin[SC::OUTQ];
 			k1w::Lane <SC> L; L.cmp = cmp; L.ins = ins; L.del = del; L.xm = xm; L.brk = brk; L.fin = fin;
 			uint32_t no = 0;
-			if (d.kind == seg::KIND_PASS) no = seg::emit_pass_segment <SC>(rc, d.k0, d.k1, L);
+			if (d.kind == seg::KIND_PASS) no = seg::emit_pass_segment <SC>(rc, d.k0, d.k1(), L);
 			else {
 				uint64_t const spos = spos0 + d.ref_start;
 				uint64_t const c_start = d.c_start, e_start = d.e_start;        // the planner's walk; cross-checked against select / rank
@@ -224,7 +224,7 @@ uint64_t k1w_emul_segments(void *p, uint64_t n, const uint32_t *src_row, const u
 				k1w::SpanIn I;
 				I.Sp = S.words.data() + (c_start >> 6); I.Dp = D.words.data() + (c_start >> 6); I.c_lo6 = (uint32_t) c_start & 63u;
 				I.src_left = S.n_zeros - spos; I.e_start = e_start; I.ref_n = R.n; I.nq = nq_seg; I.q_start = 0;
-				k1w::OpRange opr; opr.cig = rc; opr.k0 = d.k0; opr.k1 = d.k1; opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt; opr.first_val = rc[d.k0];
+				k1w::OpRange opr; opr.cig = rc; opr.k0 = d.k0; opr.k1 = d.k1(); opr.first_cnt = d.first_cnt; opr.last_cnt = d.last_cnt; opr.first_val = rc[d.k0];
 				k1w::SpanState st;
 				if (k1w::build_span <SC, true>(I, opr, L, st)) { fail = true; break; }
 				uint64_t const ea = e_start & ~31ull;
