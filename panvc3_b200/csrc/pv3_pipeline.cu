@@ -116,8 +116,13 @@ int enqueue_kernels(pv3_ctx *ctx, WorkSet &ws, DevBatch const &B, uint64_t &laun
 			if (k1_thread_layout_is_tunable(ctx->target_code_bytes)) {
 				auto &T = ctx->tuner;
 				uint32_t const c = T.launches++;
-				int const best = (T.seen[0] && T.seen[1]) ? (T.ns_per_rec[1] < T.ns_per_rec[0] ? 1 : 0) : (T.seen[0] ? 1 : 0);
-				ws.k1t_layout = (T.seen[0] && T.seen[1] && ((c & 31u) == 31u || T.reprobe)) ? 1 - best : best;
+				// two samples of each layout before either is trusted: a context's first launch is cold (page faults of fresh
+				// allocations, instruction cache) and once made the staged layout look slower than it is
+				if (T.seen[0] < 2 || T.seen[1] < 2) ws.k1t_layout = T.seen[0] <= T.seen[1] ? 0 : 1;
+				else {
+					int const best = T.ns_per_rec[1] < T.ns_per_rec[0] ? 1 : 0;
+					ws.k1t_layout = ((c & 31u) == 31u || T.reprobe) ? 1 - best : best;
+				}
 				T.reprobe = false;
 			}
 			launch_k1_thread(PT, ctx->n_sms, ctx->target_code_bytes, stream, ws.k1t_layout);
@@ -218,7 +223,7 @@ void harvest_timing(pv3_ctx *ctx, WorkSet &ws, float *ms /* rewrite, realign, sp
 			float const old = T.ns_per_rec[ws.k1t_layout];
 			bool const moved = T.seen[ws.k1t_layout] && (ns > 1.15f * old || ns < 0.85f * old);
 			T.ns_per_rec[ws.k1t_layout] = (T.seen[ws.k1t_layout] && !moved) ? 0.5f * (old + ns) : ns;
-			T.seen[ws.k1t_layout] = 1;
+			if (T.seen[ws.k1t_layout] < 2) ++T.seen[ws.k1t_layout];
 			if (moved) T.reprobe = true;
 			static bool const trace = getenv("PV3_TRACE") != nullptr;
 			if (trace) fprintf(stderr, "[pv3 trace] thread kernel layout %d: %.3f ns per record (staged %.3f, through L1 %.3f)%s\n", ws.k1t_layout, ns,
