@@ -278,14 +278,14 @@ class HostBuffers:
         from panvc3_b200.batch import RecordBatch
         from panvc3_b200.capi import PinnedArena, alloc_output
         lib = ctx.lib
-        src = batch.to_bam4() if packed else batch
+        src = batch.to_2bit() if packed == "2bit" else batch.to_bam4() if packed else batch
         self.src = src
         n = batch.n
         self.arena = PinnedArena(lib, src.input_bytes() + n * 80 + 64 * 4096 + (0 if out_view is not None else n * 48 + cig_cap * 4 + rr_cap * 32))
         take = lambda a: None if a is None else self._copy(a)
         self.pb = RecordBatch.__new__(RecordBatch)
-        for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len"):
-            setattr(self.pb, k, take(getattr(src, k)))
+        for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len", "exc_rec", "exc_off"):
+            setattr(self.pb, k, take(getattr(src, k, None)))
         self.mates = None if mates is None else (take(np.ascontiguousarray(mates[0], dtype=np.uint32)), take(np.ascontiguousarray(mates[-1], dtype=np.uint64)))
         self.compact = None
         if compact:
@@ -524,7 +524,7 @@ def run_gpu_arm(args) -> None:
         dist.all_reduce(caps, op=dist.ReduceOp.MAX)
         cig_cap, rr_cap = int(caps[0]), int(caps[1])
         seg, whole, mine, out_alloc, per_rank = shared_output_views(n, cig_cap, rr_cap, world, rank, dist, ctx.lib)
-    hb = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=True, packed=True, out_view=out_alloc)
+    hb = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=True, packed="2bit", out_view=out_alloc)
     for _ in range(max(args.warmup, 1)):
         hb.run(ctx)
     barrier()
@@ -541,7 +541,7 @@ def run_gpu_arm(args) -> None:
     clocks = sampler.stop()
 
     # ---- the same call with the wide encoding of round 1 (u32 ids, u64 offsets, byte SEQ, 36-byte records out) ---------------
-    wide_s, wide = None, None
+    wide_s, wide, bam4_s, bam4 = None, None, None, None
     if not args.no_wide_leg:
         wide = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=False, packed=False)
         for _ in range(2):
@@ -555,11 +555,23 @@ def run_gpu_arm(args) -> None:
         wide_s = (time.perf_counter() - t0) / k
         barrier()
 
+        # ... and with SEQ as a BAM record holds it (4-bit codes), the rest of the compact encoding unchanged
+        bam4 = HostBuffers(ctx, batch, mates, cig_cap, rr_cap, compact=True, packed=True)
+        for _ in range(2):
+            bam4.run(ctx)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            bres = bam4.run(ctx)
+        torch.cuda.synchronize(dev)
+        bam4_s = (time.perf_counter() - t0) / k
+        barrier()
+
     # ---- max over ranks ---------------------------------------------------------------------------------------------
-    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches), (wide_s or 0.0) * 1e3], dtype=torch.float64, device=dev)
+    times = torch.tensor([dev_ms, e2e_s * 1e3, float(gpu_launches), (wide_s or 0.0) * 1e3, (bam4_s or 0.0) * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_ms_max, wide_ms_max = float(times[0]), float(times[1]), float(times[3])
+    dev_ms_max, e2e_ms_max, wide_ms_max, bam4_ms_max = float(times[0]), float(times[1]), float(times[3]), float(times[4])
 
     # ---- A/B: the ordered gather over NVLink (NCCL) that round 1 used, timed on its own -------------------------------------
     gather = None
@@ -636,7 +648,7 @@ def run_gpu_arm(args) -> None:
             "kernels_ms": leg["kernels_ms"],
             "realign_gcups": (stats["dp_cells"] / (leg["kernels_ms"]["realign"] * 1e-3) / 1e9) if leg["kernels_ms"]["realign"] > 0 else None,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(hb.h2d_bytes), "d2h_bytes_per_step": hb.d2h_bytes(e2e_stats),
-                    "encoding": "compact input (u16 ids, u32 positions, lengths instead of offsets, BAM 4-bit SEQ) and narrow ordered output written in place by the last kernel of every chunk; QUAL read in place from pinned memory, only where a run is realigned",
+                    "encoding": "compact input (u16 ids, u32 positions, lengths instead of offsets, SEQ in two bits per base with the N bases listed apart) and narrow ordered output written in place by the last kernel of every chunk; QUAL read in place from pinned memory, only where a run is realigned",
                     "ordered_output": ("every rank writes its shard into its slice of ONE shared pinned buffer (POSIX shared memory + pv3_host_register); the timed region ends when all shards of all steps are there"
                                        if world > 1 else "records in input order in the caller's pinned arrays"),
                     "ms_per_step": e2e_ms_max / args.steps, "h2d_ms": statistics.mean(h2d_ms), "writeback_ms": statistics.mean(d2h_ms),
@@ -646,6 +658,9 @@ def run_gpu_arm(args) -> None:
             "clocks": clocks,
         }
         if wide_s is not None:
+            line["e2e_bam4_seq"] = {"value": n * world / (bam4_ms_max * 1e-3), "unit": UNIT, "ms_per_step": bam4_ms_max, "h2d_bytes_per_step": int(bam4.h2d_bytes),
+                                    "d2h_bytes_per_step": bam4.d2h_bytes(dict(bres.stats)),
+                                    "what": "same call, SEQ in BAM's 4-bit packing (what a BAM record holds) instead of two bits per base + N list"}
             line["e2e_wide_encoding"] = {"value": n * world / (wide_ms_max * 1e-3), "unit": UNIT, "ms_per_step": wide_ms_max,
                                          "h2d_bytes_per_step": int(wide.h2d_bytes), "d2h_bytes_per_step": wide.d2h_bytes(dict(wres.stats)),
                                          "what": "same records, same call, round 1's encoding (u32 ids, u64 offsets and positions, one byte per base, 36-byte records out)"}

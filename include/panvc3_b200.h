@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define PV3_ABI_VERSION 5
+#define PV3_ABI_VERSION 6
 
 typedef struct pv3_ctx pv3_ctx;
 
@@ -94,6 +94,16 @@ typedef struct {
 	const uint32_t *src_pos32, *mate_pos32;
 	const uint16_t *cig_len16;
 	const uint8_t  *has_qual;  /* bit i & 7 of byte i / 8; NULL: no record has QUAL */
+	/* -- ABI 6 (optional) ---------------------------------------------------------------------------------------------
+	 * Two-bit SEQ (pv3_project / pv3_multi_project with compact != 0, instead of seq_bam4): seq holds A C G T as 0 1 2 3,
+	 * FOUR bases per byte, base 4 k + i of a record in bits 2 i .. 2 i + 1 of its byte k, every record starting on a byte;
+	 * seq_off (host) counts these bytes. Bases that are not A C G T (dna5's N) are listed apart: exception j says that base
+	 * exc_off[j] of record exc_rec[j] is N (its two bits are ignored); entries sorted by record. SEQ is 3/4 of what a
+	 * 150-bp record sends over PCIe in the compact encoding, so this is 60 instead of 97 bytes per record. The device
+	 * expands it to the 4-bit layout the kernels read (one pass, 0.03 ms per 10^6 records). */
+	int             seq_2bit;
+	uint64_t        n_seq_exceptions;
+	const uint32_t *exc_rec, *exc_off;
 } pv3_batch_in;
 
 /* Output batch. CIGARs and realigned ranges live in arenas and are addressed per record by (off, len); arena order

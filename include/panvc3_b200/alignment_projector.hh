@@ -489,8 +489,8 @@ namespace panvc3_b200 {
 
 	// The batched entry of the host pipeline: what fills the reference's 4-record tasks
 	// (project-alignments/project_alignments.cc:597-631) packs records here instead, into ONE pinned structure of arrays in
-	// the compact encoding of pv3_batch_in (16-bit ids, 32-bit positions, lengths; SEQ one dna5 rank per byte as seqan3 holds
-	// it); flush() = one pv3_project (or pv3_multi_project) call; results are read in submission order. Register every
+	// the compact encoding of pv3_batch_in (16-bit ids, 32-bit positions, lengths; SEQ packed to two bits per base on
+	// push_back, N bases listed apart); flush() = one pv3_project (or pv3_multi_project) call; results are read in submission order. Register every
 	// sequence entry and contig (register_entry / register_reference) before the first push_back that uses it.
 	template <typename t_traits, typename t_index = device_index>
 	class basic_batch_projector
@@ -506,7 +506,7 @@ namespace panvc3_b200 {
 		t_index							*m_index{};
 		// input, pinned
 		pinned_vector <std::uint16_t>	m_src_row, m_dst_row, m_dst_ref, m_cig_len, m_mate_row;
-		pinned_vector <std::uint32_t>	m_src_pos, m_seq_len, m_cig, m_mate_pos;
+		pinned_vector <std::uint32_t>	m_src_pos, m_seq_len, m_cig, m_mate_pos, m_exc_rec, m_exc_off;
 		pinned_vector <std::uint8_t>	m_seq, m_qual, m_has_qual;
 		std::vector <std::uint64_t>		m_seq_off{0}, m_cig_off{0}, m_qual_off{0};     // host only: chunk cuts
 		bool							m_any_qual{}, m_mates{};
@@ -533,7 +533,7 @@ namespace panvc3_b200 {
 		void clear()
 		{
 			for (auto *v : { &m_src_row, &m_dst_row, &m_dst_ref, &m_cig_len, &m_mate_row }) v->clear();
-			for (auto *v : { &m_src_pos, &m_seq_len, &m_cig, &m_mate_pos }) v->clear();
+			for (auto *v : { &m_src_pos, &m_seq_len, &m_cig, &m_mate_pos, &m_exc_rec, &m_exc_off }) v->clear();
 			for (auto *v : { &m_seq, &m_qual, &m_has_qual }) v->clear();
 			m_seq_off.assign(1, 0); m_cig_off.assign(1, 0); m_qual_off.assign(1, 0);
 			m_any_qual = false; m_mates = false; m_flushed = 0;
@@ -553,8 +553,18 @@ namespace panvc3_b200 {
 			std::size_t const i(size());
 			m_src_row.push_back(std::uint16_t(src_row)); m_dst_row.push_back(std::uint16_t(dst_row)); m_dst_ref.push_back(std::uint16_t(dst_ref));
 			m_src_pos.push_back(std::uint32_t(src_pos)); m_seq_len.push_back(std::uint32_t(query_seq.size())); m_cig_len.push_back(std::uint16_t(cigar_seq.size()));
-			std::uint8_t *sp(m_seq.append(query_seq.size()));
-			for (std::size_t k(0); k < query_seq.size(); ++k) sp[k] = t_traits::seq_rank(query_seq[k]);
+			// SEQ in two bits per base (pv3_batch_in.seq_2bit): A C G T (dna5 ranks 0 1 2 4) = 0 1 2 3, four per byte, base 4 b + i in
+			// bits 2 i; every other base goes to the exception list as an N
+			std::size_t const n_bytes((query_seq.size() + 3) / 4);
+			std::uint8_t *sp(m_seq.append(n_bytes));
+			for (std::size_t b(0); b < n_bytes; ++b) sp[b] = 0;
+			for (std::size_t k(0); k < query_seq.size(); ++k)
+			{
+				std::uint8_t const rank(t_traits::seq_rank(query_seq[k]));
+				std::uint8_t const code(rank < 3 ? rank : std::uint8_t(3));
+				if (3 == rank || rank > 4) { m_exc_rec.push_back(std::uint32_t(i)); m_exc_off.push_back(std::uint32_t(k)); }
+				else sp[k / 4] = std::uint8_t(sp[k / 4] | (code << (2 * (k % 4))));
+			}
 			std::uint32_t *cp(m_cig.append(cigar_seq.size()));
 			for (std::size_t k(0); k < cigar_seq.size(); ++k) cp[k] = (t_traits::cigar_count(cigar_seq[k]) << 4) | bam_op(t_traits::cigar_op_char(cigar_seq[k]));
 			if (0 == i % 8) m_has_qual.push_back(0);
@@ -586,7 +596,8 @@ namespace panvc3_b200 {
 			m_index->commit();
 			m_index->set_params(gap_opening_cost, gap_extension_cost);
 			pv3_batch_in in{};
-			in.n = n; in.compact = 1; in.seq_bam4 = 0;
+			in.n = n; in.compact = 1; in.seq_bam4 = 0; in.seq_2bit = 1;
+			in.n_seq_exceptions = m_exc_rec.size(); in.exc_rec = m_exc_rec.data(); in.exc_off = m_exc_off.data();
 			in.src_row16 = m_src_row.data(); in.dst_row16 = m_dst_row.data(); in.dst_ref16 = m_dst_ref.data(); in.src_pos32 = m_src_pos.data();
 			in.seq_len = m_seq_len.data(); in.cig_len16 = m_cig_len.data(); in.has_qual = m_any_qual ? m_has_qual.data() : nullptr;
 			in.seq_off = m_seq_off.data(); in.cig_off = m_cig_off.data(); in.qual_off = m_any_qual ? m_qual_off.data() : nullptr;

@@ -105,6 +105,8 @@ class RecordBatch:
     qual_off: np.ndarray | None = None
     qual: np.ndarray | None = None
     seq_len: np.ndarray | None = None     # set ⇒ seq is BAM 4-bit packed, seq_off counts bytes (pv3_batch_in.seq_len)
+    exc_rec: np.ndarray | None = None     # set (with exc_off, seq_len) ⇒ seq is TWO-bit packed (pv3_batch_in.seq_2bit): the N bases are listed here
+    exc_off: np.ndarray | None = None
 
     def __post_init__(self) -> None:
         self.src_row = np.ascontiguousarray(self.src_row, dtype=np.uint32)
@@ -243,6 +245,28 @@ class RecordBatch:
                            seq=packed, cig_off=self.cig_off, cig=self.cig, qual_off=self.qual_off, qual=self.qual,
                            seq_len=lens.astype(np.uint32))
 
+    def to_2bit(self) -> "RecordBatch":
+        """The same records with SEQ in two bits per base (pv3_batch_in.seq_2bit): A C G T = 0 1 2 3, four bases per byte, base
+        4 k + i in bits 2 i of byte k, records byte-aligned; every other base (dna5's N) listed in exc_rec / exc_off. Compact
+        encoding only (Context.project(..., compact=...))."""
+        assert self.seq_len is None
+        n = self.n
+        lens = np.diff(self.seq_off).astype(np.int64)
+        nbytes = (lens + 3) // 4
+        off = np.zeros(n + 1, dtype=np.uint64)
+        off[1:] = np.cumsum(nbytes)
+        code = np.array([0, 1, 2, 0, 3, 0, 0, 0], dtype=np.uint8)[np.minimum(self.seq, 7)]          # dna5 ranks A C G N T
+        padded = np.zeros(4 * int(off[-1]), dtype=np.uint8)
+        rec_of = np.repeat(np.arange(n, dtype=np.int64), lens)
+        within = np.arange(self.seq.size, dtype=np.int64) - np.repeat(self.seq_off[:-1].astype(np.int64), lens)
+        if self.seq.size:
+            padded[4 * off[:-1].astype(np.int64)[rec_of] + within] = code
+        packed = padded[0::4] | (padded[1::4] << 2) | (padded[2::4] << 4) | (padded[3::4] << 6)
+        is_n = np.flatnonzero(~np.isin(self.seq, (0, 1, 2, 4)))
+        return RecordBatch(src_row=self.src_row, dst_row=self.dst_row, dst_ref=self.dst_ref, src_pos=self.src_pos, seq_off=off,
+                           seq=packed.astype(np.uint8), cig_off=self.cig_off, cig=self.cig, qual_off=self.qual_off, qual=self.qual,
+                           seq_len=lens.astype(np.uint32), exc_rec=rec_of[is_n].astype(np.uint32), exc_off=within[is_n].astype(np.uint32))
+
     def compact_arrays(self, mates=None) -> dict:
         """The narrow arrays of the compact encoding (pv3_batch_in.compact): what crosses PCIe instead of the u32 ids, u64
         positions and the three u64 offset arrays."""
@@ -263,7 +287,8 @@ class RecordBatch:
 
     def compact_input_bytes(self, mates: bool = False) -> int:
         n = self.n
-        return n * (6 + 4 + 4 + 2 + (6 if mates else 0)) + (n + 7) // 8 + self.seq.nbytes + self.cig.nbytes
+        exc = (self.exc_rec.nbytes + self.exc_off.nbytes) if self.exc_rec is not None else 0
+        return n * (6 + 4 + 4 + 2 + (6 if mates else 0)) + (n + 7) // 8 + self.seq.nbytes + self.cig.nbytes + exc
 
     def input_bytes(self) -> int:
         tot = sum(a.nbytes for a in (self.src_row, self.dst_row, self.dst_ref, self.src_pos, self.seq_off, self.seq, self.cig_off, self.cig))

@@ -37,7 +37,9 @@ class BatchIn(C.Structure):
                 # ABI 5
                 ("mate_row", C.c_void_p), ("mate_pos", C.c_void_p), ("compact", C.c_int), ("seq_bam4", C.c_int),
                 ("src_row16", C.c_void_p), ("dst_row16", C.c_void_p), ("dst_ref16", C.c_void_p), ("mate_row16", C.c_void_p),
-                ("src_pos32", C.c_void_p), ("mate_pos32", C.c_void_p), ("cig_len16", C.c_void_p), ("has_qual", C.c_void_p)]
+                ("src_pos32", C.c_void_p), ("mate_pos32", C.c_void_p), ("cig_len16", C.c_void_p), ("has_qual", C.c_void_p),
+                # ABI 6
+                ("seq_2bit", C.c_int), ("n_seq_exceptions", C.c_uint64), ("exc_rec", C.c_void_p), ("exc_off", C.c_void_p)]
 
 
 class BatchOut(C.Structure):
@@ -266,7 +268,13 @@ class Context:
             bi.mate_row, bi.mate_pos = _ptr(mr), _ptr(mp)
         if compact is not None:
             bi.compact = 1
-            bi.seq_bam4 = 1 if batch.seq_len is not None else 0
+            two_bit = getattr(batch, "exc_rec", None) is not None
+            bi.seq_bam4 = 1 if (batch.seq_len is not None and not two_bit) else 0
+            if two_bit:
+                er = compact.get("exc_rec", batch.exc_rec); eo = compact.get("exc_off", batch.exc_off)
+                keep += [er, eo]
+                bi.seq_2bit, bi.n_seq_exceptions = 1, int(er.size)
+                bi.exc_rec, bi.exc_off = (_ptr(er), _ptr(eo)) if er.size else (None, None)
             for k in ("src_row16", "dst_row16", "dst_ref16", "src_pos32", "cig_len16", "has_qual", "mate_row16", "mate_pos32"):
                 setattr(bi, k, _ptr(compact.get(k)))
             bi.seq_len = _ptr(compact["seq_len"])

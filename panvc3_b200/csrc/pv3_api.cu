@@ -115,7 +115,8 @@ int pv3_create(pv3_ctx **out, int device)
 	if (const char *e = getenv("PV3_CHUNK_EDGE_LAST")) { long long v = atoll(e); if (v >= 0) ctx->chunk_edge_last = (uint64_t) v; }
 	if (const char *e = getenv("PV3_CHUNK_EDGE")) { long long v = atoll(e); if (v >= 0) ctx->chunk_edge = (uint64_t) v; }
 	bool ok = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess
-		&& cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) == cudaSuccess;
+		&& cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking) == cudaSuccess
+		&& cudaStreamCreateWithFlags(&ctx->stream3, cudaStreamNonBlocking) == cudaSuccess;
 	ctx->stream = ctx->own_stream;
 	for (auto &ws : ctx->sets) {
 		for (auto &ev : ws.ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
@@ -138,6 +139,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	if (ctx->own_stream) cudaStreamSynchronize(ctx->own_stream);
 	if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
+	if (ctx->stream3) cudaStreamSynchronize(ctx->stream3);
 	for (auto &ws : ctx->sets) ws.release();
 	for (auto &r : ctx->rows) r.mem.release();
 	for (auto &r : ctx->refs) r.mem.release();
@@ -149,6 +151,7 @@ void pv3_destroy(pv3_ctx *ctx)
 	if (ctx->h_reports) cudaFreeHost(ctx->h_reports);
 	for (auto &ev : ctx->ev_misc) if (ev) cudaEventDestroy(ev);
 	if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+	if (ctx->stream3) cudaStreamDestroy(ctx->stream3);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -196,6 +199,7 @@ int pv3_index_remove_ref(pv3_ctx *ctx, int ref_id)
 	cudaStreamSynchronize(ctx->stream);
 	cudaStreamSynchronize(ctx->own_stream);
 	cudaStreamSynchronize(ctx->stream2);
+	cudaStreamSynchronize(ctx->stream3);
 	HostRef &ref = ctx->refs[ref_id];
 	ctx->target_code_bytes -= std::min <uint64_t>(ctx->target_code_bytes, (ref.n + 1) / 2);
 	ref.mem.release();
@@ -214,6 +218,7 @@ int pv3_index_commit(pv3_ctx *ctx)
 	if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 	cudaStreamSynchronize(ctx->own_stream);
 	cudaStreamSynchronize(ctx->stream2);
+	cudaStreamSynchronize(ctx->stream3);
 
 	// host mirrors of the descriptor tables: entries of rows / contigs uploaded by earlier commits stay as they are
 	std::vector <RowDesc> &rd = ctx->h_row_desc;

@@ -66,8 +66,11 @@ struct pv3_ctx {
 	int          n_sms = 148;
 	cudaStream_t stream = nullptr;       // the stream all work is issued on
 	cudaStream_t own_stream = nullptr;
-	cudaStream_t stream2 = nullptr;      // second stream of the chunked host pipeline
-	pv3::WorkSet sets[2];
+	cudaStream_t stream2 = nullptr, stream3 = nullptr;      // further streams of the chunked host pipeline
+	// Work sets of the host pipeline, used round robin by the chunks of a call: with two, the upload of chunk c + 2 waited for
+	// chunk c's write-back (same stream) and the copy engine idled once uploads were short (two-bit SEQ); three keep it busy.
+	static constexpr int N_SETS = 3;
+	pv3::WorkSet sets[N_SETS];
 	cudaEvent_t  ev_misc[4] = {};
 	std::string  error;
 
@@ -88,7 +91,7 @@ struct pv3_ctx {
 	int32_t      gap_open = 0, gap_ext = -1;   // project-alignments/cmdline.ggo defaults
 	int32_t      lut[84];
 	int          stage = 0;
-	uint64_t     chunk_records = 500000;     // records per chunk of the host pipeline (PV3_CHUNK_RECORDS overrides)
+	uint64_t     chunk_records = 250000;     // records per chunk of the host pipeline (PV3_CHUNK_RECORDS overrides)
 	uint64_t     chunk_edge_last = 0;        // records of the last chunk when it should differ from the first (PV3_CHUNK_EDGE_LAST; 0 = chunk_edge)
 	uint64_t     chunk_edge = 125000;        // records of the first and the last chunk: a short pipeline fill and drain (PV3_CHUNK_EDGE; 0 = equal chunks)
 	uint64_t     dp_thread_min = 16384;      // fewer small runs than this: the warp-per-run kernel takes them all

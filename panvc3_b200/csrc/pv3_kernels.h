@@ -148,7 +148,7 @@ struct UnpackParams {
 	const uint8_t  *has_qual;     // bit i: record i has QUAL (as long as its SEQ); null: none has
 	const uint16_t *mate_row16;   // null: no mates
 	const uint32_t *mate_pos32;
-	int             seq_packed;   // SEQ bytes per record: (bases + 1) / 2 instead of bases
+	int             seq_packed;   // SEQ bytes per record on the device: 0 = bases, 1 = (bases + 1) / 2 (BAM 4-bit), 2 = 2 * ceil(bases / 4) (BAM 4-bit expanded from two-bit input)
 	uint32_t       *src_row, *dst_row, *dst_ref, *mate_row;
 	uint64_t       *src_pos, *mate_pos, *seq_off, *cig_off, *qual_off;   // qual_off null when has_qual is null
 	uint64_t       *tile_sums;    // scratch: 3 * pack_tiles(n) + 3 words
@@ -198,6 +198,9 @@ struct StreamOutParams {
 };
 void launch_stream_out(const StreamOutParams &P, cudaStream_t stream);
 uint64_t pack_tiles(uint64_t n);
+// two-bit SEQ (pv3_batch_in.seq_2bit) → BAM 4-bit layout, records padded to four bases; then the N exceptions
+void launch_expand_seq2(const uint8_t *seq2, uint64_t n_bytes2, uint8_t *seq4, const uint32_t *exc_rec, const uint32_t *exc_off, uint64_t n_exc,
+	uint64_t rec_base, const uint64_t *seq_off, cudaStream_t stream);
 void launch_unpack_in(const UnpackParams &P, cudaStream_t stream);
 void launch_pack_out(const PackParams &P, cudaStream_t stream);
 

@@ -9,6 +9,7 @@
 // 16-byte or lane-consecutive accesses.
 #include "pv3_device.cuh"
 #include "pv3_kernels.h"
+#include <algorithm>
 
 namespace pv3 {
 
@@ -49,7 +50,7 @@ __device__ uint64_t block_excl_scan(uint64_t v, uint64_t *smem /* 9 words */, ui
 __device__ __forceinline__ void in_lengths(const UnpackParams &P, uint64_t i, uint64_t &seq_b, uint64_t &cig_n, uint64_t &qual_n)
 {
 	uint32_t const bases = P.seq_len[i];
-	seq_b = P.seq_packed ? (uint64_t) ((bases + 1u) / 2u) : (uint64_t) bases;
+	seq_b = P.seq_packed == 2 ? 2ull * ((bases + 3u) / 4u) : P.seq_packed ? (uint64_t) ((bases + 1u) / 2u) : (uint64_t) bases;
 	cig_n = P.cig_len16[i];
 	qual_n = (P.has_qual && P.has_qual[i >> 3] >> (i & 7) & 1u) ? bases : 0u;
 }
@@ -229,6 +230,54 @@ void launch_stream_out(const StreamOutParams &P, cudaStream_t stream)
 }
 
 uint64_t pack_tiles(uint64_t n) { return (n + PK_TILE - 1) / PK_TILE; }
+
+// Two-bit SEQ → the 4-bit codes of a BAM record (A = 1, C = 2, G = 4, T = 8: 1 << code), first base in the high nibble.
+// A thread takes 4 input bytes (16 bases) and writes 8 output bytes; a record of ceil(L / 4) input bytes becomes
+// 2 ceil(L / 4) output bytes, so output offsets are twice the input offsets and no per-record work is needed.
+__global__ void __launch_bounds__(256) expand_seq2_kernel(const uint8_t *seq2, uint64_t n_bytes2, uint8_t *seq4)
+{
+	uint64_t const n_words = (n_bytes2 + 3) / 4;
+	for (uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; w < n_words; w += (uint64_t) gridDim.x * blockDim.x) {
+		uint32_t const x = reinterpret_cast <const uint32_t *>(seq2)[w];       // (buffers are padded to 64 bytes)
+		uint32_t o[2];
+		#pragma unroll
+		for (int h = 0; h < 2; ++h) {
+			uint32_t r = 0;
+			#pragma unroll
+			for (int b = 0; b < 2; ++b) {                                        // input byte 2 h + b → output bytes 2 b, 2 b + 1 of word h
+				uint32_t const v = (x >> (16 * h + 8 * b)) & 0xffu;
+				uint32_t const c0 = 1u << (v & 3u), c1 = 1u << ((v >> 2) & 3u), c2 = 1u << ((v >> 4) & 3u), c3 = 1u << ((v >> 6) & 3u);
+				r |= (((c0 << 4) | c1) | (((c2 << 4) | c3) << 8)) << (16 * b);
+			}
+			o[h] = r;
+		}
+		reinterpret_cast <uint2 *>(seq4)[w] = make_uint2(o[0], o[1]);
+	}
+}
+
+// base exc_off[j] of record exc_rec[j] is N (BAM code 15): OR the nibble with 0xf (atomic on the aligned word: neighbours may be hit at once)
+__global__ void __launch_bounds__(256) seq_exceptions_kernel(uint8_t *seq4, const uint32_t *exc_rec, const uint32_t *exc_off, uint64_t n_exc,
+	uint64_t rec_base, const uint64_t *seq_off)
+{
+	uint64_t const j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= n_exc) return;
+	uint64_t const r = (uint64_t) exc_rec[j] - rec_base;
+	uint32_t const o = exc_off[j];
+	uint64_t const byte = seq_off[r] + (o >> 1);
+	uint32_t const shift = 8u * (uint32_t) (byte & 3u) + ((o & 1u) ? 0u : 4u);
+	atomicOr(reinterpret_cast <unsigned int *>(seq4 + (byte & ~3ull)), 0xfu << shift);
+}
+
+void launch_expand_seq2(const uint8_t *seq2, uint64_t n_bytes2, uint8_t *seq4, const uint32_t *exc_rec, const uint32_t *exc_off, uint64_t n_exc,
+	uint64_t rec_base, const uint64_t *seq_off, cudaStream_t stream)
+{
+	if (n_bytes2) {
+		uint64_t const n_words = (n_bytes2 + 3) / 4;
+		unsigned const blocks = (unsigned) std::min <uint64_t>((n_words + 255) / 256, 148u * 16u);
+		expand_seq2_kernel<<<blocks, 256, 0, stream>>>(seq2, n_bytes2, seq4);
+	}
+	if (n_exc) seq_exceptions_kernel<<<(unsigned) ((n_exc + 255) / 256), 256, 0, stream>>>(seq4, exc_rec, exc_off, n_exc, rec_base, seq_off);
+}
 
 void launch_unpack_in(const UnpackParams &P, cudaStream_t stream)
 {

@@ -338,7 +338,8 @@ int host_enqueue(HostCall &hc)
 	uint64_t n_chunks = hc.own_streams ? (n + ctx->chunk_records / 2) / ctx->chunk_records : 1;
 	if (n_chunks < 1) n_chunks = 1;
 	if (n_chunks > 64) n_chunks = 64;
-	cudaStream_t const streams[2] = { ctx->stream, hc.own_streams ? ctx->stream2 : ctx->stream };
+	constexpr int NS = pv3_ctx::N_SETS;
+	cudaStream_t const streams[NS] = { ctx->stream, hc.own_streams ? ctx->stream2 : ctx->stream, hc.own_streams ? ctx->stream3 : ctx->stream };
 	// Chunk cuts (tile-aligned). Only the first chunk's upload and the last chunk's kernels and write-back are not hidden
 	// behind other chunks' transfers, so those two chunks are small and the ones between them large.
 	{
@@ -374,7 +375,8 @@ int host_enqueue(HostCall &hc)
 	if (getenv("PV3_NO_ZERO_COPY")) zero_copy = false;
 	hc.zero_copy = zero_copy;
 	bool const compact = in->compact != 0;
-	bool const packed = compact ? in->seq_bam4 != 0 : in->seq_len != nullptr;
+	bool const two_bit = compact && in->seq_2bit != 0;
+	bool const packed = compact ? (in->seq_bam4 != 0 || two_bit) : in->seq_len != nullptr;
 	bool const has_qual = compact ? in->has_qual != nullptr : in->qual_off != nullptr;
 	bool const mates = compact ? in->mate_row16 != nullptr : in->mate_row != nullptr;
 	const uint8_t *qual_alias = has_qual ? (const uint8_t *) mapped_alias(in->qual) : nullptr;
@@ -386,7 +388,7 @@ int host_enqueue(HostCall &hc)
 	PV3_CUDA(ctx, cudaMemsetAsync(ctx->running.p, 0, 16, streams[0]));
 	PV3_CUDA(ctx, cudaEventRecord(ctx->ev_misc[2], streams[0]));
 	for (uint64_t c = 0; c < n_chunks; ++c) {
-		int const k = (int) (c % 2);
+		int const k = (int) (c % NS);
 		WorkSet &ws = ctx->sets[k];
 		ws.stream = streams[k];
 		cudaStream_t const stream = ws.stream;
@@ -416,7 +418,16 @@ int host_enqueue(HostCall &hc)
 			if (has_qual) add(6, in->has_qual + b / 8, (m + 7) / 8);
 			if (mates) { add(8, in->mate_row16 + b, m * 2); add(9, in->mate_pos32 + b, m * 4); }
 		}
-		add(10, in->seq + s0, s1 - s0);
+		uint64_t x0 = 0, x1 = 0;                                      // this chunk's N exceptions (sorted by record)
+		if (two_bit) {
+			if (in->n_seq_exceptions) {
+				x0 = (uint64_t) (std::lower_bound(in->exc_rec, in->exc_rec + in->n_seq_exceptions, (uint32_t) b) - in->exc_rec);
+				x1 = (uint64_t) (std::lower_bound(in->exc_rec, in->exc_rec + in->n_seq_exceptions, (uint32_t) e) - in->exc_rec);
+			}
+			add(13, in->seq + s0, s1 - s0);
+			if (x1 > x0) { add(14, in->exc_rec + x0, (x1 - x0) * 4); add(15, in->exc_off + x0, (x1 - x0) * 4); }
+			PV3_CUDA(ctx, ws.in[10].ensure_idle(2 * (s1 - s0) + 128, stream));
+		} else add(10, in->seq + s0, s1 - s0);
 		add(11, in->cig + c0, (c1 - c0) * 4);
 		if (qual_bulk) add(12, in->qual + q0, q1 - q0);
 		for (int i = 0; i < n_copies; ++i) PV3_CUDA(ctx, ws.in[copies[i].slot].ensure_idle((copies[i].bytes ? copies[i].bytes : 16) + 64, stream));
@@ -454,7 +465,7 @@ int host_enqueue(HostCall &hc)
 			U.src_pos32 = ws.in[3].as <uint32_t>(); U.seq_len = ws.in[4].as <uint32_t>(); U.cig_len16 = ws.in[5].as <uint16_t>();
 			U.has_qual = has_qual ? ws.in[6].as <uint8_t>() : nullptr;
 			U.mate_row16 = mates ? ws.in[8].as <uint16_t>() : nullptr; U.mate_pos32 = mates ? ws.in[9].as <uint32_t>() : nullptr;
-			U.seq_packed = packed ? 1 : 0;
+			U.seq_packed = two_bit ? 2 : packed ? 1 : 0;
 			U.src_row = ws.un[0].as <uint32_t>(); U.dst_row = ws.un[1].as <uint32_t>(); U.dst_ref = ws.un[2].as <uint32_t>();
 			U.src_pos = ws.un[3].as <uint64_t>(); U.seq_off = ws.un[4].as <uint64_t>(); U.cig_off = ws.un[5].as <uint64_t>();
 			U.qual_off = has_qual ? ws.un[6].as <uint64_t>() : nullptr;
@@ -463,6 +474,12 @@ int host_enqueue(HostCall &hc)
 			launch_unpack_in(U, stream);
 			PV3_CUDA(ctx, cudaGetLastError());
 			hc.launches += 3;
+			if (two_bit) {
+				launch_expand_seq2(ws.in[13].as <uint8_t>(), s1 - s0, ws.in[10].as <uint8_t>(), ws.in[14].as <uint32_t>(), ws.in[15].as <uint32_t>(), x1 - x0,
+					b, U.seq_off, stream);
+				PV3_CUDA(ctx, cudaGetLastError());
+				hc.launches += (s1 > s0 ? 1 : 0) + (x1 > x0 ? 1 : 0);
+			}
 			B.in.src_row = U.src_row; B.in.dst_row = U.dst_row; B.in.dst_ref = U.dst_ref; B.in.src_pos = U.src_pos;
 			B.in.seq_off = U.seq_off; B.in.cig_off = U.cig_off;          // chunk-relative: they start at 0
 			B.in.seq = ws.in[10].as <uint8_t>(); B.in.cig = ws.in[11].as <uint32_t>();
@@ -526,7 +543,7 @@ int host_enqueue(HostCall &hc)
 			K.cig_dst_word0 = zero_copy ? (((uint64_t) (uintptr_t) d_cig.alias) >> 2) + hc.cig_place : 0;
 		}
 		mark(c, 2, stream);
-		PV3_CUDA(ctx, cudaStreamWaitEvent(stream, c == 0 ? ctx->ev_misc[2] : ctx->sets[(c - 1) % 2].ev[5], 0));
+		PV3_CUDA(ctx, cudaStreamWaitEvent(stream, c == 0 ? ctx->ev_misc[2] : ctx->sets[(c - 1) % NS].ev[5], 0));
 		PV3_CUDA(ctx, cudaEventRecord(ws.cev[2], stream));
 		mark(c, 3, stream);
 		launch_pack_out(K, stream);
@@ -590,7 +607,7 @@ int host_finish(HostCall &hc, uint64_t &cig_used, uint64_t &rr_used)
 	uint64_t flagged = 0, realigned = 0, cells = 0, n_deferred = 0;
 	for (uint64_t c = 0; c < hc.n_chunks; ++c) {
 		ChunkReport const &r = ctx->h_reports[c];
-		WorkSet &ws = ctx->sets[c % 2];
+		WorkSet &ws = ctx->sets[c % pv3_ctx::N_SETS];
 		uint64_t const m = hc.cuts[c + 1] - hc.cuts[c];
 		if (!m) continue;
 		if (!r.done) return fail(ctx, PV3_ERR_CUDA, "pv3_project: chunk %llu did not report", (unsigned long long) c);
@@ -617,7 +634,7 @@ void host_timing(HostCall &hc)
 	pv3_ctx *ctx = hc.ctx;
 	float ms[5] = { 0, 0, 0, 0, 0 }, h2d = 0, d2h = 0, t = 0;
 	// events are reused by the chunks of a set: only the last chunk of every set is still on record
-	for (int k = 0; k < 2 && (uint64_t) k < hc.n_chunks; ++k) {
+	for (int k = 0; k < pv3_ctx::N_SETS && (uint64_t) k < hc.n_chunks; ++k) {
 		WorkSet &ws = ctx->sets[k];
 		harvest_timing(ctx, ws, ms);
 		if (cudaEventElapsedTime(&t, ws.cev[0], ws.cev[1]) == cudaSuccess) h2d += t;
@@ -638,7 +655,13 @@ int validate_host_batch(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out
 		if (!in->src_row16 || !in->dst_row16 || !in->dst_ref16 || !in->src_pos32 || !in->seq_len || !in->cig_len16)
 			return fail(ctx, PV3_ERR_INVALID, "%s: compact encoding needs src_row16, dst_row16, dst_ref16, src_pos32, seq_len, cig_len16", who);
 		if (ctx->rows.size() > 65536 || ctx->refs.size() > 65536) return fail(ctx, PV3_ERR_INVALID, "%s: compact encoding holds 16-bit ids", who);
-	} else if (!in->src_row || !in->dst_row || !in->dst_ref || !in->src_pos) return fail(ctx, PV3_ERR_INVALID, "%s: NULL input array", who);
+		if (in->seq_2bit && in->seq_bam4) return fail(ctx, PV3_ERR_INVALID, "%s: seq_2bit and seq_bam4 exclude each other", who);
+		if (in->seq_2bit && in->n_seq_exceptions && (!in->exc_rec || !in->exc_off)) return fail(ctx, PV3_ERR_INVALID, "%s: exc_rec and exc_off are required with n_seq_exceptions", who);
+		if (in->seq_2bit && in->n > 0xffffffffull) return fail(ctx, PV3_ERR_INVALID, "%s: two-bit SEQ addresses records with 32 bits", who);
+	} else if (in->seq_2bit) {
+		return fail(ctx, PV3_ERR_INVALID, "%s: seq_2bit needs the compact encoding", who);
+	}
+	if (!in->compact && (!in->src_row || !in->dst_row || !in->dst_ref || !in->src_pos)) return fail(ctx, PV3_ERR_INVALID, "%s: NULL input array", who);
 	if (!(out->dst_pos || out->dst_pos32) || !(out->cig_len || out->cig_len16) || !out->cig)
 		return fail(ctx, PV3_ERR_INVALID, "%s: dst_pos, cig_len (either width) and cig are required outputs", who);
 	return PV3_OK;
@@ -669,7 +692,8 @@ int pv3_project(pv3_ctx *ctx, const pv3_batch_in *in, pv3_batch_out *out)
 		st = host_enqueue(hc);
 		auto const t1 = std::chrono::steady_clock::now();
 		// whatever happened, nothing of this call may still be in flight when it returns: the caller owns the buffers again
-		cudaError_t const e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->stream2);
+		cudaError_t e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->stream2);
+		{ cudaError_t const e2 = cudaStreamSynchronize(ctx->stream3); if (e1 == cudaSuccess) e1 = e2; }
 		if (trace) {
 			auto const t2 = std::chrono::steady_clock::now();
 			dump_timeline(hc.n_chunks);
@@ -754,7 +778,8 @@ int pv3_multi_project(pv3_multi *m, const pv3_batch_in *in, pv3_batch_out *out)
 		for (size_t g = 0; g < G; ++g) {
 			pv3_ctx *c = m->ctx[g];
 			cudaSetDevice(c->device);
-			cudaError_t const e0 = cudaStreamSynchronize(c->stream), e1 = cudaStreamSynchronize(c->stream2);
+			cudaError_t e0 = cudaStreamSynchronize(c->stream), e1 = cudaStreamSynchronize(c->stream2);
+			{ cudaError_t const e2 = cudaStreamSynchronize(c->stream3); if (e1 == cudaSuccess) e1 = e2; }
 			if ((e0 != cudaSuccess || e1 != cudaSuccess) && !first_err) { first_err = fail(c, PV3_ERR_CUDA, "pv3_multi_project: %s", cudaGetErrorString(e0 != cudaSuccess ? e0 : e1)); err_ctx = c; }
 		}
 		if (first_err) return failm(first_err, err_ctx);

@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol(lib_path):
         assert hasattr(lib, n), f"{n} declared in include/ but not exported"
     from panvc3_b200 import capi
     assert sorted(capi.EXPORTED_SYMBOLS) == names
-    assert lib.pv3_abi_version() == 5
+    assert lib.pv3_abi_version() == 6
 
 
 def test_sass_is_sm100a(lib_path):

@@ -848,3 +848,58 @@ def test_chromosome_shape_paired_reads_all_paths(gpu, port):
         dh = dout.to_host()
         assert_same(dh, exp, b, f"{what}, device entry")
         assert np.array_equal(dh.mate_dst_pos[:k], mexp)
+
+
+def test_two_bit_seq_encoding(gpu, port, workflow_msa):
+    """pv3_batch_in.seq_2bit (ABI 6): SEQ as two bits per base with the N bases listed apart, compact encoding, host entry —
+    a batch large enough for several chunks (exceptions are cut per chunk), reads with N bases at every offset class, odd
+    lengths, an empty read; pageable and pinned memory, with mates and narrow output; equal to the oracle on the byte SEQ."""
+    from panvc3_b200.capi import PinnedArena, alloc_output
+    from panvc3_b200.workload import sample_reads
+    idx = device_index(workflow_msa)
+    oi = port.make_index(*casegen.index_inputs(workflow_msa))
+    b = sample_reads(workflow_msa, 300_000, 150, seed=91, ins=0.004, dele=0.004, clip_frac=0.1)
+    rng = np.random.default_rng(5)
+    seq = b.seq.copy()
+    hit = rng.random(seq.size) < 0.002                       # N bases anywhere (dna5 rank 3)
+    seq[hit] = 3
+    seq[int(b.seq_off[7]):int(b.seq_off[8])] = 3             # a read of Ns only
+    b = RecordBatch(src_row=b.src_row, dst_row=b.dst_row, dst_ref=b.dst_ref, src_pos=b.src_pos, seq_off=b.seq_off, seq=seq,
+                    cig_off=b.cig_off, cig=b.cig, qual_off=b.qual_off, qual=b.qual)
+    exp = oi.project_batch(b, 0, -1, n_threads=os.cpu_count() or 1)
+    t = b.to_2bit()
+    assert t.exc_rec.size > 1000 and t.seq.size < b.seq.size // 3
+    lens = np.asarray([u.size for u in workflow_msa.ungapped], dtype=np.int64)
+    mrow = rng.integers(1, workflow_msa.n_rows, b.n).astype(np.uint32)
+    mpos = (rng.random(b.n) * (lens[mrow] - 1)).astype(np.uint64)
+    idx.ctx.set_params(0, -1)
+    got = idx.ctx.project(t, compact=t.compact_arrays((mrow, mpos)))
+    assert_same(got, exp, b, "two-bit SEQ, pageable")
+    mexp = np.array([oi.project_position(int(r), 0, int(p)) for r, p in zip(mrow[:2000], mpos[:2000])], dtype=np.uint64)
+    assert np.array_equal(got.mate_dst_pos[:2000], mexp)
+    # pinned input and output, narrow fields
+    n = b.n
+    arena = PinnedArena(idx.ctx.lib, t.input_bytes() + n * 64 + int(exp.cig_len.sum()) * 8 + (1 << 24))
+    pb = RecordBatch.__new__(RecordBatch)
+    for k in ("src_row", "dst_row", "dst_ref", "src_pos", "seq_off", "seq", "cig_off", "cig", "qual_off", "qual", "seq_len", "exc_rec", "exc_off"):
+        a = getattr(t, k)
+        setattr(pb, k, None if a is None else _pinned_copy(arena, a))
+    comp = {k: (None if v is None else _pinned_copy(arena, v)) for k, v in t.compact_arrays((mrow, mpos)).items()}
+    pout = alloc_output(n, int(exp.cig_len.sum()) + 4096, int(exp.rr_len.sum()) + 64, arena)
+    narrow = dict(dst_pos32=arena.take((n,), np.uint32), flags8=arena.take((n,), np.uint8), cig_len16=arena.take((n,), np.uint16),
+                  rr_len8=arena.take((n,), np.uint8), mate_dst_pos32=arena.take((n,), np.uint32))
+    got = idx.ctx.project(pb, pout, compact=comp, narrow=narrow)
+    cl = narrow["cig_len16"].astype(np.uint32)
+    rl = narrow["rr_len8"].astype(np.uint32)
+    got = type(got)(dst_pos=narrow["dst_pos32"].astype(np.uint64), flags=narrow["flags8"].astype(np.uint32), cig_off=_exclusive(cl), cig_len=cl,
+                    cig=got.cig, rr_off=_exclusive(rl), rr_len=rl, rr=got.rr, mate_dst_pos=narrow["mate_dst_pos32"].astype(np.uint64))
+    assert_same(got, exp, b, "two-bit SEQ, pinned + narrow")
+    assert np.array_equal(got.mate_dst_pos[:2000], mexp)
+    # ragged shapes: odd lengths, an empty read, a read of one base
+    recs = [dict(src_row=1, dst_row=0, dst_ref=0, src_pos=5, seq="ACGTN", cigar="5M", qual=None),
+            dict(src_row=1, dst_row=0, dst_ref=0, src_pos=9, seq="", cigar="0M", qual=None),
+            dict(src_row=2, dst_row=0, dst_ref=0, src_pos=30, seq="N", cigar="1M", qual=None),
+            dict(src_row=2, dst_row=0, dst_ref=0, src_pos=40, seq="ACGTACGTACGTACGTA", cigar="17M", qual=None)]
+    sb = RecordBatch.from_records(recs)
+    st = sb.to_2bit()
+    assert_same(idx.ctx.project(st, compact=st.compact_arrays()), oi.project_batch(sb, 0, -1), sb, "two-bit SEQ, ragged")
